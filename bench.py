@@ -1,0 +1,292 @@
+#!/usr/bin/env python
+"""Headline benchmark: tokens/s (and MFU) of Llama-3.1-8B FSDP full-shard training, bf16, seq 4096,
+per-GPU batch 1 (weak scaling), synthetic tokens, random-init weights -- BASELINE.json's metric on
+BASELINE.json's config (reference script: 04-fully-sharded-data-parallel/train_llm.py).
+
+  python bench.py --gpus N --steps K --warmup W            # this framework
+  python bench.py --impl reference --gpus N ...            # the unmodified reference from baseline/_ref
+
+For N > 1 launch with ``python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N``.
+Rank 0 prints ONE JSON line. Timing: W untimed warm-up steps, then exactly K steps between
+barrier + synchronize, CUDA events on the launching stream, max over ranks. Every step streams the
+16 GB of weights (>> 126 MB L2), so no explicit L2 flush is needed ("inputs_exceed_l2").
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+BASELINE_PUBLISHED = None  # BASELINE.json "published" is {} -> vs_baseline is null
+PEAK_BF16_TFLOPS = 1637.5  # MEASURED_PEAKS.json (burst), used for the MFU note only
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clocks and throttle reasons of the local GPU during the timed region (NVML)."""
+
+    def __init__(self, index: int, period_s: float = 0.2):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period_s
+        self.samples, self.reasons = [], set()
+        self.max_mhz = None
+        self._stop = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+            getattr(nv, "nvmlClocksEventReasonHwPowerBrakeSlowdown", 0x80): "hw_power_brake",
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(self.period)
+
+    def stop(self):
+        self._stop.set()
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": 0}
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def _physical_gpu_index(local_rank: int) -> int:
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        try:
+            return int(vis.split(",")[local_rank])
+        except Exception:
+            return local_rank
+    return local_rank
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=8)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200train", choices=["b200train", "reference"])
+    ap.add_argument("--model", default="llama-3.1-8b")
+    ap.add_argument("--seq-len", type=int, default=4096)
+    ap.add_argument("--batch-size", type=int, default=1, help="per-GPU batch (reference default -b 1)")
+    ap.add_argument("--layers", type=int, default=None, help="debug only: truncating layers makes the run INVALID")
+    ap.add_argument("--no-fuse-optimizer", action="store_true")
+    return ap.parse_args()
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    from b200train import _C
+    from b200train.models import load_config
+    from b200train.parallel import make_strategy
+    from b200train.parallel.comm import init_distributed
+
+    rank, local_rank, world, device = init_distributed("cuda")
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world} (launch with torch.distributed.run)"
+    cfg = load_config(args.model)
+    if args.layers:
+        cfg.num_hidden_layers = args.layers
+    B, S = args.batch_size, args.seq_len
+    eng = make_strategy("fsdp", cfg, device, lr=3e-5, seed=0, fuse_optimizer=not args.no_fuse_optimizer)
+
+    def host_batch(i):
+        g = torch.Generator().manual_seed(1234 + i * world + rank)
+        ids = torch.randint(0, cfg.vocab_size, (B, S), generator=g)
+        return {"input_ids": ids.pin_memory(), "labels": ids.clone().pin_memory()}
+
+    n_total = args.warmup + 2 * args.steps
+    batches = [host_batch(i) for i in range(n_total)]
+    h2d = sum(t.numel() * t.element_size() for t in batches[0].values())
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- warm-up ----
+    for i in range(args.warmup):
+        loss = eng.train_step(batches[i])
+    float(loss)
+    sampler = ClockSampler(_physical_gpu_index(local_rank))
+    sampler.start()
+
+    # ---- region 1: end to end through the public API (pinned H2D of the inputs + D2H loss read) ----
+    sync_all()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    for i in range(args.steps):
+        loss = eng.train_step(batches[args.warmup + i])
+        lv = loss.item()          # device -> host read of the step result (4 bytes)
+    e1.record()
+    sync_all()
+    e2e_wall = time.perf_counter() - t0
+    e2e_ms = max(e0.elapsed_time(e1), e2e_wall * 1e3)
+
+    # ---- region 2: device-resident inputs, no host sync inside the region ----
+    dev_batches = [eng.to_device(b) for b in batches[args.warmup + args.steps:]]
+    sync_all()
+    launches0 = _C.launch_count()
+    e0.record()
+    for i in range(args.steps):
+        out = eng.forward(dev_batches[i])
+        eng.zero_grad()
+        eng.backward(out.loss)
+        eng.optimizer_step()
+    e1.record()
+    sync_all()
+    launches = _C.launch_count() - launches0
+    dev_ms = e0.elapsed_time(e1)
+    sampler.stop()
+    sampler.join(timeout=2)
+
+    t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_ms = t.tolist()
+    tokens = world * B * S * args.steps
+    value = tokens / (dev_ms / 1e3)
+    e2e_value = tokens / (e2e_ms / 1e3)
+    flops_tok = cfg.flops_per_token(S)
+    if rank == 0:
+        line = {
+            "metric": "tokens/sec, Llama-3.1-8B FSDP full-shard training (max over ranks)",
+            "value": round(value, 1),
+            "unit": "tokens/s",
+            "n_gpus": world,
+            "steps": args.steps,
+            "warmup": args.warmup,
+            "ms_per_step": round(dev_ms / args.steps, 3),
+            "higher_is_better": True,
+            "scaling": "weak",
+            "vs_baseline": BASELINE_PUBLISHED,
+            "dtype": "bf16",
+            "data": "synthetic tokens, random-init weights",
+            "impl": "b200train",
+            "config": {"model": cfg.name or args.model, "layers": cfg.num_hidden_layers,
+                       "global_batch": world * B, "seq_len": S,
+                       "parallelism": f"fsdp{world}", "l2": "inputs_exceed_l2 (16 GB of weights per step)",
+                       "optimizer": "AdamW bf16 state, update inside the timed step"},
+            "mfu_vs_measured_burst": round(value * flops_tok / (world * PEAK_BF16_TFLOPS * 1e12), 4),
+            "e2e": {"value": round(e2e_value, 1), "unit": "tokens/s", "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": 4, "ms_per_step": round(e2e_ms / args.steps, 3)},
+            "gpu_launches": int(launches),
+            "clocks": sampler.summary(),
+            "final_loss": round(lv, 4),
+            "peak_alloc_gb": round(torch.cuda.max_memory_allocated() / 1e9, 2),
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def run_reference(args):
+    sys.path.insert(0, os.path.join(ROOT, "baseline"))
+    import run_reference as rr
+
+    ok, why = rr.reference_available()
+    rank = int(os.environ.get("RANK", "0"))
+    if not ok:
+        if rank == 0:
+            print(json.dumps({"impl": "reference", "unavailable": why}), flush=True)
+        return
+    import torch
+
+    from b200train.models import load_config, to_hf_dict
+
+    cfg = load_config(args.model)
+    if args.layers:
+        cfg.num_hidden_layers = args.layers
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    sampler = ClockSampler(_physical_gpu_index(local_rank))
+    sampler.start()
+    try:
+        res = rr.run_reference("fsdp", to_hf_dict(cfg), args.batch_size, args.seq_len, args.steps, args.warmup)
+    except Exception as e:  # the reference failing to run offline is reported, not fatal
+        sampler.stop()
+        if rank == 0:
+            print(json.dumps({"impl": "reference", "unavailable": f"{type(e).__name__}: {str(e)[:300]}"}),
+                  flush=True)
+        return
+    sampler.stop()
+    sampler.join(timeout=2)
+    if rank == 0:
+        S = args.seq_len
+        line = {
+            "metric": "tokens/sec, Llama-3.1-8B FSDP full-shard training (max over ranks)",
+            "value": round(res["tokens_per_s"], 1),
+            "unit": "tokens/s",
+            "n_gpus": res["world"],
+            "steps": args.steps,
+            "warmup": args.warmup,
+            "ms_per_step": round(res["ms_per_step"], 3),
+            "higher_is_better": True,
+            "scaling": "weak",
+            "vs_baseline": BASELINE_PUBLISHED,
+            "dtype": "bf16",
+            "data": "synthetic tokens, random-init weights",
+            "impl": "reference",
+            "config": {"model": cfg.name or args.model, "layers": cfg.num_hidden_layers,
+                       "global_batch": res["world"] * args.batch_size, "seq_len": S,
+                       "parallelism": f"fsdp{res['world']}", "l2": "inputs_exceed_l2",
+                       "script": "04-fully-sharded-data-parallel/train_llm.py (unmodified, baseline/_ref)"},
+            "mfu_vs_measured_burst": round(res["tokens_per_s"] * cfg.flops_per_token(S)
+                                           / (res["world"] * PEAK_BF16_TFLOPS * 1e12), 4),
+            "e2e": {"value": round(res["e2e_tokens_per_s"], 1), "unit": "tokens/s",
+                    "h2d_bytes_per_step": 3 * args.batch_size * S * 8, "d2h_bytes_per_step": 4},
+            "gpu_launches": 0,
+            "clocks": sampler.summary(),
+            "peak_alloc_gb": round(res["peak_alloc_gb"], 2),
+        }
+        print(json.dumps(line), flush=True)
+    import torch.distributed as dist
+
+    if dist.is_initialized():
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

@@ -1,0 +1,883 @@
+// Memory-bound training ops for sm_100a, each one pass over its operands with 16-byte accesses:
+// RMSNorm / LayerNorm (+fused residual add) fwd+bwd, SwiGLU, gelu_new, RoPE, embedding gather /
+// scatter-add, cross-entropy (online softmax, in-place dlogits) and AdamW over flat bf16 buffers.
+//
+// These replace the chains of ATen eager kernels that the reference reaches through HF modeling
+// code (reference: 01-single-gpu/train_llm.py:65,140-149).
+#include "common.cuh"
+#include <math.h>
+
+namespace b2 {
+
+constexpr int kNormThreads = 256;
+constexpr int kNormMaxVec = 8;  // per-thread 16B vectors -> H <= 256*8*8 = 16384
+
+struct alignas(16) BF8 { uint32_t u[4]; };
+
+__device__ __forceinline__ void bf8_to_f(const BF8& v, float (&f)[8]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float2 t = unpack_bf16(v.u[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+__device__ __forceinline__ BF8 f_to_bf8(const float (&f)[8]) {
+  BF8 v;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) v.u[i] = pack_bf16(f[2 * i], f[2 * i + 1]);
+  return v;
+}
+__device__ __forceinline__ float bf16_round(float x) {
+  return __bfloat162float(__float2bfloat16_rn(x));
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+// block-wide sum; `red` is >= 33 floats of shared memory. All threads get the result.
+__device__ __forceinline__ float block_sum(float v, float* red) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  v = warp_sum(v);
+  __syncthreads();
+  if (lane == 0) red[w] = v;
+  __syncthreads();
+  if (w == 0) {
+    float t = lane < nw ? red[lane] : 0.f;
+    t = warp_sum(t);
+    if (lane == 0) red[32] = t;
+  }
+  __syncthreads();
+  return red[32];
+}
+__device__ __forceinline__ float block_max(float v, float* red) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  v = warp_max(v);
+  __syncthreads();
+  if (lane == 0) red[w] = v;
+  __syncthreads();
+  if (w == 0) {
+    float t = lane < nw ? red[lane] : -INFINITY;
+    t = warp_max(t);
+    if (lane == 0) red[32] = t;
+  }
+  __syncthreads();
+  return red[32];
+}
+
+// ------------------------------------------------------------------------------------------------
+// RMSNorm.  y = w * bf16(h * rsqrt(mean(h^2) + eps)),  h = x (+ res)   [HF LlamaRMSNorm rounding]
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kNormThreads)
+rmsnorm_fwd_kernel(__nv_bfloat16* __restrict__ y, float* __restrict__ rstd_out,
+                   __nv_bfloat16* __restrict__ h_out, const __nv_bfloat16* __restrict__ x,
+                   const __nv_bfloat16* __restrict__ res, const __nv_bfloat16* __restrict__ w,
+                   int H, float eps) {
+  __shared__ float red[33];
+  const int row = blockIdx.x;
+  const int nvec = H >> 3;
+  const BF8* xr = reinterpret_cast<const BF8*>(x + (size_t)row * H);
+  const BF8* rr = res ? reinterpret_cast<const BF8*>(res + (size_t)row * H) : nullptr;
+  float v[kNormMaxVec][8];
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < kNormMaxVec; ++i) {
+    const int idx = threadIdx.x + i * kNormThreads;
+    if (idx < nvec) {
+      bf8_to_f(xr[idx], v[i]);
+      if (rr) {
+        float r[8];
+        bf8_to_f(rr[idx], r);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[i][j] = bf16_round(v[i][j] + r[j]);
+        if (h_out) reinterpret_cast<BF8*>(h_out + (size_t)row * H)[idx] = f_to_bf8(v[i]);
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) ss += v[i][j] * v[i][j];
+    }
+  }
+  ss = block_sum(ss, red);
+  const float rstd = rsqrtf(ss / (float)H + eps);
+  if (threadIdx.x == 0 && rstd_out) rstd_out[row] = rstd;
+  const BF8* wr = reinterpret_cast<const BF8*>(w);
+  BF8* yr = reinterpret_cast<BF8*>(y + (size_t)row * H);
+#pragma unroll
+  for (int i = 0; i < kNormMaxVec; ++i) {
+    const int idx = threadIdx.x + i * kNormThreads;
+    if (idx < nvec) {
+      float wf[8], o[8];
+      bf8_to_f(wr[idx], wf);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = wf[j] * bf16_round(v[i][j] * rstd);
+      yr[idx] = f_to_bf8(o);
+    }
+  }
+}
+
+// Backward. Each block walks rows blockIdx.x, +gridDim.x, ... keeping its dw partial in registers,
+// then writes one fp32 partial row into `partial` [gridDim.x, H]; a second kernel folds those rows.
+//   dx = rstd * (dy*w - xhat * mean(dy*w*xhat)) (+ dres)
+template <int MV>
+__global__ void __launch_bounds__(kNormThreads)
+rmsnorm_bwd_kernel(__nv_bfloat16* __restrict__ dx, float* __restrict__ partial,
+                   const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ h,
+                   const __nv_bfloat16* __restrict__ w, const float* __restrict__ rstd,
+                   const __nv_bfloat16* __restrict__ dres, int T, int H) {
+  __shared__ float red[33];
+  const int nvec = H >> 3;
+  float dw[MV][8];
+  float wf[MV][8];
+#pragma unroll
+  for (int i = 0; i < MV; ++i) {
+    const int idx = threadIdx.x + i * kNormThreads;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dw[i][j] = 0.f;
+    if (idx < nvec) bf8_to_f(reinterpret_cast<const BF8*>(w)[idx], wf[i]);
+  }
+  for (int row = blockIdx.x; row < T; row += gridDim.x) {
+    const BF8* hr = reinterpret_cast<const BF8*>(h + (size_t)row * H);
+    const BF8* gr = reinterpret_cast<const BF8*>(dy + (size_t)row * H);
+    const float rs = rstd[row];
+    float xh[MV][8], g[MV][8];
+    float dot = 0.f;
+#pragma unroll
+    for (int i = 0; i < MV; ++i) {
+      const int idx = threadIdx.x + i * kNormThreads;
+      if (idx < nvec) {
+        bf8_to_f(hr[idx], xh[i]);
+        bf8_to_f(gr[idx], g[i]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          xh[i][j] *= rs;
+          dw[i][j] += g[i][j] * xh[i][j];
+          g[i][j] *= wf[i][j];
+          dot += g[i][j] * xh[i][j];
+        }
+      }
+    }
+    dot = block_sum(dot, red) / (float)H;
+    BF8* dxr = reinterpret_cast<BF8*>(dx + (size_t)row * H);
+    const BF8* drr = dres ? reinterpret_cast<const BF8*>(dres + (size_t)row * H) : nullptr;
+#pragma unroll
+    for (int i = 0; i < MV; ++i) {
+      const int idx = threadIdx.x + i * kNormThreads;
+      if (idx < nvec) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = rs * (g[i][j] - xh[i][j] * dot);
+        if (drr) {
+          float r[8];
+          bf8_to_f(drr[idx], r);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] += r[j];
+        }
+        dxr[idx] = f_to_bf8(o);
+      }
+    }
+  }
+  float* prow = partial + (size_t)blockIdx.x * H;
+#pragma unroll
+  for (int i = 0; i < MV; ++i) {
+    const int idx = threadIdx.x + i * kNormThreads;
+    if (idx < nvec) {
+      float4* p4 = reinterpret_cast<float4*>(prow + (size_t)idx * 8);
+      p4[0] = make_float4(dw[i][0], dw[i][1], dw[i][2], dw[i][3]);
+      p4[1] = make_float4(dw[i][4], dw[i][5], dw[i][6], dw[i][7]);
+    }
+  }
+}
+
+// out[h] (+)= sum_b partial[b, h]
+__global__ void fold_partials_kernel(__nv_bfloat16* __restrict__ out,
+                                     const float* __restrict__ partial, int nblocks, int H,
+                                     int accumulate) {
+  const int hcol = blockIdx.x * blockDim.x + threadIdx.x;
+  if (hcol >= H) return;
+  float s = 0.f;
+  for (int b = 0; b < nblocks; ++b) s += partial[(size_t)b * H + hcol];
+  if (accumulate) s += __bfloat162float(out[hcol]);
+  out[hcol] = __float2bfloat16_rn(s);
+}
+
+// ------------------------------------------------------------------------------------------------
+// LayerNorm (GPT-2): y = (x - mean) * rstd * w + b, optional residual add in front
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kNormThreads)
+layernorm_fwd_kernel(__nv_bfloat16* __restrict__ y, float* __restrict__ mean_out,
+                     float* __restrict__ rstd_out, __nv_bfloat16* __restrict__ h_out,
+                     const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res,
+                     const __nv_bfloat16* __restrict__ w, const __nv_bfloat16* __restrict__ b,
+                     int H, float eps) {
+  __shared__ float red[33];
+  const int row = blockIdx.x;
+  const int nvec = H >> 3;
+  const BF8* xr = reinterpret_cast<const BF8*>(x + (size_t)row * H);
+  const BF8* rr = res ? reinterpret_cast<const BF8*>(res + (size_t)row * H) : nullptr;
+  float v[kNormMaxVec][8];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < kNormMaxVec; ++i) {
+    const int idx = threadIdx.x + i * kNormThreads;
+    if (idx < nvec) {
+      bf8_to_f(xr[idx], v[i]);
+      if (rr) {
+        float r[8];
+        bf8_to_f(rr[idx], r);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[i][j] = bf16_round(v[i][j] + r[j]);
+        if (h_out) reinterpret_cast<BF8*>(h_out + (size_t)row * H)[idx] = f_to_bf8(v[i]);
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s += v[i][j];
+    }
+  }
+  const float mean = block_sum(s, red) / (float)H;
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < kNormMaxVec; ++i) {
+    const int idx = threadIdx.x + i * kNormThreads;
+    if (idx < nvec) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float d = v[i][j] - mean;
+        ss += d * d;
+      }
+    }
+  }
+  const float rstd = rsqrtf(block_sum(ss, red) / (float)H + eps);
+  if (threadIdx.x == 0) {
+    if (mean_out) mean_out[row] = mean;
+    if (rstd_out) rstd_out[row] = rstd;
+  }
+  BF8* yr = reinterpret_cast<BF8*>(y + (size_t)row * H);
+#pragma unroll
+  for (int i = 0; i < kNormMaxVec; ++i) {
+    const int idx = threadIdx.x + i * kNormThreads;
+    if (idx < nvec) {
+      float wf[8], bf[8], o[8];
+      bf8_to_f(reinterpret_cast<const BF8*>(w)[idx], wf);
+      bf8_to_f(reinterpret_cast<const BF8*>(b)[idx], bf);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mean) * rstd * wf[j] + bf[j];
+      yr[idx] = f_to_bf8(o);
+    }
+  }
+}
+
+// partial layout: [gridDim.x, 2, H]  (dw row then db row)
+__global__ void __launch_bounds__(kNormThreads)
+layernorm_bwd_kernel(__nv_bfloat16* __restrict__ dx, float* __restrict__ partial,
+                     const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ h,
+                     const __nv_bfloat16* __restrict__ w, const float* __restrict__ mean,
+                     const float* __restrict__ rstd, const __nv_bfloat16* __restrict__ dres, int T,
+                     int H) {
+  __shared__ float red[33];
+  const int nvec = H >> 3;
+  // GPT-2 scale hidden sizes only (H <= 4096): keep register use bounded
+  constexpr int MV = 2;
+  float dw[MV][8], db[MV][8], wf[MV][8];
+#pragma unroll
+  for (int i = 0; i < MV; ++i) {
+    const int idx = threadIdx.x + i * kNormThreads;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { dw[i][j] = 0.f; db[i][j] = 0.f; }
+    if (idx < nvec) bf8_to_f(reinterpret_cast<const BF8*>(w)[idx], wf[i]);
+  }
+  for (int row = blockIdx.x; row < T; row += gridDim.x) {
+    const BF8* hr = reinterpret_cast<const BF8*>(h + (size_t)row * H);
+    const BF8* gr = reinterpret_cast<const BF8*>(dy + (size_t)row * H);
+    const float mu = mean[row], rs = rstd[row];
+    float xh[MV][8], g[MV][8];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < MV; ++i) {
+      const int idx = threadIdx.x + i * kNormThreads;
+      if (idx < nvec) {
+        bf8_to_f(hr[idx], xh[i]);
+        bf8_to_f(gr[idx], g[i]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          xh[i][j] = (xh[i][j] - mu) * rs;
+          dw[i][j] += g[i][j] * xh[i][j];
+          db[i][j] += g[i][j];
+          g[i][j] *= wf[i][j];
+          s1 += g[i][j];
+          s2 += g[i][j] * xh[i][j];
+        }
+      }
+    }
+    s1 = block_sum(s1, red) / (float)H;
+    s2 = block_sum(s2, red) / (float)H;
+    BF8* dxr = reinterpret_cast<BF8*>(dx + (size_t)row * H);
+    const BF8* drr = dres ? reinterpret_cast<const BF8*>(dres + (size_t)row * H) : nullptr;
+#pragma unroll
+    for (int i = 0; i < MV; ++i) {
+      const int idx = threadIdx.x + i * kNormThreads;
+      if (idx < nvec) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = rs * (g[i][j] - s1 - xh[i][j] * s2);
+        if (drr) {
+          float r[8];
+          bf8_to_f(drr[idx], r);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] += r[j];
+        }
+        dxr[idx] = f_to_bf8(o);
+      }
+    }
+  }
+  float* pw = partial + (size_t)blockIdx.x * 2 * H;
+  float* pb = pw + H;
+#pragma unroll
+  for (int i = 0; i < MV; ++i) {
+    const int idx = threadIdx.x + i * kNormThreads;
+    if (idx < nvec) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        pw[(size_t)idx * 8 + j] = dw[i][j];
+        pb[(size_t)idx * 8 + j] = db[i][j];
+      }
+    }
+  }
+}
+
+__global__ void fold_partials2_kernel(__nv_bfloat16* __restrict__ dw, __nv_bfloat16* __restrict__ db,
+                                      const float* __restrict__ partial, int nblocks, int H,
+                                      int accumulate) {
+  const int hcol = blockIdx.x * blockDim.x + threadIdx.x;
+  if (hcol >= H) return;
+  float s = 0.f, t = 0.f;
+  for (int b = 0; b < nblocks; ++b) {
+    s += partial[(size_t)b * 2 * H + hcol];
+    t += partial[(size_t)b * 2 * H + H + hcol];
+  }
+  if (accumulate) {
+    s += __bfloat162float(dw[hcol]);
+    t += __bfloat162float(db[hcol]);
+  }
+  dw[hcol] = __float2bfloat16_rn(s);
+  db[hcol] = __float2bfloat16_rn(t);
+}
+
+// ------------------------------------------------------------------------------------------------
+// SwiGLU on a fused [T, 2I] gate|up buffer, and gelu_new
+// ------------------------------------------------------------------------------------------------
+__global__ void swiglu_fwd_kernel(__nv_bfloat16* __restrict__ out,
+                                  const __nv_bfloat16* __restrict__ gu, int T, int I) {
+  const int nvec = I >> 3;
+  const size_t total = (size_t)T * nvec;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const size_t row = i / nvec;
+    const int c = (int)(i - row * nvec);
+    const BF8* base = reinterpret_cast<const BF8*>(gu + row * 2 * (size_t)I);
+    float g[8], u[8], o[8];
+    bf8_to_f(base[c], g);
+    bf8_to_f(base[nvec + c], u);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float s = bf16_round(g[j] / (1.f + __expf(-g[j])));
+      o[j] = s * u[j];
+    }
+    reinterpret_cast<BF8*>(out + row * (size_t)I)[c] = f_to_bf8(o);
+  }
+}
+
+__global__ void swiglu_bwd_kernel(__nv_bfloat16* __restrict__ dgu,
+                                  const __nv_bfloat16* __restrict__ dout,
+                                  const __nv_bfloat16* __restrict__ gu, int T, int I) {
+  const int nvec = I >> 3;
+  const size_t total = (size_t)T * nvec;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const size_t row = i / nvec;
+    const int c = (int)(i - row * nvec);
+    const BF8* base = reinterpret_cast<const BF8*>(gu + row * 2 * (size_t)I);
+    float g[8], u[8], d[8], dg[8], du[8];
+    bf8_to_f(base[c], g);
+    bf8_to_f(base[nvec + c], u);
+    bf8_to_f(reinterpret_cast<const BF8*>(dout + row * (size_t)I)[c], d);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float sig = 1.f / (1.f + __expf(-g[j]));
+      const float silu = g[j] * sig;
+      du[j] = d[j] * silu;
+      dg[j] = d[j] * u[j] * (sig * (1.f + g[j] * (1.f - sig)));
+    }
+    BF8* ob = reinterpret_cast<BF8*>(dgu + row * 2 * (size_t)I);
+    ob[c] = f_to_bf8(dg);
+    ob[nvec + c] = f_to_bf8(du);
+  }
+}
+
+__device__ __forceinline__ float gelu_new_f(float x) {
+  const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+  return 0.5f * x * (1.f + tanhf(k0 * (x + k1 * x * x * x)));
+}
+__device__ __forceinline__ float gelu_new_grad(float x) {
+  const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+  const float t = tanhf(k0 * (x + k1 * x * x * x));
+  return 0.5f * (1.f + t) + 0.5f * x * (1.f - t * t) * k0 * (1.f + 3.f * k1 * x * x);
+}
+// mode 0: out = gelu(x);  mode 1: out = dout * gelu'(x)
+__global__ void gelu_kernel(__nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ x,
+                            const __nv_bfloat16* __restrict__ dout, size_t nvec, int mode) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec;
+       i += (size_t)gridDim.x * blockDim.x) {
+    float a[8], o[8];
+    bf8_to_f(reinterpret_cast<const BF8*>(x)[i], a);
+    if (mode == 0) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = gelu_new_f(a[j]);
+    } else {
+      float d[8];
+      bf8_to_f(reinterpret_cast<const BF8*>(dout)[i], d);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = d[j] * gelu_new_grad(a[j]);
+    }
+    reinterpret_cast<BF8*>(out)[i] = f_to_bf8(o);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// RoPE, in place on the first `nheads` heads of each row of a fused QKV buffer.
+// x: [T, row_stride] ; cos/sin: [P, D] bf16 tables ; pos: [T] int32 (nullptr -> t % seq_len)
+// out = x*cos + rotate_half(x)*sin ; sign = -1 applies the transpose (backward).
+// ------------------------------------------------------------------------------------------------
+__global__ void rope_kernel(__nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ cosT,
+                            const __nv_bfloat16* __restrict__ sinT, const int* __restrict__ pos,
+                            int T, int nheads, int D, int row_stride, int seq_len, float sign) {
+  const int half_vec = D >> 4;  // 16B vectors per half head
+  const size_t total = (size_t)T * nheads * half_vec;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % half_vec);
+    const size_t th = i / half_vec;
+    const int head = (int)(th % nheads);
+    const size_t t = th / nheads;
+    const int p = pos ? pos[t] : (int)(t % seq_len);
+    __nv_bfloat16* base = x + t * (size_t)row_stride + (size_t)head * D;
+    BF8* lo = reinterpret_cast<BF8*>(base) + c;
+    BF8* hi = reinterpret_cast<BF8*>(base + (D >> 1)) + c;
+    const BF8* cl = reinterpret_cast<const BF8*>(cosT + (size_t)p * D) + c;
+    const BF8* ch = reinterpret_cast<const BF8*>(cosT + (size_t)p * D + (D >> 1)) + c;
+    const BF8* sl = reinterpret_cast<const BF8*>(sinT + (size_t)p * D) + c;
+    const BF8* sh = reinterpret_cast<const BF8*>(sinT + (size_t)p * D + (D >> 1)) + c;
+    float a[8], b[8], c0[8], c1[8], s0[8], s1[8], oa[8], ob[8];
+    bf8_to_f(*lo, a);
+    bf8_to_f(*hi, b);
+    bf8_to_f(*cl, c0);
+    bf8_to_f(*ch, c1);
+    bf8_to_f(*sl, s0);
+    bf8_to_f(*sh, s1);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (sign > 0.f) {
+        // rotate_half(x) = [-x_hi, x_lo]
+        oa[j] = a[j] * c0[j] - b[j] * s0[j];
+        ob[j] = b[j] * c1[j] + a[j] * s1[j];
+      } else {
+        // transpose: d_lo = g_lo*cos_lo + g_hi*sin_hi ; d_hi = g_hi*cos_hi - g_lo*sin_lo
+        oa[j] = a[j] * c0[j] + b[j] * s1[j];
+        ob[j] = b[j] * c1[j] - a[j] * s0[j];
+      }
+    }
+    *lo = f_to_bf8(oa);
+    *hi = f_to_bf8(ob);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Embedding
+// ------------------------------------------------------------------------------------------------
+__global__ void embedding_fwd_kernel(__nv_bfloat16* __restrict__ out,
+                                     const __nv_bfloat16* __restrict__ table,
+                                     const long long* __restrict__ ids, int T, int H) {
+  const int nvec = H >> 3;
+  const size_t total = (size_t)T * nvec;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const size_t t = i / nvec;
+    const int c = (int)(i - t * nvec);
+    reinterpret_cast<BF8*>(out + t * (size_t)H)[c] =
+        reinterpret_cast<const BF8*>(table + (size_t)ids[t] * H)[c];
+  }
+}
+// dtable[ids[t], :] += dout[t, :]   (bf16x2 atomics; dtable must be zeroed or hold prior grads)
+__global__ void embedding_bwd_kernel(__nv_bfloat16* __restrict__ dtable,
+                                     const __nv_bfloat16* __restrict__ dout,
+                                     const long long* __restrict__ ids, int T, int H) {
+  const int npair = H >> 1;
+  const size_t total = (size_t)T * npair;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const size_t t = i / npair;
+    const int c = (int)(i - t * npair);
+    const __nv_bfloat162 v = reinterpret_cast<const __nv_bfloat162*>(dout + t * (size_t)H)[c];
+    atomicAdd(reinterpret_cast<__nv_bfloat162*>(dtable + (size_t)ids[t] * H) + c, v);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Cross entropy over bf16 logits [T, ld] (first V columns valid), fp32 math (HF upcasts to fp32).
+// fwd: lse[t], loss[t] (0 where label == ignore). bwd: dlogits = (softmax - onehot) * scale, in place
+// allowed; columns >= V and ignored rows are zeroed so the buffer can feed the wgrad GEMM directly.
+// `vocab_start` supports vocabulary-parallel shards: labels are global, columns are local.
+// ------------------------------------------------------------------------------------------------
+constexpr int kCEThreads = 512;
+
+__global__ void __launch_bounds__(kCEThreads)
+ce_fwd_kernel(float* __restrict__ lse_out, float* __restrict__ loss_out,
+              float* __restrict__ max_out, float* __restrict__ sum_out,
+              float* __restrict__ tgt_out, const __nv_bfloat16* __restrict__ logits,
+              const long long* __restrict__ labels, int V, int ld, int ignore_index,
+              int vocab_start) {
+  __shared__ float red[33];
+  const int row = blockIdx.x;
+  const __nv_bfloat16* lr = logits + (size_t)row * ld;
+  const int nvec = V >> 3;
+  float m = -INFINITY, s = 0.f;
+  for (int i = threadIdx.x; i < nvec; i += kCEThreads) {
+    float f[8];
+    bf8_to_f(reinterpret_cast<const BF8*>(lr)[i], f);
+    float lm = f[0];
+#pragma unroll
+    for (int j = 1; j < 8; ++j) lm = fmaxf(lm, f[j]);
+    if (lm > m) {
+      s *= __expf(m - lm);
+      m = lm;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += __expf(f[j] - m);
+  }
+  for (int i = (nvec << 3) + threadIdx.x; i < V; i += kCEThreads) {
+    const float f = __bfloat162float(lr[i]);
+    if (f > m) {
+      s *= __expf(m - f);
+      m = f;
+    }
+    s += __expf(f - m);
+  }
+  const float gm = block_max(m, red);
+  s = (m == -INFINITY) ? 0.f : s * __expf(m - gm);
+  const float gs = block_sum(s, red);
+  if (threadIdx.x == 0) {
+    const long long lab = labels[row];
+    const long long local = lab - vocab_start;
+    const bool mine = lab != ignore_index && local >= 0 && local < V;
+    const float tgt = mine ? __bfloat162float(lr[local]) : 0.f;
+    if (max_out) {  // vocabulary-parallel: export the shard statistics, finish after the exchange
+      max_out[row] = gm;
+      sum_out[row] = gs;
+      tgt_out[row] = tgt;
+    } else {
+      const float lse = gm + logf(gs);
+      lse_out[row] = lse;
+      loss_out[row] = (lab == ignore_index) ? 0.f : (lse - tgt);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kCEThreads)
+ce_bwd_kernel(__nv_bfloat16* __restrict__ dlogits, const __nv_bfloat16* __restrict__ logits,
+              const float* __restrict__ lse, const long long* __restrict__ labels, int V, int ld,
+              int ignore_index, int vocab_start, float scale_in,
+              const float* __restrict__ scale_ptr) {
+  const float scale = scale_ptr ? scale_in * (*scale_ptr) : scale_in;
+  const int row = blockIdx.x;
+  const __nv_bfloat16* lr = logits + (size_t)row * ld;
+  __nv_bfloat16* dr = dlogits + (size_t)row * ld;
+  const long long lab = labels[row];
+  const bool ignored = lab == ignore_index;
+  const long long local = lab - vocab_start;
+  const float l = lse[row];
+  const int nvec_all = ld >> 3;
+  for (int i = threadIdx.x; i < nvec_all; i += kCEThreads) {
+    float f[8], o[8];
+    bf8_to_f(reinterpret_cast<const BF8*>(lr)[i], f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int col = i * 8 + j;
+      float g = 0.f;
+      if (!ignored && col < V) {
+        g = __expf(f[j] - l);
+        if (col == local) g -= 1.f;
+        g *= scale;
+      }
+      o[j] = g;
+    }
+    reinterpret_cast<BF8*>(dr)[i] = f_to_bf8(o);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// AdamW over a flat bf16 parameter range with bf16 moments (matches torch fused AdamW on bf16
+// params: fp32 math per element, decoupled weight decay, bias correction). `grad_scale` folds the
+// 1/world factor of a data-parallel mean into the update.
+// ------------------------------------------------------------------------------------------------
+__global__ void adamw_kernel(__nv_bfloat16* __restrict__ p, __nv_bfloat16* __restrict__ m,
+                             __nv_bfloat16* __restrict__ v, const __nv_bfloat16* __restrict__ g,
+                             size_t n, float lr, float beta1, float beta2, float eps, float wd,
+                             float bc1, float bc2_sqrt, float grad_scale) {
+  const size_t nvec = n >> 3;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec;
+       i += (size_t)gridDim.x * blockDim.x) {
+    float pf[8], mf[8], vf[8], gf[8];
+    bf8_to_f(reinterpret_cast<const BF8*>(p)[i], pf);
+    bf8_to_f(reinterpret_cast<const BF8*>(m)[i], mf);
+    bf8_to_f(reinterpret_cast<const BF8*>(v)[i], vf);
+    bf8_to_f(reinterpret_cast<const BF8*>(g)[i], gf);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float gr = gf[j] * grad_scale;
+      pf[j] *= (1.f - lr * wd);
+      mf[j] = beta1 * mf[j] + (1.f - beta1) * gr;
+      vf[j] = beta2 * vf[j] + (1.f - beta2) * gr * gr;
+      const float denom = sqrtf(vf[j]) / bc2_sqrt + eps;
+      pf[j] -= (lr / bc1) * (mf[j] / denom);
+    }
+    reinterpret_cast<BF8*>(p)[i] = f_to_bf8(pf);
+    reinterpret_cast<BF8*>(m)[i] = f_to_bf8(mf);
+    reinterpret_cast<BF8*>(v)[i] = f_to_bf8(vf);
+  }
+  // tail (n % 8) handled by the first block
+  if (blockIdx.x == 0) {
+    for (size_t i = (nvec << 3) + threadIdx.x; i < n; i += blockDim.x) {
+      const float gr = __bfloat162float(g[i]) * grad_scale;
+      float pf = __bfloat162float(p[i]) * (1.f - lr * wd);
+      const float mf = beta1 * __bfloat162float(m[i]) + (1.f - beta1) * gr;
+      const float vf = beta2 * __bfloat162float(v[i]) + (1.f - beta2) * gr * gr;
+      pf -= (lr / bc1) * (mf / (sqrtf(vf) / bc2_sqrt + eps));
+      p[i] = __float2bfloat16_rn(pf);
+      m[i] = __float2bfloat16_rn(mf);
+      v[i] = __float2bfloat16_rn(vf);
+    }
+  }
+}
+
+// out = a + b (bf16), used for gradient accumulation into flat buffers and residual joins
+__global__ void add_kernel(__nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ a,
+                           const __nv_bfloat16* __restrict__ b, size_t nvec) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec;
+       i += (size_t)gridDim.x * blockDim.x) {
+    float x[8], y[8];
+    bf8_to_f(reinterpret_cast<const BF8*>(a)[i], x);
+    bf8_to_f(reinterpret_cast<const BF8*>(b)[i], y);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) x[j] += y[j];
+    reinterpret_cast<BF8*>(out)[i] = f_to_bf8(x);
+  }
+}
+
+static inline int ew_grid(size_t work_items, int threads) {
+  size_t b = (work_items + threads - 1) / threads;
+  const size_t cap = (size_t)sm_count() * 16;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+}  // namespace b2
+
+using namespace b2;
+typedef __nv_bfloat16 bf16;
+
+extern "C" {
+
+int b2_rmsnorm_bwd_partial_rows(int T) {
+  int nb = sm_count() * 4;
+  return nb < T ? nb : T;
+}
+
+int b2_rmsnorm_fwd(void* y, float* rstd, void* h_out, const void* x, const void* res,
+                   const void* w, int T, int H, float eps, cudaStream_t stream) {
+  B2_REQUIRE(H % 8 == 0 && H <= kNormThreads * kNormMaxVec * 8, "rmsnorm: unsupported H=%d", H);
+  if (T == 0) return 0;
+  rmsnorm_fwd_kernel<<<T, kNormThreads, 0, stream>>>((bf16*)y, rstd, (bf16*)h_out, (const bf16*)x,
+                                                     (const bf16*)res, (const bf16*)w, H, eps);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// partial: caller-provided fp32 scratch of b2_rmsnorm_bwd_partial_rows(T) * H floats
+int b2_rmsnorm_bwd(void* dx, void* dw, float* partial, const void* dy, const void* h,
+                   const void* w, const float* rstd, const void* dres, int T, int H,
+                   int accumulate_dw, cudaStream_t stream) {
+  B2_REQUIRE(H % 8 == 0 && H <= kNormThreads * kNormMaxVec * 8, "rmsnorm: unsupported H=%d", H);
+  if (T == 0) return 0;
+  const int nb = b2_rmsnorm_bwd_partial_rows(T);
+#define B2_RMS_BWD(MV)                                                                     \
+  rmsnorm_bwd_kernel<MV><<<nb, kNormThreads, 0, stream>>>(                                 \
+      (bf16*)dx, partial, (const bf16*)dy, (const bf16*)h, (const bf16*)w, rstd,           \
+      (const bf16*)dres, T, H)
+  if (H <= kNormThreads * 8 * 2) B2_RMS_BWD(2);
+  else if (H <= kNormThreads * 8 * 4) B2_RMS_BWD(4);
+  else B2_RMS_BWD(8);
+#undef B2_RMS_BWD
+  B2_CUDA_CHECK(cudaGetLastError());
+  fold_partials_kernel<<<(H + 255) / 256, 256, 0, stream>>>((bf16*)dw, partial, nb, H,
+                                                            accumulate_dw);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int b2_layernorm_fwd(void* y, float* mean, float* rstd, void* h_out, const void* x,
+                     const void* res, const void* w, const void* b, int T, int H, float eps,
+                     cudaStream_t stream) {
+  B2_REQUIRE(H % 8 == 0 && H <= kNormThreads * kNormMaxVec * 8, "layernorm: unsupported H=%d", H);
+  if (T == 0) return 0;
+  layernorm_fwd_kernel<<<T, kNormThreads, 0, stream>>>((bf16*)y, mean, rstd, (bf16*)h_out,
+                                                       (const bf16*)x, (const bf16*)res,
+                                                       (const bf16*)w, (const bf16*)b, H, eps);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// partial: fp32 scratch of b2_rmsnorm_bwd_partial_rows(T) * 2 * H floats
+int b2_layernorm_bwd(void* dx, void* dw, void* db, float* partial, const void* dy, const void* h,
+                     const void* w, const float* mean, const float* rstd, const void* dres, int T,
+                     int H, int accumulate, cudaStream_t stream) {
+  B2_REQUIRE(H % 8 == 0 && H <= kNormThreads * 2 * 8, "layernorm bwd: unsupported H=%d", H);
+  if (T == 0) return 0;
+  const int nb = b2_rmsnorm_bwd_partial_rows(T);
+  layernorm_bwd_kernel<<<nb, kNormThreads, 0, stream>>>((bf16*)dx, partial, (const bf16*)dy,
+                                                        (const bf16*)h, (const bf16*)w, mean, rstd,
+                                                        (const bf16*)dres, T, H);
+  B2_CUDA_CHECK(cudaGetLastError());
+  fold_partials2_kernel<<<(H + 255) / 256, 256, 0, stream>>>((bf16*)dw, (bf16*)db, partial, nb, H,
+                                                             accumulate);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int b2_swiglu_fwd(void* out, const void* gu, int T, int I, cudaStream_t stream) {
+  B2_REQUIRE(I % 8 == 0, "swiglu: I=%d not a multiple of 8", I);
+  if (T == 0) return 0;
+  swiglu_fwd_kernel<<<ew_grid((size_t)T * (I / 8), 256), 256, 0, stream>>>((bf16*)out,
+                                                                           (const bf16*)gu, T, I);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+int b2_swiglu_bwd(void* dgu, const void* dout, const void* gu, int T, int I, cudaStream_t stream) {
+  B2_REQUIRE(I % 8 == 0, "swiglu: I=%d not a multiple of 8", I);
+  if (T == 0) return 0;
+  swiglu_bwd_kernel<<<ew_grid((size_t)T * (I / 8), 256), 256, 0, stream>>>(
+      (bf16*)dgu, (const bf16*)dout, (const bf16*)gu, T, I);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+int b2_gelu_fwd(void* out, const void* x, size_t n, cudaStream_t stream) {
+  B2_REQUIRE(n % 8 == 0, "gelu: n not a multiple of 8");
+  if (n == 0) return 0;
+  gelu_kernel<<<ew_grid(n / 8, 256), 256, 0, stream>>>((bf16*)out, (const bf16*)x, nullptr, n / 8,
+                                                       0);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+int b2_gelu_bwd(void* dx, const void* x, const void* dout, size_t n, cudaStream_t stream) {
+  B2_REQUIRE(n % 8 == 0, "gelu: n not a multiple of 8");
+  if (n == 0) return 0;
+  gelu_kernel<<<ew_grid(n / 8, 256), 256, 0, stream>>>((bf16*)dx, (const bf16*)x,
+                                                       (const bf16*)dout, n / 8, 1);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int b2_rope(void* x, const void* cosT, const void* sinT, const int* pos, int T, int nheads, int D,
+            int row_stride, int seq_len, int backward, cudaStream_t stream) {
+  B2_REQUIRE(D % 16 == 0 && row_stride % 8 == 0, "rope: D=%d row_stride=%d unsupported", D,
+             row_stride);
+  if (T == 0 || nheads == 0) return 0;
+  rope_kernel<<<ew_grid((size_t)T * nheads * (D / 16), 256), 256, 0, stream>>>(
+      (bf16*)x, (const bf16*)cosT, (const bf16*)sinT, pos, T, nheads, D, row_stride, seq_len,
+      backward ? -1.f : 1.f);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int b2_embedding_fwd(void* out, const void* table, const long long* ids, int T, int H,
+                     cudaStream_t stream) {
+  B2_REQUIRE(H % 8 == 0, "embedding: H=%d not a multiple of 8", H);
+  if (T == 0) return 0;
+  embedding_fwd_kernel<<<ew_grid((size_t)T * (H / 8), 256), 256, 0, stream>>>(
+      (bf16*)out, (const bf16*)table, ids, T, H);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+int b2_embedding_bwd(void* dtable, const void* dout, const long long* ids, int T, int H,
+                     cudaStream_t stream) {
+  B2_REQUIRE(H % 2 == 0, "embedding: H=%d odd", H);
+  if (T == 0) return 0;
+  embedding_bwd_kernel<<<ew_grid((size_t)T * (H / 2), 256), 256, 0, stream>>>(
+      (bf16*)dtable, (const bf16*)dout, ids, T, H);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int b2_ce_fwd(float* lse, float* loss, const void* logits, const long long* labels, int T, int V,
+              int ld, int ignore_index, cudaStream_t stream) {
+  B2_REQUIRE(ld % 8 == 0 && ld >= V, "ce: ld=%d V=%d unsupported", ld, V);
+  if (T == 0) return 0;
+  ce_fwd_kernel<<<T, kCEThreads, 0, stream>>>(lse, loss, nullptr, nullptr, nullptr,
+                                              (const bf16*)logits, labels, V, ld, ignore_index, 0);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+// vocabulary-parallel shard statistics: row max, sum exp(l - max), target logit (0 if not local)
+int b2_ce_shard_stats(float* row_max, float* row_sum, float* row_tgt, const void* logits,
+                      const long long* labels, int T, int V, int ld, int ignore_index,
+                      int vocab_start, cudaStream_t stream) {
+  B2_REQUIRE(ld % 8 == 0 && ld >= V, "ce: ld=%d V=%d unsupported", ld, V);
+  if (T == 0) return 0;
+  ce_fwd_kernel<<<T, kCEThreads, 0, stream>>>(nullptr, nullptr, row_max, row_sum, row_tgt,
+                                              (const bf16*)logits, labels, V, ld, ignore_index,
+                                              vocab_start);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+// effective scale = scale * (*scale_dev) when scale_dev (a device float) is given
+int b2_ce_bwd(void* dlogits, const void* logits, const float* lse, const long long* labels, int T,
+              int V, int ld, int ignore_index, int vocab_start, float scale, const float* scale_dev,
+              cudaStream_t stream) {
+  B2_REQUIRE(ld % 8 == 0 && ld >= V, "ce: ld=%d V=%d unsupported", ld, V);
+  if (T == 0) return 0;
+  ce_bwd_kernel<<<T, kCEThreads, 0, stream>>>((bf16*)dlogits, (const bf16*)logits, lse, labels, V,
+                                              ld, ignore_index, vocab_start, scale, scale_dev);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int b2_adamw(void* p, void* m, void* v, const void* g, size_t n, float lr, float beta1,
+             float beta2, float eps, float wd, int step, float grad_scale, int max_blocks,
+             cudaStream_t stream) {
+  if (n == 0) return 0;
+  B2_REQUIRE(((uintptr_t)p | (uintptr_t)m | (uintptr_t)v | (uintptr_t)g) % 16 == 0,
+             "adamw: buffers must be 16B aligned");
+  const float bc1 = 1.f - powf(beta1, (float)step);
+  const float bc2 = 1.f - powf(beta2, (float)step);
+  int grid = ew_grid(n / 8 + 1, 256);
+  if (max_blocks > 0 && grid > max_blocks) grid = max_blocks;
+  adamw_kernel<<<grid, 256, 0, stream>>>((bf16*)p, (bf16*)m, (bf16*)v, (const bf16*)g, n, lr,
+                                         beta1, beta2, eps, wd, bc1, sqrtf(bc2), grad_scale);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int b2_add(void* out, const void* a, const void* b, size_t n, cudaStream_t stream) {
+  B2_REQUIRE(n % 8 == 0, "add: n not a multiple of 8");
+  if (n == 0) return 0;
+  add_kernel<<<ew_grid(n / 8, 256), 256, 0, stream>>>((bf16*)out, (const bf16*)a, (const bf16*)b,
+                                                      n / 8);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

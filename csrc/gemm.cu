@@ -1,0 +1,488 @@
+// bf16 GEMM for sm_100a: C[M,N] = epilogue(A[M,K] * B[N,K]^T), fp32 accumulation in tensor memory.
+//
+// Structure (one persistent CTA, or CTA pair, per SM):
+//   warp 0      TMA producer   : cp.async.bulk.tensor loads of A/B k-blocks into a multi-stage ring
+//   warp 1      MMA issuer     : one elected lane issues tcgen05.mma (cta_group::1 or ::2), fp32 D in TMEM
+//   warp 2      TMEM allocator
+//   warps 4..7  epilogue       : tcgen05.ld TMEM -> registers -> (bias / GELU / accumulate) -> bf16 ->
+//                                128B-swizzled smem staging -> TMA store
+// The accumulator is double buffered in TMEM (2 x BN columns) so the epilogue of tile i overlaps the
+// main loop of tile i+1. Operands may be K-major ([rows, K], K contiguous) or MN-major ([K, rows],
+// rows contiguous): forward uses K/K, dgrad K/MN, wgrad MN/MN, so no transposes are materialised.
+//
+// Replaces the cuBLAS calls behind every nn.Linear / Conv1D of the reference
+// (reference: 01-single-gpu/train_llm.py:140,145 -> HF modeling -> F.linear).
+#include "common.cuh"
+#include <mutex>
+#include <unordered_map>
+#include <string>
+#include <cstring>
+#include <cstdarg>
+#include <cstdio>
+
+namespace b2 {
+
+constexpr int BM = 128;  // rows of C per CTA
+constexpr int BK = 64;   // k-block: one 128B swizzle span of bf16
+constexpr int kEpiChunk = 64;
+constexpr int kEpiStageBytes = BM * kEpiChunk * 2;  // 16 KB
+constexpr int kNumEpiStages = 2;
+constexpr int kSmemBudget = 232448 - 1024;  // max dynamic smem minus alignment slack
+
+enum Epilogue { EPI_NONE = 0, EPI_BIAS = 1, EPI_BIAS_GELU = 2, EPI_ACCUM = 3 };
+
+struct EpiArgs {
+  const __nv_bfloat16* bias;  // [N] (EPI_BIAS*)
+  const __nv_bfloat16* c_old; // [M, ldc] (EPI_ACCUM)
+  int ldc;
+};
+
+template <int kCta, int BN>
+struct GemmCfg {
+  static constexpr int kABytes = BM * BK * 2;
+  static constexpr int kBBytes = (BN / kCta) * BK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kEpiBytes = kNumEpiStages * kEpiStageBytes;
+  static constexpr int kStagesRaw = (kSmemBudget - kEpiBytes - 256) / kStageBytes;
+  static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + 256 + 1024;
+  static constexpr int kTmemCols = 2 * BN;  // double-buffered accumulator (power of two)
+};
+
+__device__ __forceinline__ float gelu_new(float x) {
+  // 0.5 x (1 + tanh(sqrt(2/pi) (x + 0.044715 x^3)))  (HF "gelu_new")
+  const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+  float u = k0 * (x + k1 * x * x * x);
+  float t = 1.f - 2.f / (1.f + __expf(2.f * u));
+  return 0.5f * x * (1.f + t);
+}
+
+template <int kCta, bool kAK, bool kBK, int kEpi, int BN>
+__global__ void __launch_bounds__(256, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const __grid_constant__ CUtensorMap tmC, int M, int N, int K, EpiArgs epi) {
+  using Cfg = GemmCfg<kCta, BN>;
+  constexpr int kStages = Cfg::kStages;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // swizzle-128B operands need 1024B alignment; align by hand (slack is included in kSmemBytes)
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + kStages * Cfg::kABytes;
+  uint8_t* smem_c = smem + kStages * Cfg::kStageBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_c + Cfg::kEpiBytes);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + kStages;
+  uint64_t* tfull_bar = bars + 2 * kStages;
+  uint64_t* tempty_bar = bars + 2 * kStages + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const uint32_t cta_rank = (kCta == 2) ? cluster_ctarank() : 0u;
+  const bool leader = cta_rank == 0;
+
+  if (warp == 0 && elect_one()) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmC);
+  }
+  if (warp == 1 && elect_one()) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull_bar[a], 1);
+      mbar_init(&tempty_bar[a], 4 * kCta);  // one arrival per epilogue warp of each CTA
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc<kCta>(tmem_slot, Cfg::kTmemCols);
+  tc_fence_before();
+  if constexpr (kCta == 2) cluster_sync_all(); else __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // ---- persistent tile schedule (identical in every role) ----
+  const int tile_m = BM * kCta;
+  const int num_m = (M + tile_m - 1) / tile_m;
+  const int num_n = (N + BN - 1) / BN;
+  const int num_tiles = num_m * num_n;
+  const int num_k = (K + BK - 1) / BK;
+  const int num_workers = gridDim.x / kCta;
+  const int worker = blockIdx.x / kCta;
+  constexpr int kGroupM = 8;
+  auto tile_coord = [&](int t, int& mb, int& nb) {
+    const int per_group = kGroupM * num_n;
+    const int g = t / per_group;
+    const int first_m = g * kGroupM;
+    const int gsz = min(num_m - first_m, kGroupM);
+    const int r = t - g * per_group;
+    mb = first_m + r % gsz;
+    nb = r / gsz;
+  };
+
+  if (warp == 0) {
+    // ================= TMA producer =================
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = worker; t < num_tiles; t += num_workers) {
+        int mb, nb;
+        tile_coord(t, mb, nb);
+        const int m0 = mb * tile_m + (int)cta_rank * BM;
+        const int n0 = nb * BN + (int)cta_rank * (BN / kCta);
+        for (int kb = 0; kb < num_k; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          if (leader) mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes * kCta);
+          const int k0 = kb * BK;
+          uint8_t* sa = smem_a + stage * Cfg::kABytes;
+          uint8_t* sb = smem_b + stage * Cfg::kBBytes;
+          if constexpr (kAK) tma_load_2d<kCta>(&tmA, &full_bar[stage], sa, k0, m0, kEvictNormal);
+          else tma_load_3d<kCta>(&tmA, &full_bar[stage], sa, 0, k0, m0 / 64, kEvictNormal);
+          if constexpr (kBK) tma_load_2d<kCta>(&tmB, &full_bar[stage], sb, k0, n0, kEvictNormal);
+          else tma_load_3d<kCta>(&tmB, &full_bar[stage], sb, 0, k0, n0 / 64, kEvictNormal);
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer (pair leader only) =================
+    if (leader) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM * kCta, BN, !kAK, !kBK);
+      // K-major: rows are 128B apart, 8-row groups 1024B apart (SBO); LBO unused.
+      // MN-major: 64-element MN atoms are BK*128 B apart (LBO), 8-row K groups 1024B apart (SBO).
+      constexpr uint32_t lbo_a = kAK ? 16 : BK * 128, lbo_b = kBK ? 16 : BK * 128;
+      constexpr uint32_t kstep_a = kAK ? 32 : 2048, kstep_b = kBK ? 32 : 2048;  // bytes per UMMA_K=16
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int t = worker; t < num_tiles; t += num_workers) {
+        if constexpr (kCta == 2) mbar_wait_cluster(&tempty_bar[acc], acc_phase ^ 1);
+        else mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * BN;
+        for (int kb = 0; kb < num_k; ++kb) {
+          if constexpr (kCta == 2) mbar_wait_cluster(&full_bar[stage], phase);
+          else mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          if (elect_one()) {
+            const uint32_t a_addr = smem_u32(smem_a + stage * Cfg::kABytes);
+            const uint32_t b_addr = smem_u32(smem_b + stage * Cfg::kBBytes);
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k) {
+              const uint64_t da = make_smem_desc_sw128(a_addr + k * kstep_a, lbo_a, 1024);
+              const uint64_t db = make_smem_desc_sw128(b_addr + k * kstep_b, lbo_b, 1024);
+              umma_f16<kCta>(tmem_d, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+            }
+            umma_commit<kCta>(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
+            if (kb == num_k - 1) umma_commit<kCta>(&tfull_bar[acc]);
+          }
+          __syncwarp();
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ================= epilogue =================
+    const int ew = warp - 4;                // TMEM lane quarter owned by this warp
+    const int row = ew * 32 + (int)lane_id();
+    const bool epi_leader = threadIdx.x == 128;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    uint32_t chunk_ctr = 0;
+    for (int t = worker; t < num_tiles; t += num_workers) {
+      int mb, nb;
+      tile_coord(t, mb, nb);
+      const int m0 = mb * tile_m + (int)cta_rank * BM;
+      const int n0 = nb * BN;
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + acc * BN;
+#pragma unroll 1
+      for (int c = 0; c < BN / kEpiChunk; ++c) {
+        uint32_t r0[32], r1[32];
+        tmem_ld_32x32b_x32(taddr + c * kEpiChunk, r0);
+        tmem_ld_32x32b_x32(taddr + c * kEpiChunk + 32, r1);
+        tmem_ld_wait();
+        if (c == BN / kEpiChunk - 1) {
+          // accumulator fully drained to registers: hand the TMEM stage back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane_id() == 0) {
+            if constexpr (kCta == 2) mbar_arrive_cluster(&tempty_bar[acc], 0);
+            else mbar_arrive(&tempty_bar[acc]);
+          }
+        }
+        const int col0 = n0 + c * kEpiChunk;
+        uint32_t packed[32];
+        if constexpr (kEpi == EPI_NONE) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            packed[j] = pack_bf16(__uint_as_float(r0[2 * j]), __uint_as_float(r0[2 * j + 1]));
+            packed[16 + j] = pack_bf16(__uint_as_float(r1[2 * j]), __uint_as_float(r1[2 * j + 1]));
+          }
+        } else if constexpr (kEpi == EPI_BIAS || kEpi == EPI_BIAS_GELU) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int col = col0 + 2 * j;
+            float b0 = 0.f, b1 = 0.f;
+            if (col < N) b0 = __bfloat162float(epi.bias[col]);
+            if (col + 1 < N) b1 = __bfloat162float(epi.bias[col + 1]);
+            float v0 = __uint_as_float(j < 16 ? r0[2 * j] : r1[2 * (j - 16)]) + b0;
+            float v1 = __uint_as_float(j < 16 ? r0[2 * j + 1] : r1[2 * (j - 16) + 1]) + b1;
+            if constexpr (kEpi == EPI_BIAS_GELU) { v0 = gelu_new(v0); v1 = gelu_new(v1); }
+            packed[j] = pack_bf16(v0, v1);
+          }
+        } else {  // EPI_ACCUM: C = C_old + acc
+          const int grow = m0 + row;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int col = col0 + 2 * j;
+            float o0 = 0.f, o1 = 0.f;
+            if (grow < M && col + 1 < N) {
+              float2 o = unpack_bf16(*reinterpret_cast<const uint32_t*>(
+                  epi.c_old + (size_t)grow * epi.ldc + col));
+              o0 = o.x; o1 = o.y;
+            } else if (grow < M && col < N) {
+              o0 = __bfloat162float(epi.c_old[(size_t)grow * epi.ldc + col]);
+            }
+            float v0 = __uint_as_float(j < 16 ? r0[2 * j] : r1[2 * (j - 16)]) + o0;
+            float v1 = __uint_as_float(j < 16 ? r0[2 * j + 1] : r1[2 * (j - 16) + 1]) + o1;
+            packed[j] = pack_bf16(v0, v1);
+          }
+        }
+        // staging buffer reuse: the TMA store issued two chunks ago must have finished reading
+        uint8_t* sc = smem_c + (chunk_ctr & 1) * kEpiStageBytes;
+        if (epi_leader) tma_store_wait_read<kNumEpiStages - 1>();
+        named_bar_sync(1, 128);
+        const uint32_t row_addr = smem_u32(sc) + row * 128;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint32_t addr = row_addr + ((j ^ (row & 7)) << 4);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(packed[4 * j]),
+                       "r"(packed[4 * j + 1]), "r"(packed[4 * j + 2]), "r"(packed[4 * j + 3])
+                       : "memory");
+        }
+        fence_proxy_async_smem();
+        named_bar_sync(1, 128);
+        if (epi_leader) {
+          if (col0 < N && m0 < M) tma_store_2d(&tmC, sc, col0, m0);
+          tma_store_commit();
+        }
+        ++chunk_ctr;
+      }
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+    if (epi_leader) tma_store_wait<0>();
+  }
+
+  // ---- teardown ----
+  tc_fence_before();
+  if constexpr (kCta == 2) cluster_sync_all(); else __syncthreads();
+  if (warp == 2) tmem_dealloc<kCta>(tmem_base, Cfg::kTmemCols);
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+static char g_err[1024] = "";
+void set_last_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+const char* last_error() { return g_err; }
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+            cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+int make_tmap_2d_bf16(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols,
+                      uint64_t row_stride_elems, uint32_t box_rows, uint32_t box_cols) {
+  EncodeTiledFn enc = get_encode();
+  B2_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
+  B2_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "TMA base %p not 16B aligned", ptr);
+  B2_REQUIRE((row_stride_elems * 2) % 16 == 0, "TMA row stride %llu elems not 16B multiple",
+             (unsigned long long)row_stride_elems);
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {row_stride_elems * 2};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides,
+                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  B2_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(2d) failed: %d (rows=%llu cols=%llu ld=%llu)",
+             (int)r, (unsigned long long)rows, (unsigned long long)cols,
+             (unsigned long long)row_stride_elems);
+  return 0;
+}
+
+int make_tmap_mn_bf16(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols,
+                      uint64_t row_stride_elems, uint32_t box_rows, uint32_t box_chunks) {
+  EncodeTiledFn enc = get_encode();
+  B2_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
+  B2_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "TMA base %p not 16B aligned", ptr);
+  B2_REQUIRE((row_stride_elems * 2) % 16 == 0, "TMA row stride not 16B multiple");
+  B2_REQUIRE(cols % 64 == 0, "MN-major operand needs its contiguous extent (%llu) %% 64 == 0",
+             (unsigned long long)cols);
+  cuuint64_t dims[3] = {64, rows, cols / 64};
+  cuuint64_t strides[2] = {row_stride_elems * 2, 128};
+  cuuint32_t box[3] = {64, box_rows, box_chunks};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides,
+                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  B2_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(3d) failed: %d", (int)r);
+  return 0;
+}
+
+int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+  }
+  return n;
+}
+
+template <int kCta, bool kAK, bool kBK, int kEpi, int BN>
+static int launch_gemm(void* C, const void* A, const void* B, int M, int N, int K, int lda, int ldb,
+                       int ldc, const EpiArgs& epi, int max_ctas, cudaStream_t stream) {
+  using Cfg = GemmCfg<kCta, BN>;
+  CUtensorMap tmA, tmB, tmC;
+  int rc;
+  if constexpr (kAK) rc = make_tmap_2d_bf16(&tmA, A, M, K, lda, BM, BK);
+  else rc = make_tmap_mn_bf16(&tmA, A, K, M, lda, BK, BM / 64);
+  if (rc) return rc;
+  if constexpr (kBK) rc = make_tmap_2d_bf16(&tmB, B, N, K, ldb, BN / kCta, BK);
+  else rc = make_tmap_mn_bf16(&tmB, B, K, N, ldb, BK, BN / kCta / 64);
+  if (rc) return rc;
+  rc = make_tmap_2d_bf16(&tmC, C, M, N, ldc, BM, kEpiChunk);
+  if (rc) return rc;
+
+  auto kern = gemm_bf16_kernel<kCta, kAK, kBK, kEpi, BN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B2_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  const int tile_m = BM * kCta;
+  const int num_tiles = ((M + tile_m - 1) / tile_m) * ((N + BN - 1) / BN);
+  int sms = sm_count();
+  if (max_ctas > 0 && max_ctas < sms) sms = max_ctas;
+  int workers = sms / kCta;
+  if (workers > num_tiles) workers = num_tiles;
+  if (workers < 1) workers = 1;
+
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(workers * kCta);
+  cfg.blockDim = dim3(256);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attrs[1];
+  attrs[0].id = cudaLaunchAttributeClusterDimension;
+  attrs[0].val.clusterDim.x = kCta;
+  attrs[0].val.clusterDim.y = 1;
+  attrs[0].val.clusterDim.z = 1;
+  cfg.attrs = attrs;
+  cfg.numAttrs = 1;
+  B2_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, M, N, K, epi));
+  return 0;
+}
+
+template <int kCta, int BN>
+static int dispatch_layout(void* C, const void* A, const void* B, int M, int N, int K, int a_mn,
+                           int b_mn, int lda, int ldb, int ldc, int epilogue, const EpiArgs& epi,
+                           int max_ctas, cudaStream_t stream) {
+#define B2_GEMM_CASE(AK, BKM, EPI)                                                                 \
+  return launch_gemm<kCta, AK, BKM, EPI, BN>(C, A, B, M, N, K, lda, ldb, ldc, epi, max_ctas, stream)
+  if (!a_mn && !b_mn) {
+    switch (epilogue) {
+      case EPI_NONE: B2_GEMM_CASE(true, true, EPI_NONE);
+      case EPI_BIAS: B2_GEMM_CASE(true, true, EPI_BIAS);
+      case EPI_BIAS_GELU: B2_GEMM_CASE(true, true, EPI_BIAS_GELU);
+      case EPI_ACCUM: B2_GEMM_CASE(true, true, EPI_ACCUM);
+    }
+  } else if (!a_mn && b_mn) {
+    switch (epilogue) {
+      case EPI_NONE: B2_GEMM_CASE(true, false, EPI_NONE);
+      case EPI_ACCUM: B2_GEMM_CASE(true, false, EPI_ACCUM);
+    }
+  } else if (a_mn && b_mn) {
+    switch (epilogue) {
+      case EPI_NONE: B2_GEMM_CASE(false, false, EPI_NONE);
+      case EPI_ACCUM: B2_GEMM_CASE(false, false, EPI_ACCUM);
+    }
+  } else {
+    switch (epilogue) {
+      case EPI_NONE: B2_GEMM_CASE(false, true, EPI_NONE);
+    }
+  }
+#undef B2_GEMM_CASE
+  set_last_error("b2_gemm_bf16: unsupported layout/epilogue combination a_mn=%d b_mn=%d epi=%d",
+                 a_mn, b_mn, epilogue);
+  return -2;
+}
+
+}  // namespace b2
+
+extern "C" {
+
+const char* b2_last_error() { return b2::last_error(); }
+
+// C[M,N] (row-major, ldc) = epilogue(A * B^T) with A logically [M,K], B logically [N,K].
+//   a_mn = 0: A stored [M,K] (lda = row stride); a_mn = 1: A stored [K,M] (rows of length M).
+//   b_mn = 0: B stored [N,K];                    b_mn = 1: B stored [K,N].
+//   epilogue: 0 none, 1 +bias[N], 2 gelu_new(+bias), 3 C += (reads c_old == C, same ldc).
+//   config: 0 auto; otherwise (cta_group) | (BN << 8), e.g. 2 | (256 << 8).
+//   max_ctas: cap on the persistent grid (0 = all SMs) so a concurrent kernel keeps some SMs.
+int b2_gemm_bf16(void* C, const void* A, const void* B, int M, int N, int K, int a_mn, int b_mn,
+                 int lda, int ldb, int ldc, int epilogue, const void* bias, int config,
+                 int max_ctas, cudaStream_t stream) {
+  using namespace b2;
+  B2_REQUIRE(M > 0 && N > 0 && K > 0, "b2_gemm_bf16: empty problem %dx%dx%d", M, N, K);
+  EpiArgs epi;
+  epi.bias = static_cast<const __nv_bfloat16*>(bias);
+  epi.c_old = static_cast<const __nv_bfloat16*>(C);
+  epi.ldc = ldc;
+  int cta = config & 0xff, bn = (config >> 8) & 0xffff;
+  if (cta == 0) cta = 2;
+  if (bn == 0) bn = 256;
+  // MN-major operands are fetched in 64-element atoms: each CTA's slice must be atom aligned
+  if (cta == 2 && (M <= BM)) cta = 1;
+  if (cta == 1 && bn == 256)
+    return dispatch_layout<1, 256>(C, A, B, M, N, K, a_mn, b_mn, lda, ldb, ldc, epilogue, epi,
+                                   max_ctas, stream);
+  if (cta == 1 && bn == 128)
+    return dispatch_layout<1, 128>(C, A, B, M, N, K, a_mn, b_mn, lda, ldb, ldc, epilogue, epi,
+                                   max_ctas, stream);
+  if (cta == 2 && bn == 256)
+    return dispatch_layout<2, 256>(C, A, B, M, N, K, a_mn, b_mn, lda, ldb, ldc, epilogue, epi,
+                                   max_ctas, stream);
+  if (cta == 2 && bn == 128)
+    return dispatch_layout<2, 128>(C, A, B, M, N, K, a_mn, b_mn, lda, ldb, ldc, epilogue, epi,
+                                   max_ctas, stream);
+  set_last_error("b2_gemm_bf16: bad config %d", config);
+  return -2;
+}
+
+}  // extern "C"

@@ -1,0 +1,105 @@
+/* C ABI of libb200train.so: hand-written sm_100a kernels for the b200train framework.
+ *
+ * Conventions
+ *   - every function returns 0 on success; on failure it returns non-zero and b2_last_error()
+ *     describes the problem (argument validation happens before any launch).
+ *   - all tensors are device pointers to bf16 unless the type says otherwise; `stream` is the CUDA
+ *     stream to launch on (a cudaStream_t passed as an opaque pointer).
+ *   - no function allocates device memory unless its comment says so; scratch buffers are passed in.
+ *   - parity citations point into the reference tree (rimelabs/lambda-labs_distributed-training-guide),
+ *     which reaches the equivalent library kernels through PyTorch / HF transformers / flash-attn.
+ */
+#ifndef B200TRAIN_H_
+#define B200TRAIN_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* b2_stream_t;
+
+const char* b2_last_error(void);
+
+/* ---- tcgen05 GEMM (csrc/gemm.cu) ----------------------------------------------------------
+ * C[M,N] = epilogue(A * B^T), A logically [M,K], B logically [N,K], fp32 accumulate in TMEM.
+ * a_mn / b_mn = 0: operand stored [rows, K] (K contiguous); = 1: stored [K, rows] (rows contiguous).
+ * epilogue: 0 none, 1 + bias[N], 2 gelu_new(. + bias[N]), 3 C += result.
+ * config: 0 auto, else cta_group | (BN << 8).  max_ctas: 0 = all SMs.
+ * Reference: every nn.Linear / Conv1D matmul, 01-single-gpu/train_llm.py:140,145 (cuBLAS via ATen). */
+int b2_gemm_bf16(void* C, const void* A, const void* B, int M, int N, int K, int a_mn, int b_mn,
+                 int lda, int ldb, int ldc, int epilogue, const void* bias, int config,
+                 int max_ctas, b2_stream_t stream);
+
+/* ---- flash attention forward (csrc/attention_fwd.cu) --------------------------------------
+ * Reference: attn_implementation="flash_attention_2", 05-training-llama-405b/train_llm.py:87;
+ * varlen via restarting position ids, 00-rime/packed_dataset.py:35-48. */
+int b2_attn_fwd(void* o, float* lse, const void* q, const void* k, const void* v,
+                const int* cu_seqlens, int ndocs, int max_seqlen, int T, int Hq, int Hkv, int D,
+                int q_stride, int k_stride, int v_stride, int o_stride, float softmax_scale,
+                int causal, b2_stream_t stream);
+
+/* ---- flash attention backward (csrc/attention_bwd.cu) -------------------------------------
+ * dq_accum: fp32 scratch [T, Hq*D] (zeroed by the call); delta: fp32 scratch [Hq, T]. */
+int b2_attn_bwd(void* dq, void* dk, void* dv, float* dq_accum, float* delta, const void* dout,
+                const void* q, const void* k, const void* v, const void* o, const float* lse,
+                const int* cu_seqlens, int ndocs, int max_seqlen, int T, int Hq, int Hkv, int D,
+                int q_stride, int k_stride, int v_stride, int o_stride, int do_stride,
+                int dq_stride, int dk_stride, int dv_stride, float softmax_scale, int causal,
+                b2_stream_t stream);
+
+/* ---- norms (csrc/elementwise.cu) -----------------------------------------------------------
+ * RMSNorm with the HF LlamaRMSNorm rounding; `res` (optional) is added first and the sum is
+ * written to h_out. Backward needs an fp32 scratch `partial` of
+ * b2_rmsnorm_bwd_partial_rows(T) * H floats (LayerNorm: * 2 * H).
+ * Reference: HF LlamaRMSNorm / GPT-2 LayerNorm eager kernels behind 01-single-gpu/train_llm.py:140. */
+int b2_rmsnorm_bwd_partial_rows(int T);
+int b2_rmsnorm_fwd(void* y, float* rstd, void* h_out, const void* x, const void* res,
+                   const void* w, int T, int H, float eps, b2_stream_t stream);
+int b2_rmsnorm_bwd(void* dx, void* dw, float* partial, const void* dy, const void* h,
+                   const void* w, const float* rstd, const void* dres, int T, int H,
+                   int accumulate_dw, b2_stream_t stream);
+int b2_layernorm_fwd(void* y, float* mean, float* rstd, void* h_out, const void* x,
+                     const void* res, const void* w, const void* b, int T, int H, float eps,
+                     b2_stream_t stream);
+int b2_layernorm_bwd(void* dx, void* dw, void* db, float* partial, const void* dy, const void* h,
+                     const void* w, const float* mean, const float* rstd, const void* dres, int T,
+                     int H, int accumulate, b2_stream_t stream);
+
+/* ---- activations / rope / embedding ---------------------------------------------------------
+ * Reference: HF LlamaMLP act_fn(gate)*up, apply_rotary_pos_emb, nn.Embedding (eager ATen). */
+int b2_swiglu_fwd(void* out, const void* gu, int T, int I, b2_stream_t stream);
+int b2_swiglu_bwd(void* dgu, const void* dout, const void* gu, int T, int I, b2_stream_t stream);
+int b2_gelu_fwd(void* out, const void* x, size_t n, b2_stream_t stream);
+int b2_gelu_bwd(void* dx, const void* x, const void* dout, size_t n, b2_stream_t stream);
+int b2_rope(void* x, const void* cosT, const void* sinT, const int* pos, int T, int nheads, int D,
+            int row_stride, int seq_len, int backward, b2_stream_t stream);
+int b2_embedding_fwd(void* out, const void* table, const long long* ids, int T, int H,
+                     b2_stream_t stream);
+int b2_embedding_bwd(void* dtable, const void* dout, const long long* ids, int T, int H,
+                     b2_stream_t stream);
+
+/* ---- cross entropy ---------------------------------------------------------------------------
+ * Reference: HF ForCausalLMLoss (fp32 log-softmax + nll), loss parallel 06-tensor-parallel/train_llm.py:239. */
+int b2_ce_fwd(float* lse, float* loss, const void* logits, const long long* labels, int T, int V,
+              int ld, int ignore_index, b2_stream_t stream);
+int b2_ce_shard_stats(float* row_max, float* row_sum, float* row_tgt, const void* logits,
+                      const long long* labels, int T, int V, int ld, int ignore_index,
+                      int vocab_start, b2_stream_t stream);
+int b2_ce_bwd(void* dlogits, const void* logits, const float* lse, const long long* labels, int T,
+              int V, int ld, int ignore_index, int vocab_start, float scale, const float* scale_dev,
+              b2_stream_t stream);
+
+/* ---- optimizer --------------------------------------------------------------------------------
+ * Reference: torch.optim.AdamW(fused=True) on bf16 params, 01-single-gpu/train_llm.py:65. */
+int b2_adamw(void* p, void* m, void* v, const void* g, size_t n, float lr, float beta1,
+             float beta2, float eps, float wd, int step, float grad_scale, int max_blocks,
+             b2_stream_t stream);
+int b2_add(void* out, const void* a, const void* b, size_t n, b2_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200TRAIN_H_ */

@@ -1,0 +1,121 @@
+"""ctypes binding of ``libb200train.so`` (C ABI declared in ``include/b200train.h``).
+
+The library is loaded lazily, on the first call that needs a kernel. On a machine with a GPU a missing
+or unloadable library is a hard error (no silent fallback to PyTorch ops); on a CPU-only machine the
+ops modules never reach this file because they dispatch CPU tensors to their PyTorch reference math.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import c_char_p, c_float, c_int, c_size_t, c_void_p
+from pathlib import Path
+
+import torch
+
+_LIB = None
+_LAUNCHES = 0
+# kernels launched per library call (for the bench's launch count)
+_LAUNCH_MULT = {"b2_rmsnorm_bwd": 2, "b2_layernorm_bwd": 2, "b2_attn_bwd": 3, "b2_rmsnorm_bwd_partial_rows": 0}
+_LIB_PATH = Path(__file__).resolve().parent / "_lib" / "libb200train.so"
+
+
+class KernelError(RuntimeError):
+    pass
+
+
+def lib_path() -> Path:
+    return _LIB_PATH
+
+
+def _declare(lib):
+    P, I, F, Z = c_void_p, c_int, c_float, c_size_t
+    sig = {
+        "b2_gemm_bf16": [P, P, P, I, I, I, I, I, I, I, I, I, P, I, I, P],
+        "b2_attn_fwd": [P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, F, I, P],
+        "b2_attn_bwd": [P, P, P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, I, I, I, I, F, I, P],
+        "b2_rmsnorm_bwd_partial_rows": [I],
+        "b2_rmsnorm_fwd": [P, P, P, P, P, P, I, I, F, P],
+        "b2_rmsnorm_bwd": [P, P, P, P, P, P, P, P, I, I, I, P],
+        "b2_layernorm_fwd": [P, P, P, P, P, P, P, P, I, I, F, P],
+        "b2_layernorm_bwd": [P, P, P, P, P, P, P, P, P, P, I, I, I, P],
+        "b2_swiglu_fwd": [P, P, I, I, P],
+        "b2_swiglu_bwd": [P, P, P, I, I, P],
+        "b2_gelu_fwd": [P, P, Z, P],
+        "b2_gelu_bwd": [P, P, P, Z, P],
+        "b2_rope": [P, P, P, P, I, I, I, I, I, I, P],
+        "b2_embedding_fwd": [P, P, P, I, I, P],
+        "b2_embedding_bwd": [P, P, P, I, I, P],
+        "b2_ce_fwd": [P, P, P, P, I, I, I, I, P],
+        "b2_ce_shard_stats": [P, P, P, P, P, I, I, I, I, I, P],
+        "b2_ce_bwd": [P, P, P, P, I, I, I, I, I, F, P, P],
+        "b2_adamw": [P, P, P, P, Z, F, F, F, F, F, I, F, I, P],
+        "b2_add": [P, P, P, Z, P],
+    }
+    for name, argtypes in sig.items():
+        fn = getattr(lib, name, None)
+        if fn is None:
+            continue  # optional symbol (checked at call time)
+        fn.argtypes = argtypes
+        fn.restype = c_int
+    lib.b2_last_error.restype = c_char_p
+    lib.b2_last_error.argtypes = []
+
+
+def load():
+    """Load (building first if the .so is missing and nvcc is present) and return the library."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    if not _LIB_PATH.exists():
+        if os.environ.get("B200TRAIN_NO_AUTOBUILD") == "1":
+            raise KernelError(f"{_LIB_PATH} is missing; run `python -m b200train.build`")
+        from . import build as _build
+
+        _build.build()
+    try:
+        lib = ctypes.CDLL(str(_LIB_PATH))
+    except OSError as e:  # pragma: no cover - depends on the machine
+        raise KernelError(f"cannot load {_LIB_PATH}: {e}") from e
+    _declare(lib)
+    _LIB = lib
+    return lib
+
+
+def available() -> bool:
+    """True when kernels can run here: a CUDA device is visible and the library loads."""
+    if not torch.cuda.is_available():
+        return False
+    load()
+    return True
+
+
+def stream_ptr(device=None) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def ptr(t):
+    """Device pointer of a tensor (or None)."""
+    if t is None:
+        return None
+    return t.data_ptr()
+
+
+def call(name: str, *args):
+    """Invoke ``name`` from the library; raise KernelError with the library's message on failure."""
+    lib = load()
+    fn = getattr(lib, name, None)
+    if fn is None:
+        raise KernelError(f"{name} is not exported by {_LIB_PATH}")
+    global _LAUNCHES
+    _LAUNCHES += _LAUNCH_MULT.get(name, 1)
+    rc = fn(*args)
+    if rc != 0:
+        msg = lib.b2_last_error()
+        raise KernelError(f"{name} failed (rc={rc}): {msg.decode() if msg else 'unknown error'}")
+    return rc
+
+
+def launch_count() -> int:
+    """Number of b200train kernels launched so far by this process."""
+    return _LAUNCHES

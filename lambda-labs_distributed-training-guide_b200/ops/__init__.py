@@ -1,0 +1,15 @@
+"""Differentiable ops backed by the sm_100a kernels in ``csrc/`` (PyTorch reference math on CPU)."""
+from .activation import gelu_new, swiglu
+from .attention import attention
+from .cross_entropy import (IGNORE, linear_cross_entropy, shift_labels, vocab_parallel_cross_entropy)
+from .embedding import embedding
+from .linear import gemm, linear
+from .norm import layernorm, rmsnorm
+from .optim import adamw_step
+from .rope import rope_qk, rope_tables
+
+__all__ = [
+    "gelu_new", "swiglu", "attention", "IGNORE", "linear_cross_entropy", "shift_labels",
+    "vocab_parallel_cross_entropy", "embedding", "gemm", "linear", "layernorm", "rmsnorm", "adamw_step",
+    "rope_qk", "rope_tables",
+]

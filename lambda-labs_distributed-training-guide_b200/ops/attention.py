@@ -1,0 +1,116 @@
+"""Causal flash attention over a fused QKV activation (csrc/attention_fwd.cu, attention_bwd.cu).
+
+``attention(qkv, n_q, n_kv, head_dim, cu_seqlens, max_seqlen)`` takes the post-RoPE projection
+output [T, (Hq + 2 Hkv) * D] and returns [T, Hq * D]; q/k/v are strided views of that buffer and the
+backward writes dq/dk/dv into one fused gradient buffer, so the QKV GEMM's dgrad consumes it as is.
+Packed batches are described by ``cu_seqlens`` (int32 [ndocs+1]).
+
+Reference: HF attention dispatch to ``flash_attn`` / SDPA (``05-training-llama-405b/train_llm.py:87``,
+``01-single-gpu/train_llm.py:140``); varlen via ``position_ids`` restarts (``00-rime/packed_dataset.py:35-48``).
+"""
+from __future__ import annotations
+
+import math
+import os
+
+import torch
+
+from .. import _C
+from .dispatch import check_bf16, stream, use_kernels
+
+# "kernel": tcgen05 backward (csrc/attention_bwd.cu); "flash_attn": library backward (debug only)
+BWD_IMPL = os.environ.get("B200TRAIN_ATTN_BWD", "kernel")
+
+
+def _split(qkv, n_q, n_kv, D):
+    q = qkv[:, : n_q * D]
+    k = qkv[:, n_q * D: (n_q + n_kv) * D]
+    v = qkv[:, (n_q + n_kv) * D:]
+    return q, k, v
+
+
+def attn_fwd_raw(q, k, v, cu_seqlens, max_seqlen, n_q, n_kv, D, scale, causal=True):
+    """Forward on strided [T, heads*D] views; returns (o [T, Hq*D], lse [Hq, T])."""
+    T = q.shape[0]
+    o = torch.empty((T, n_q * D), dtype=torch.bfloat16, device=q.device)
+    lse = torch.empty((n_q, T), dtype=torch.float32, device=q.device)
+    _C.call("b2_attn_fwd", o.data_ptr(), lse.data_ptr(), q.data_ptr(), k.data_ptr(), v.data_ptr(),
+            cu_seqlens.data_ptr(), cu_seqlens.numel() - 1, max_seqlen, T, n_q, n_kv, D, q.stride(0),
+            k.stride(0), v.stride(0), o.stride(0), scale, int(causal), stream(q))
+    return o, lse
+
+
+def attn_bwd_raw(do, q, k, v, o, lse, dq, dk, dv, cu_seqlens, max_seqlen, n_q, n_kv, D, scale, causal=True):
+    T = q.shape[0]
+    if BWD_IMPL == "flash_attn":
+        from flash_attn.flash_attn_interface import _flash_attn_varlen_backward
+
+        _flash_attn_varlen_backward(
+            do.view(T, n_q, D), q.unflatten(1, (n_q, D)), k.unflatten(1, (n_kv, D)), v.unflatten(1, (n_kv, D)),
+            o.view(T, n_q, D), lse, dq.unflatten(1, (n_q, D)), dk.unflatten(1, (n_kv, D)),
+            dv.unflatten(1, (n_kv, D)), cu_seqlens, cu_seqlens, max_seqlen, max_seqlen, 0.0, scale, causal,
+            -1, -1, 0.0, None, False, None)
+        return
+    dq_accum = torch.empty((T, n_q * D), dtype=torch.float32, device=q.device)
+    delta = torch.empty((n_q, T), dtype=torch.float32, device=q.device)
+    _C.call("b2_attn_bwd", dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), dq_accum.data_ptr(), delta.data_ptr(),
+            do.data_ptr(), q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), lse.data_ptr(),
+            cu_seqlens.data_ptr(), cu_seqlens.numel() - 1, max_seqlen, T, n_q, n_kv, D, q.stride(0), k.stride(0),
+            v.stride(0), o.stride(0), do.stride(0), dq.stride(0), dk.stride(0), dv.stride(0), scale, int(causal),
+            stream(q))
+
+
+class _Attention(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, qkv, cu_seqlens, max_seqlen, n_q, n_kv, D, scale, causal):
+        check_bf16(qkv)
+        assert qkv.dim() == 2 and qkv.is_contiguous()
+        q, k, v = _split(qkv, n_q, n_kv, D)
+        o, lse = attn_fwd_raw(q, k, v, cu_seqlens, max_seqlen, n_q, n_kv, D, scale, causal)
+        ctx.save_for_backward(qkv, o, lse, cu_seqlens)
+        ctx.args = (max_seqlen, n_q, n_kv, D, scale, causal)
+        return o
+
+    @staticmethod
+    def backward(ctx, do):
+        qkv, o, lse, cu_seqlens = ctx.saved_tensors
+        max_seqlen, n_q, n_kv, D, scale, causal = ctx.args
+        do = do.contiguous()
+        dqkv = torch.empty_like(qkv)
+        q, k, v = _split(qkv, n_q, n_kv, D)
+        dq, dk, dv = _split(dqkv, n_q, n_kv, D)
+        attn_bwd_raw(do, q, k, v, o, lse, dq, dk, dv, cu_seqlens, max_seqlen, n_q, n_kv, D, scale, causal)
+        return dqkv, None, None, None, None, None, None, None
+
+
+def attention_ref(qkv, cu_seqlens, max_seqlen, n_q, n_kv, D, scale=None, causal=True):
+    """fp32 PyTorch reference over each document separately."""
+    scale = scale if scale is not None else 1.0 / math.sqrt(D)
+    T = qkv.shape[0]
+    q, k, v = _split(qkv, n_q, n_kv, D)
+    q = q.reshape(T, n_q, D)
+    k = k.reshape(T, n_kv, D)
+    v = v.reshape(T, n_kv, D)
+    outs = []
+    bounds = cu_seqlens.tolist()
+    g = n_q // n_kv
+    for s, e in zip(bounds[:-1], bounds[1:]):
+        qi = q[s:e].transpose(0, 1).float()
+        ki = k[s:e].transpose(0, 1).repeat_interleave(g, dim=0).float()
+        vi = v[s:e].transpose(0, 1).repeat_interleave(g, dim=0).float()
+        att = (qi @ ki.transpose(-1, -2)) * scale
+        if causal:
+            L = e - s
+            mask = torch.ones(L, L, dtype=torch.bool, device=qkv.device).tril()
+            att = att.masked_fill(~mask, float("-inf"))
+        oi = torch.softmax(att, dim=-1) @ vi
+        outs.append(oi.transpose(0, 1).reshape(e - s, n_q * D))
+    return torch.cat(outs, 0).to(qkv.dtype)
+
+
+def attention(qkv: torch.Tensor, cu_seqlens: torch.Tensor, max_seqlen: int, n_q: int, n_kv: int,
+              head_dim: int, scale: float | None = None, causal: bool = True) -> torch.Tensor:
+    scale = scale if scale is not None else 1.0 / math.sqrt(head_dim)
+    if use_kernels(qkv):
+        return _Attention.apply(qkv, cu_seqlens, max_seqlen, n_q, n_kv, head_dim, scale, causal)
+    return attention_ref(qkv, cu_seqlens, max_seqlen, n_q, n_kv, head_dim, scale, causal)

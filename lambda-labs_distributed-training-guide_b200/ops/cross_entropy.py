@@ -1,0 +1,156 @@
+"""LM-head projection + shifted-label cross entropy without fp32 logits.
+
+The head GEMM writes bf16 logits (padded to a multiple of 64 columns so the same buffer can be the
+MN-major operand of the head's wgrad GEMM); one kernel computes the per-row log-sum-exp / loss and
+one kernel turns the logits into dlogits in place. The reference materialises fp32 logits
+(``logits.float()`` in HF ``ForCausalLMLoss``, 2.1 GB at T=4096, V=128256) and runs ATen
+log_softmax + nll_loss (``01-single-gpu/train_llm.py:140`` -> ``outputs.loss``).
+
+``vocab_parallel_cross_entropy`` is the tensor-parallel variant (reference:
+``06-tensor-parallel/train_llm.py:117-127,239-243`` ``loss_parallel``): each rank holds a vocabulary
+shard of the logits; the per-row max / sum-exp / target-logit statistics are exchanged over the tp
+group instead of gathering logits.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+from .. import _C
+from .dispatch import check_bf16, stream, use_kernels
+from .linear import gemm, EPI_ACCUM, EPI_NONE, _direct_grad
+
+IGNORE = -100
+
+
+def shift_labels(labels: torch.Tensor) -> torch.Tensor:
+    """HF convention: position t predicts token t+1; the last position of each row is ignored."""
+    shifted = torch.full_like(labels, IGNORE)
+    shifted[..., :-1] = labels[..., 1:]
+    return shifted
+
+
+class _LinearCrossEntropy(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, labels):
+        """x [T,H] bf16, w [V,H] bf16, labels [T] int64 already shifted. Returns mean loss (fp32)."""
+        check_bf16(x, w)
+        T, H = x.shape
+        V = w.shape[0]
+        ld = (V + 63) // 64 * 64
+        logits = torch.empty((T, ld), dtype=torch.bfloat16, device=x.device)
+        gemm(x, w, out=logits[:, :V])
+        lse = torch.empty(T, dtype=torch.float32, device=x.device)
+        loss_rows = torch.empty(T, dtype=torch.float32, device=x.device)
+        labels = labels.contiguous()
+        _C.call("b2_ce_fwd", lse.data_ptr(), loss_rows.data_ptr(), logits.data_ptr(), labels.data_ptr(),
+                T, V, ld, IGNORE, stream(x))
+        n_valid = (labels != IGNORE).sum().clamp_(min=1)
+        loss = loss_rows.sum() / n_valid
+        ctx.save_for_backward(x, w, labels, logits, lse, n_valid)
+        return loss
+
+    @staticmethod
+    def backward(ctx, dloss):
+        x, w, labels, logits, lse, n_valid = ctx.saved_tensors
+        T, H = x.shape
+        V = w.shape[0]
+        ld = logits.shape[1]
+        # dlogits in place; the scale dloss / n_valid stays on the device (no host sync)
+        scale_t = (dloss.float() / n_valid.float()).reshape(1).contiguous()
+        _C.call("b2_ce_bwd", logits.data_ptr(), logits.data_ptr(), lse.data_ptr(), labels.data_ptr(), T, V,
+                ld, IGNORE, 0, 1.0, scale_t.data_ptr(), stream(x))
+        dl = logits[:, :V]
+        dx = gemm(dl, w, b_mn=True) if ctx.needs_input_grad[0] else None
+        dw = None
+        if ctx.needs_input_grad[1]:
+            # dW[V,H] = dlogits^T x ; the padded columns of dlogits are zero
+            a = logits
+            if _direct_grad(w):
+                acc = getattr(w, "_b2_grad_ready", False)
+                out = w.grad
+                if ld != V:
+                    tmp = gemm(a, x, a_mn=True, b_mn=True)
+                    if acc:
+                        out.add_(tmp[:V])
+                    else:
+                        out.copy_(tmp[:V])
+                else:
+                    gemm(a, x, a_mn=True, b_mn=True, out=out, epilogue=EPI_ACCUM if acc else EPI_NONE)
+                w._b2_grad_ready = True
+            else:
+                dw = gemm(a, x, a_mn=True, b_mn=True)[:V]
+        return dx, dw, None
+
+
+def linear_cross_entropy_ref(x, w, labels):
+    logits = torch.nn.functional.linear(x, w).float()
+    return torch.nn.functional.cross_entropy(logits, labels, ignore_index=IGNORE)
+
+
+def linear_cross_entropy(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+    """mean CE of ``x @ w.T`` against already-shifted ``labels`` (ignore_index=-100)."""
+    x2 = x.reshape(-1, x.shape[-1])
+    l1 = labels.reshape(-1)
+    if use_kernels(x2):
+        return _LinearCrossEntropy.apply(x2.contiguous(), w, l1)
+    return linear_cross_entropy_ref(x2, w, l1)
+
+
+# ------------------------------------------------------------------------------------------------
+# vocabulary-parallel variant
+# ------------------------------------------------------------------------------------------------
+class _VocabParallelCE(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, labels, vocab_start, group):
+        """logits [T, Vlocal] (this rank's vocabulary shard), labels [T] global ids (shifted)."""
+        T, Vl = logits.shape
+        labels = labels.contiguous()
+        if use_kernels(logits):
+            check_bf16(logits)
+            assert logits.is_contiguous() and Vl % 8 == 0
+            stats = torch.empty((3, T), dtype=torch.float32, device=logits.device)
+            _C.call("b2_ce_shard_stats", stats[0].data_ptr(), stats[1].data_ptr(), stats[2].data_ptr(),
+                    logits.data_ptr(), labels.data_ptr(), T, Vl, Vl, IGNORE, vocab_start, stream(logits))
+            lmax, lsum, ltgt = stats[0], stats[1], stats[2]
+        else:
+            lf = logits.float()
+            lmax = lf.max(dim=1).values
+            lsum = torch.exp(lf - lmax[:, None]).sum(1)
+            local = labels - vocab_start
+            mine = (labels != IGNORE) & (local >= 0) & (local < Vl)
+            ltgt = torch.where(mine, lf.gather(1, local.clamp(0, Vl - 1)[:, None])[:, 0], torch.zeros_like(lmax))
+        gmax = lmax.clone()
+        dist.all_reduce(gmax, op=dist.ReduceOp.MAX, group=group)
+        packed = torch.stack((lsum * torch.exp(lmax - gmax), ltgt))
+        dist.all_reduce(packed, op=dist.ReduceOp.SUM, group=group)
+        lse = gmax + torch.log(packed[0])
+        valid = labels != IGNORE
+        n_valid = valid.sum().clamp_(min=1)
+        loss = torch.where(valid, lse - packed[1], torch.zeros_like(lse)).sum() / n_valid
+        ctx.save_for_backward(logits, labels, lse, n_valid)
+        ctx.vocab_start = vocab_start
+        return loss
+
+    @staticmethod
+    def backward(ctx, dloss):
+        logits, labels, lse, n_valid = ctx.saved_tensors
+        T, Vl = logits.shape
+        scale_t = (dloss.float() / n_valid.float()).reshape(1).contiguous()
+        if use_kernels(logits):
+            dl = torch.empty_like(logits)
+            _C.call("b2_ce_bwd", dl.data_ptr(), logits.data_ptr(), lse.data_ptr(), labels.data_ptr(), T, Vl,
+                    Vl, IGNORE, ctx.vocab_start, 1.0, scale_t.data_ptr(), stream(logits))
+        else:
+            p = torch.exp(logits.float() - lse[:, None])
+            local = labels - ctx.vocab_start
+            mine = (labels != IGNORE) & (local >= 0) & (local < Vl)
+            p[mine, local[mine]] -= 1.0
+            p[labels == IGNORE] = 0
+            dl = (p * scale_t).to(logits.dtype)
+        return dl, None, None, None
+
+
+def vocab_parallel_cross_entropy(logits, labels, vocab_start: int, group=None):
+    """Mean CE over vocabulary-sharded ``logits`` [T, V/tp]; ``labels`` are global, already shifted."""
+    return _VocabParallelCE.apply(logits, labels.reshape(-1), vocab_start, group)

@@ -1,0 +1,35 @@
+"""Kernel dispatch policy.
+
+CUDA tensors always go to the hand-written sm_100a kernels in ``libb200train.so``; if the library
+cannot be loaded on a GPU machine the call raises (no silent PyTorch fallback). CPU tensors (unit
+tests, gloo multi-process tests, the chapter-01 CPU plumbing config) run the PyTorch reference math
+that the kernels are validated against.
+"""
+from __future__ import annotations
+
+import os
+
+import torch
+
+from .. import _C
+
+_FORCE_REFERENCE = os.environ.get("B200TRAIN_FORCE_REFERENCE", "0") == "1"
+
+
+def use_kernels(t: torch.Tensor) -> bool:
+    if not t.is_cuda:
+        return False
+    if _FORCE_REFERENCE:
+        return False
+    _C.load()  # raises KernelError when the extension is missing on a GPU box
+    return True
+
+
+def stream(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def check_bf16(*tensors):
+    for t in tensors:
+        if t is not None and t.dtype != torch.bfloat16:
+            raise TypeError(f"b200train kernels take bf16 tensors, got {t.dtype}")

@@ -1,0 +1,104 @@
+"""Linear layers on the tcgen05 GEMM (csrc/gemm.cu).
+
+forward  y  = x W^T (+ bias)          K-major x K-major
+dgrad    dx = dy W                    K-major x MN-major (no transposed copy of W)
+wgrad    dW = dy^T x                  MN-major x MN-major, written straight into the parameter's
+                                      flat gradient buffer when the parameter owns one
+
+Reference: every ``nn.Linear`` (Llama) / ``Conv1D`` (GPT-2) reached from
+``01-single-gpu/train_llm.py:140,145`` through HF modeling code and cuBLAS.
+"""
+from __future__ import annotations
+
+import torch
+
+from .. import _C
+from .dispatch import check_bf16, stream, use_kernels
+
+EPI_NONE, EPI_BIAS, EPI_BIAS_GELU, EPI_ACCUM = 0, 1, 2, 3
+
+# 0 = library default; (cta_group | BN << 8) to pin a tile configuration (used by benches)
+GEMM_CONFIG = 0
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn=False, b_mn=False, out=None, epilogue=EPI_NONE,
+         bias=None, config=None, max_ctas=0) -> torch.Tensor:
+    """C[M,N] = epilogue(A B^T). ``a``: [M,K] (or [K,M] when a_mn), ``b``: [N,K] (or [K,N] when b_mn).
+
+    Operands are 2-D row-major views (unit stride in the last dim, arbitrary row stride)."""
+    check_bf16(a, b, out, bias)
+    assert a.dim() == 2 and b.dim() == 2 and a.stride(1) == 1 and b.stride(1) == 1
+    M, K = (a.shape[1], a.shape[0]) if a_mn else (a.shape[0], a.shape[1])
+    N, Kb = (b.shape[1], b.shape[0]) if b_mn else (b.shape[0], b.shape[1])
+    assert K == Kb, f"gemm: inner dims differ ({K} vs {Kb})"
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.bfloat16, device=a.device)
+    assert out.shape == (M, N) and out.stride(1) == 1
+    _C.call("b2_gemm_bf16", out.data_ptr(), a.data_ptr(), b.data_ptr(), M, N, K, int(a_mn), int(b_mn),
+            a.stride(0), b.stride(0), out.stride(0), epilogue, _C.ptr(bias),
+            GEMM_CONFIG if config is None else config, max_ctas, stream(a))
+    return out
+
+
+def _direct_grad(w) -> bool:
+    return getattr(w, "_b2_direct_grad", False) and w.grad is not None
+
+
+class _Linear(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, bias, w_is_kn):
+        # w_is_kn: weight stored [in, out] (GPT-2 Conv1D) instead of [out, in]
+        ctx.w_is_kn = w_is_kn
+        x2 = x.reshape(-1, x.shape[-1])
+        ctx.save_for_backward(x2, w, bias)
+        ctx.x_shape = x.shape
+        n_out = w.shape[1] if w_is_kn else w.shape[0]
+        y = gemm(x2, w, b_mn=w_is_kn, epilogue=EPI_BIAS if bias is not None else EPI_NONE, bias=bias)
+        return y.view(*x.shape[:-1], n_out)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w, bias = ctx.saved_tensors
+        dy2 = dy.reshape(-1, dy.shape[-1])
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            # dx[M, in] = dy[M, out] * W ; W as the "B" operand is [in, out]-logical
+            dx = gemm(dy2, w, b_mn=not ctx.w_is_kn).view(ctx.x_shape)
+        if ctx.needs_input_grad[1]:
+            if ctx.w_is_kn:   # dW[in, out] = x^T dy
+                a, b = x2, dy2
+            else:             # dW[out, in] = dy^T x
+                a, b = dy2, x2
+            if _direct_grad(w):
+                acc = getattr(w, "_b2_grad_ready", False)
+                gemm(a, b, a_mn=True, b_mn=True, out=w.grad, epilogue=EPI_ACCUM if acc else EPI_NONE)
+                w._b2_grad_ready = True
+            else:
+                dw = gemm(a, b, a_mn=True, b_mn=True)
+        if bias is not None and ctx.needs_input_grad[2]:
+            db_new = dy2.sum(0, dtype=torch.float32).to(torch.bfloat16)
+            if _direct_grad(bias):
+                if getattr(bias, "_b2_grad_ready", False):
+                    bias.grad.add_(db_new)
+                else:
+                    bias.grad.copy_(db_new)
+                bias._b2_grad_ready = True
+            else:
+                db = db_new
+        return dx, dw, db, None
+
+
+def linear_ref(x, w, bias=None, w_is_kn=False):
+    if w_is_kn:
+        y = x @ w
+        return y + bias if bias is not None else y
+    return torch.nn.functional.linear(x, w, bias)
+
+
+def linear(x: torch.Tensor, w: torch.Tensor, bias=None, w_is_kn: bool = False) -> torch.Tensor:
+    """y = x W^T + b for ``w`` [out, in]; with ``w_is_kn`` the weight is [in, out] (Conv1D layout)."""
+    if use_kernels(x):
+        return _Linear.apply(x, w, bias, w_is_kn)
+    return linear_ref(x, w, bias, w_is_kn)

@@ -1,0 +1,457 @@
+"""Fully sharded data parallel (ZeRO-3) over flat per-unit shards.
+
+Capabilities of the reference's FSDP chapters:
+  * FULL_SHARD of parameters, gradients and optimizer state, one flat shard per unit
+    (``04-fully-sharded-data-parallel/train_llm.py:84-95``); units = embedding, each decoder layer,
+    final norm + head (the transformer wrap policy of ``05-training-llama-405b/train_llm.py:101-107``;
+    ``--numel-to-wrap`` merges small units the way ``size_based_auto_wrap_policy`` does),
+  * construction without materialising the full model: every unit is initialised into a transient
+    buffer and only the local shard is kept (meta-device init + ``sync_module_states``:
+    ``04-.../train_llm.py:76-79,90``),
+  * all-gather before forward / backward of a unit with the next unit prefetched on a comm stream,
+    reduce-scatter (mean) of the unit's gradients right after its backward,
+  * ``cpu_offload``: parameter shards, gradient shards and optimizer state live in pinned host memory;
+    H2D/D2H copies run on a side stream and AdamW runs on the CPU shard
+    (``CPUOffload(offload_params=True)``: ``04-.../train_llm.py:94``, ``05-.../README.md:147-169``),
+  * activation checkpointing per decoder layer (``05-.../train_llm.py:124-126``),
+  * ``no_sync`` gradient accumulation (``related-topics/gradient-accumulation/README.md:28-38``).
+
+With ``fuse_optimizer=True`` the sharded AdamW update of a unit is launched as soon as its reduced
+gradient shard exists, i.e. inside backward, overlapping the remaining backward compute.
+"""
+from __future__ import annotations
+
+import contextlib
+from typing import List, Optional
+
+import torch
+
+from ..models import build_model
+from ..utils.flat import FlatUnit
+from ..utils.schedule import make_lr_scheduler
+from .base import Strategy
+from .comm import Comm, make_comm
+from .hooks import run_unit
+from .optimizer import FlatAdamW
+
+
+class _BufferPool:
+    """A few full-size buffers with a fixed unit -> slot mapping (unit ``i`` always lands at the same
+    address, so tensors autograd saved in forward stay valid when the unit is re-gathered in backward).
+    Each slot remembers the CUDA event after which it may be overwritten."""
+
+    def __init__(self, n: int, numel: int, dtype, device, dedicated_first: bool = False):
+        self.bufs = [torch.empty(numel, dtype=dtype, device=device) for _ in range(n)]
+        self.events = [None] * n
+        self.owner = [None] * n
+        self.n = n
+        self.dedicated_first = dedicated_first  # slot 0 is reserved for unit 0 (tied embedding)
+
+    def slot_of(self, unit: int) -> int:
+        if self.dedicated_first:
+            return 0 if unit == 0 else 1 + (unit - 1) % (self.n - 1)
+        return unit % self.n
+
+    def acquire(self, unit: int):
+        i = self.slot_of(unit)
+        if self.owner[i] is not None:
+            raise RuntimeError(f"FSDP buffer slot {i} still owned by unit {self.owner[i]} (wanted by {unit})")
+        self.owner[i] = unit
+        return i, self.bufs[i], self.events[i]
+
+    def release(self, i: int, event=None):
+        self.events[i] = event
+        self.owner[i] = None
+
+
+class FSDP(Strategy):
+    name = "fsdp"
+
+    def __init__(self, cfg, device, lr=3e-5, seed=0, dtype=torch.bfloat16, group=None,
+                 comm: Optional[Comm] = None, cpu_offload: bool = False, activation_checkpointing: bool = False,
+                 reshard_after_forward: bool = True, fuse_optimizer: bool = False, numel_to_wrap: int = 0,
+                 prefer_peer: bool = True):
+        super().__init__(cfg, device, lr, seed, dtype)
+        self.comm = comm if comm is not None else make_comm(group, prefer_peer, self.device)
+        self.W, self.R = self.comm.world, self.comm.rank
+        self.cpu_offload = cpu_offload
+        self.act_ckpt = activation_checkpointing
+        self.fuse_optimizer = fuse_optimizer and not cpu_offload
+        self.is_cuda = self.device.type == "cuda"
+        self.numel_to_wrap = numel_to_wrap
+        self.sync_grads = True
+        # resident mode: one process, nothing offloaded -> parameters and gradients stay in their flat
+        # buffers and the gather / scatter machinery is bypassed
+        self.resident = self.W == 1 and not cpu_offload
+        self.reshard = reshard_after_forward and not self.resident
+        tied = cfg.tie_word_embeddings
+
+        # ---- model skeleton on the meta device; units define the flat layout -------------------
+        self.model = build_model(cfg, dtype=dtype, device="meta", init=False)
+        self.units: List[_Layout] = [_Layout(name, params, self.W) for name, params in self.model.units()]
+        n_units = len(self.units)
+        max_numel = max(u.numel for u in self.units)
+        if self.resident:
+            self.param_pool = self.grad_pool = None
+        else:
+            # transient full buffers: current + prefetched (+ the tied embedding kept resident);
+            # without resharding every unit keeps its gathered copy for the whole step
+            self.param_pool = _BufferPool((3 + int(tied)) if self.reshard else n_units, max_numel, dtype,
+                                          self.device, dedicated_first=tied and self.reshard)
+            self.grad_pool = _BufferPool(2 + int(tied), max_numel, dtype, self.device, dedicated_first=tied)
+        host = dict(device="cpu", pin_memory=self.is_cuda) if cpu_offload else dict(device=self.device)
+        self.shard_param: List[torch.Tensor] = []
+        self.shard_grad: List[torch.Tensor] = []
+        swap = {}
+        for ui, u in enumerate(self.units):
+            n = u.numel // self.W
+            full = (torch.empty(u.numel, dtype=dtype, device=self.device) if self.resident
+                    else self.param_pool.bufs[0][:u.numel])
+            swap.update(u.materialize(self.model, full, seed, ui, cfg))
+            if self.resident:
+                self.shard_param.append(full)
+                self.shard_grad.append(torch.zeros(u.numel, dtype=dtype, device=self.device))
+            else:
+                shard = torch.empty(n, dtype=dtype, **host)
+                shard.copy_(full[self.R * n:(self.R + 1) * n])
+                self.shard_param.append(shard)
+                self.shard_grad.append(torch.zeros(n, dtype=dtype, **host))
+        for mod in self.model.modules():
+            for pname, old in list(mod._parameters.items()):
+                if old is not None and id(old) in swap:
+                    mod._parameters[pname] = swap[id(old)]
+        if self.resident:
+            for u, g in zip(self.units, self.shard_grad):
+                u.assign_grads(g)
+        if self.is_cuda:
+            torch.cuda.synchronize(self.device)
+        self._gathered = {}       # unit -> (pool slot, gather-finished event, full view)
+        self._grad_slot = {}      # unit -> pool slot of its full gradient buffer
+        self._opt_events = {}     # unit -> event after a side-stream optimizer update of its shard
+        self._local_acc = {}      # unit -> unreduced gradient accumulator (no_sync)
+        self._stepped = set()     # units already updated inside this backward (fuse_optimizer)
+        self.comm_stream = torch.cuda.Stream(self.device) if self.is_cuda else None
+        self.model.unit_runner = self._runner
+        self.model.train()
+
+        self.optimizer = FlatAdamW(self.units, lr=lr, shard=(self.R, self.W),
+                                   moments_device=("cpu" if cpu_offload else self.device),
+                                   pin=self.is_cuda and cpu_offload)
+        self.lr_scheduler = make_lr_scheduler(self.optimizer, lr)
+        self.comm.barrier()
+
+    # ------------------------------------------------------------------------------------------------
+    @property
+    def rank(self):
+        return self.R
+
+    @property
+    def world_size(self):
+        return self.W
+
+    def tokens_per_step(self, batch_size, seq_len):
+        return self.W * batch_size * seq_len
+
+    def barrier(self):
+        self.comm.barrier()
+
+    # ---- stream / event helpers -----------------------------------------------------------------------
+    def _record(self, stream=None):
+        if not self.is_cuda:
+            return None
+        ev = torch.cuda.Event()
+        ev.record(stream if stream is not None else torch.cuda.current_stream(self.device))
+        return ev
+
+    def _wait(self, ev, stream=None):
+        if ev is not None and self.is_cuda:
+            (stream if stream is not None else torch.cuda.current_stream(self.device)).wait_event(ev)
+
+    @contextlib.contextmanager
+    def _on(self, stream):
+        if stream is None:
+            yield
+        else:
+            with torch.cuda.stream(stream):
+                yield
+
+    # ---- gather / release ---------------------------------------------------------------------------
+    def _gather(self, i: int):
+        """Issue the all-gather of unit ``i`` on the comm stream (no-op if it is already in flight)."""
+        if self.resident or i in self._gathered or i < 0 or i >= len(self.units):
+            return
+        u = self.units[i]
+        slot, buf, free_ev = self.param_pool.acquire(i)
+        full = buf[:u.numel]
+        n = u.numel // self.W
+        with self._on(self.comm_stream):
+            self._wait(free_ev, self.comm_stream)
+            if self.cpu_offload:
+                src = full[self.R * n:(self.R + 1) * n]
+                src.copy_(self.shard_param[i], non_blocking=True)   # pinned H2D on the side stream
+            else:
+                src = self.shard_param[i]
+            if self.W > 1:
+                self.comm.all_gather(full, src)
+            ev = self._record(self.comm_stream)
+        self._gathered[i] = (slot, ev, full)
+
+    def _ensure(self, i: int):
+        if self.resident:
+            self._wait(self._opt_events.pop(i, None))
+            return
+        self._gather(i)
+        slot, ev, full = self._gathered[i]
+        self._wait(ev)
+        self.units[i].repoint(full)
+
+    def _release(self, i: int):
+        if self.resident or i not in self._gathered:
+            return
+        slot, _, _ = self._gathered.pop(i)
+        self.param_pool.release(slot, self._record())
+
+    def _tied_head(self, i: int) -> bool:
+        return self.cfg.tie_word_embeddings and i == len(self.units) - 1
+
+    # ---- unit callbacks (see hooks.run_unit) ----------------------------------------------------------
+    def _runner(self, idx, fn, *tensors):
+        ckpt = self.act_ckpt and 1 <= idx <= self.cfg.num_hidden_layers
+        return run_unit(self, idx, fn, *tensors, activation_checkpoint=ckpt)
+
+    def pre_forward(self, i):
+        self._ensure(i)
+        if self._tied_head(i):
+            self._ensure(0)
+        self._gather(i + 1)
+
+    def post_forward(self, i):
+        last = i == len(self.units) - 1
+        keep = (self.cfg.tie_word_embeddings and i == 0) or (last and torch.is_grad_enabled())
+        if self.reshard and not keep:
+            self._release(i)
+
+    def _assign_grad_buffer(self, i):
+        if self.resident or i in self._grad_slot:
+            return
+        u = self.units[i]
+        slot, buf, free_ev = self.grad_pool.acquire(i)
+        self._wait(free_ev)
+        u.assign_grads(buf[:u.numel])
+        self._grad_slot[i] = slot
+
+    def pre_backward(self, i):
+        self._ensure(i)
+        self._assign_grad_buffer(i)
+        if self._tied_head(i):
+            self._ensure(0)
+            self._assign_grad_buffer(0)
+        self._gather(i - 1)
+
+    def post_backward(self, i):
+        u = self.units[i]
+        u.finalize_grads()
+        if self.resident:
+            if self.fuse_optimizer and self.sync_grads:
+                self._fused_step(i, self._record())
+            return
+        if self.sync_grads:
+            self._reduce(i)
+        else:
+            self._accumulate_local(i)
+        self._release(i)
+
+    # ---- gradient reduction ---------------------------------------------------------------------------
+    def _accumulate_local(self, i):
+        """no_sync micro-step: park the unreduced gradient of the unit until the synchronising step."""
+        u = self.units[i]
+        if i in self._local_acc:
+            self._local_acc[i].add_(u.flat_grad)
+        else:
+            self._local_acc[i] = u.flat_grad.clone()
+        self.grad_pool.release(self._grad_slot.pop(i), self._record())
+
+    def _reduce(self, i):
+        u = self.units[i]
+        n = u.numel // self.W
+        full = u.flat_grad
+        if i in self._local_acc:
+            full.add_(self._local_acc.pop(i))
+        ready = self._record()
+        slot = self._grad_slot.pop(i)
+        with self._on(self.comm_stream):
+            self._wait(ready, self.comm_stream)
+            if self.cpu_offload:
+                if self.W > 1:
+                    dev = torch.empty(n, dtype=full.dtype, device=self.device)
+                    self.comm.reduce_scatter(dev, full, average=True)
+                else:
+                    dev = full[:n]
+                self.shard_grad[i].copy_(dev, non_blocking=True)      # D2H into pinned memory
+            else:
+                self.comm.reduce_scatter(self.shard_grad[i], full, average=True)
+            done = self._record(self.comm_stream)
+        self.grad_pool.release(slot, done)
+        if self.fuse_optimizer:
+            self._fused_step(i, done)
+
+    def _fused_step(self, i, after_event):
+        """Sharded AdamW for unit ``i`` on the side stream as soon as its gradient shard is final."""
+        if not self._stepped:
+            self.optimizer.begin_step()
+        self._stepped.add(i)
+        with self._on(self.comm_stream):
+            self._wait(after_event, self.comm_stream)
+            self.optimizer.step_unit(i, grad=self.shard_grad[i], param=self.shard_param[i],
+                                     max_blocks=(96 if self.is_cuda else 0))
+            if self.resident:
+                self._opt_events[i] = self._record(self.comm_stream)
+
+    # ---- phases ---------------------------------------------------------------------------------------
+    def backward(self, loss):
+        loss.backward()
+        self.post_backward(0)  # the embedding unit has no differentiable input to fire it
+        for i in list(self._gathered):
+            self._release(i)
+
+    def zero_grad(self):
+        for u in self.units:
+            u.zero_grad()
+
+    @contextlib.contextmanager
+    def no_sync(self):
+        """Skip the gradient reduction for micro-steps inside the context (gradient accumulation,
+        ``related-topics/gradient-accumulation/README.md:28-38``)."""
+        old = self.sync_grads
+        self.sync_grads = False
+        try:
+            yield
+        finally:
+            self.sync_grads = old
+
+    def optimizer_step(self):
+        if self.is_cuda:
+            if self.cpu_offload:
+                self.comm_stream.synchronize()   # gradient shards must have landed in host memory
+            else:
+                torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
+        if not self._stepped:
+            self.optimizer.begin_step()
+        for i in range(len(self.units)):
+            if i not in self._stepped:
+                self.optimizer.step_unit(i, grad=self.shard_grad[i], param=self.shard_param[i])
+        self._stepped.clear()
+        self.lr_scheduler.step()
+        if self.is_cuda:
+            self.comm_stream.wait_stream(torch.cuda.current_stream(self.device))
+
+    # ---- state ----------------------------------------------------------------------------------------
+    @torch.no_grad()
+    def gather_full_state_dict(self):
+        """HF-named full (unsharded) parameters on every rank -- for tests and export."""
+        if self.is_cuda:
+            torch.cuda.synchronize(self.device)
+        keep = []
+        for i, u in enumerate(self.units):
+            if self.resident:
+                continue
+            full = torch.empty(u.numel, dtype=self.dtype, device=self.device)
+            n = u.numel // self.W
+            full[self.R * n:(self.R + 1) * n].copy_(self.shard_param[i])
+            if self.W > 1:
+                self.comm.all_gather(full, full[self.R * n:(self.R + 1) * n].clone())
+            u.repoint(full)
+            keep.append(full)
+        return {k: v.clone() for k, v in self.model.hf_state_dict().items()}
+
+    def model_state_dict(self):
+        return self.gather_full_state_dict()
+
+
+class _Layout(FlatUnit):
+    """A FlatUnit whose storage is transient: ``repoint``/``assign_grads`` attach it to pool buffers."""
+
+    def __init__(self, name, params, world):
+        # layout only (parameters are on the meta device at this point)
+        self.name = name
+        self.params = []
+        seen = set()
+        for p in params:
+            if id(p) not in seen:
+                seen.add(id(p))
+                self.params.append(p)
+        from ..utils.flat import ALIGN, _round_up
+
+        self.offsets = []
+        off = 0
+        for p in self.params:
+            self.offsets.append(off)
+            off += _round_up(p.numel(), ALIGN)
+        self.numel = _round_up(off, ALIGN * world)
+        self.dtype = self.params[0].dtype
+        self.device = None
+        self.flat_param = None
+        self.flat_grad = None
+        self.direct = False
+
+    def materialize(self, model, full, seed, unit_index, cfg):
+        """Initialise this unit's parameters into ``full`` (HF ``_init_weights`` rules), identically on
+        every rank (same generator seed), which stands in for rank-0 init + broadcast."""
+        self.device = full.device
+        self.direct = full.device.type == "cuda" and full.dtype == torch.bfloat16
+        full.zero_()
+        gen = torch.Generator(device=full.device).manual_seed(seed * 100003 + unit_index)
+        names = {id(p): n for n, p in model.named_parameters()}
+        for p, o in zip(self.params, self.offsets):
+            view = full[o:o + p.numel()].view(p.shape)
+            name = names.get(id(p), "")
+            if name.endswith("bias"):
+                view.zero_()
+            elif "norm" in name or ".ln_" in name or "ln_f" in name:
+                view.fill_(1.0)
+            else:
+                view.normal_(0.0, cfg.initializer_range, generator=gen)
+        self.flat_param = full
+        # meta parameters cannot adopt real storage: create real Parameters (views of the flat buffer)
+        # and let the caller swap them into the module tree (ties are preserved by identity)
+        swap = {}
+        new_params = []
+        for p, o in zip(self.params, self.offsets):
+            # (.data assignment: the Parameter must not share the pool buffer's version counter)
+            q = torch.nn.Parameter(torch.empty(0, dtype=full.dtype, device=full.device), requires_grad=True)
+            q.data = full[o:o + p.numel()].view(p.shape)
+            q._b2_unit = self
+            swap[id(p)] = q
+            new_params.append(q)
+        self.params = new_params
+        return swap
+
+    def repoint(self, full):
+        self.flat_param = full
+        for p, o in zip(self.params, self.offsets):
+            p.data = full[o:o + p.numel()].view(p.shape)
+
+    def assign_grads(self, flat_grad):
+        self.flat_grad = flat_grad
+        if not self.direct:
+            flat_grad.zero_()  # autograd accumulates into these views (reference-math path)
+        for p, o in zip(self.params, self.offsets):
+            p.grad = flat_grad[o:o + p.numel()].view(p.shape)
+            p._b2_direct_grad = self.direct
+            p._b2_grad_ready = False
+
+    def zero_grad(self):
+        if self.flat_grad is None:
+            return
+        if not self.direct:
+            self.flat_grad.zero_()
+            return
+        for p in self.params:
+            p._b2_grad_ready = False
+
+    def finalize_grads(self):
+        if not self.direct or self.flat_grad is None:
+            return
+        for p in self.params:
+            if not getattr(p, "_b2_grad_ready", False):
+                p.grad.zero_()

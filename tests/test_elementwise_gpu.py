@@ -1,0 +1,172 @@
+"""Memory-bound kernels vs fp32 PyTorch references (forward and backward)."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _r(*shape, seed=0, scale=1.0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    return (torch.randn(*shape, device="cuda", generator=g) * scale).to(torch.bfloat16)
+
+
+def _close(a, b, atol, rtol=2e-2):
+    a, b = a.float(), b.float()
+    err = (a - b).abs()
+    tol = atol + rtol * b.abs()
+    assert bool((err <= tol).all()), f"max err {err.max().item()} at tol {tol.flatten()[err.argmax()].item()}"
+
+
+@pytest.mark.parametrize("H", [768, 4096, 8192, 16384])
+@pytest.mark.parametrize("with_res", [False, True])
+def test_rmsnorm(H, with_res):
+    from b200train.ops.norm import rmsnorm, rmsnorm_ref
+
+    T = 300
+    x = _r(T, H, seed=1).requires_grad_()
+    res = _r(T, H, seed=2).requires_grad_() if with_res else None
+    w = (1 + 0.1 * _r(H, seed=3).float()).to(torch.bfloat16).requires_grad_()
+    y, h = rmsnorm(x, w, 1e-5, res)
+    gy, gh = _r(T, H, seed=4), _r(T, H, seed=5)
+    (y.float() * gy.float()).sum().backward() if not with_res else ((y.float() * gy.float()).sum() + (h.float() * gh.float()).sum()).backward()
+    xr = x.detach().float().requires_grad_()
+    rr = res.detach().float().requires_grad_() if with_res else None
+    wr = w.detach().float().requires_grad_()
+    hr = xr + rr if with_res else xr
+    yr = wr * (hr * torch.rsqrt(hr.pow(2).mean(-1, keepdim=True) + 1e-5))
+    loss = (yr * gy.float()).sum() + ((hr * gh.float()).sum() if with_res else 0)
+    loss.backward()
+    _close(y, yr, 2e-2)
+    _close(x.grad, xr.grad, 3e-2)
+    if with_res:
+        _close(h, hr, 2e-2)
+        _close(res.grad, rr.grad, 3e-2)
+    _close(w.grad, wr.grad, 0.3, 3e-2)
+
+
+@pytest.mark.parametrize("H", [768, 2048])
+def test_layernorm(H):
+    from b200train.ops.norm import layernorm
+
+    T = 257
+    x, res = _r(T, H, seed=1).requires_grad_(), _r(T, H, seed=2).requires_grad_()
+    w = (1 + 0.1 * _r(H, seed=3).float()).to(torch.bfloat16).requires_grad_()
+    b = _r(H, seed=4, scale=0.1).requires_grad_()
+    y, h = layernorm(x, w, b, 1e-5, res)
+    gy = _r(T, H, seed=5)
+    (y.float() * gy.float()).sum().backward()
+    xr, rr = x.detach().float().requires_grad_(), res.detach().float().requires_grad_()
+    wr, br = w.detach().float().requires_grad_(), b.detach().float().requires_grad_()
+    yr = torch.nn.functional.layer_norm(xr + rr, (H,), wr, br, 1e-5)
+    (yr * gy.float()).sum().backward()
+    _close(y, yr, 3e-2)
+    _close(x.grad, xr.grad, 3e-2)
+    _close(res.grad, rr.grad, 3e-2)
+    _close(w.grad, wr.grad, 0.3, 3e-2)
+    _close(b.grad, br.grad, 0.3, 3e-2)
+
+
+def test_swiglu_and_gelu():
+    from b200train.ops.activation import gelu_new, gelu_new_ref, swiglu, swiglu_ref
+
+    gu = _r(513, 2 * 1024, seed=1).requires_grad_()
+    g = _r(513, 1024, seed=2)
+    out = swiglu(gu)
+    out.backward(g)
+    gr = gu.detach().float().requires_grad_()
+    outr = swiglu_ref(gr)
+    outr.backward(g.float())
+    _close(out, outr, 2e-2)
+    _close(gu.grad, gr.grad, 2e-2)
+    x = _r(300, 3072, seed=3).requires_grad_()
+    gx = _r(300, 3072, seed=4)
+    y = gelu_new(x)
+    y.backward(gx)
+    xr = x.detach().float().requires_grad_()
+    yr = gelu_new_ref(xr)
+    yr.backward(gx.float())
+    _close(y, yr, 2e-2)
+    _close(x.grad, xr.grad, 2e-2)
+
+
+@pytest.mark.parametrize("D", [64, 128])
+@pytest.mark.parametrize("packed", [False, True])
+def test_rope(D, packed):
+    from b200train.ops.rope import rope_qk, rope_qk_ref, rope_tables
+
+    nq, nkv, S, B = 8, 2, 96, 3
+    T = B * S
+    cos, sin = rope_tables(D, 256, 500000.0, None, device="cuda")
+    base = _r(T, (nq + 2 * nkv) * D, seed=1)
+    pos = None
+    if packed:
+        pos = (torch.arange(T, device="cuda") % 50).to(torch.int32)
+    ref_in = base.clone().float().requires_grad_()
+    ref = rope_qk_ref(ref_in, cos.float(), sin.float(), pos, nq + nkv, D, S)
+    g = _r(T, (nq + 2 * nkv) * D, seed=2)
+    ref.backward(g.float())
+    lin = base.clone().requires_grad_()
+    out = rope_qk(lin * 1, cos, sin, pos, nq + nkv, D, S)
+    out.backward(g)
+    _close(out, ref, 2e-2)
+    _close(lin.grad, ref_in.grad, 2e-2)
+
+
+def test_embedding():
+    from b200train.ops.embedding import embedding
+
+    V, H, T = 1000, 512, 777
+    table = _r(V, H, seed=1).requires_grad_()
+    ids = torch.randint(0, V, (T,), device="cuda")
+    ids[:50] = 7  # heavy duplicates exercise the atomics
+    out = embedding(ids, table)
+    g = _r(T, H, seed=2)
+    out.backward(g)
+    tr = table.detach().float().requires_grad_()
+    outr = torch.nn.functional.embedding(ids, tr)
+    outr.backward(g.float())
+    assert torch.equal(out.float(), outr)
+    _close(table.grad, tr.grad, 0.15, 3e-2)
+
+
+@pytest.mark.parametrize("V", [1000, 50257, 128256])
+def test_linear_cross_entropy(V):
+    from b200train.ops.cross_entropy import IGNORE, linear_cross_entropy
+
+    T, H = 384, 256
+    x = _r(T, H, seed=1).requires_grad_()
+    w = _r(V, H, seed=2, scale=0.05).requires_grad_()
+    labels = torch.randint(0, V, (T,), device="cuda")
+    labels[::7] = IGNORE
+    loss = linear_cross_entropy(x, w, labels)
+    loss.backward()
+    xr, wr = x.detach().float().requires_grad_(), w.detach().float().requires_grad_()
+    logits = (xr @ wr.t()).to(torch.bfloat16).float()  # kernel sees bf16 logits (as HF does before .float())
+    lr = torch.nn.functional.cross_entropy(xr @ wr.t(), labels, ignore_index=IGNORE)
+    lr.backward()
+    assert abs(loss.item() - lr.item()) < 2e-2, (loss.item(), lr.item())
+    _close(x.grad, xr.grad, 2e-4, 5e-2)
+    _close(w.grad, wr.grad, 2e-4, 5e-2)
+
+
+def test_adamw_matches_torch_fused():
+    from b200train.ops.optim import adamw_step
+
+    n = 1_000_003
+    p = _r(n, seed=1)
+    g = _r(n, seed=2, scale=0.01)
+    p_ref = torch.nn.Parameter(p.clone())
+    opt = torch.optim.AdamW([p_ref], lr=1e-3, fused=True)
+    m, v = torch.zeros_like(p), torch.zeros_like(p)
+    for step in range(1, 4):
+        p_ref.grad = g.clone()
+        opt.step()
+        adamw_step(p, g, m, v, 1e-3, step=step)
+    torch.cuda.synchronize()
+    diff = (p.float() - p_ref.detach().float()).abs().max().item()
+    assert diff <= 2 ** -7 * p.float().abs().max().item(), diff  # <= 1 bf16 ulp at the largest magnitude
+    st = opt.state[p_ref]
+    _close(m, st["exp_avg"], 1e-5, 1e-2)
+    _close(v, st["exp_avg_sq"], 1e-8, 1e-2)
