@@ -1,0 +1,503 @@
+// Causal flash-attention backward for sm_100a on tcgen05 tensor cores with TMEM accumulators.
+//
+// One CTA per (document, kv head, 64-row kv block j). It keeps K_j and V_j in shared memory and walks
+// every (query head of the GQA group, 128-row query block i that can see block j). Per step:
+//     S    = Q_i  K_j^T            [128 x 64]   TMEM, double buffered
+//     dP   = dO_i V_j^T            [128 x 64]   TMEM, double buffered
+//     P    = exp2(S*c - lse), dS = P * (dP - delta) * scale        (softmax warpgroup, registers)
+//     dV^T += dO_i^T P             [D x 64]     TMEM accumulator over all steps
+//     dK^T += Q_i^T  dS            [D x 64]     TMEM accumulator over all steps
+//     dQ_i  = dS K_j               [128 x D]    TMEM -> fp32 red.global.add into dq_accum
+// dV and dK are accumulated transposed so that every MMA has M = 128 (full tensor-core rate); the same
+// 128B-swizzled smem tile serves as a K-major operand ([rows, 64] atoms) and as the MN-major operand of
+// the transposed product, so Q, dO, K, P and dS are each stored once.
+//   warp 0     TMA producer (K_j, V_j once; 2-stage ring of Q_i / dO_i)
+//   warp 1     MMA issuer
+//   warps 2-5  softmax warpgroup (one thread per query row)
+//   warps 6-9  dQ warpgroup (TMEM -> red.global.add.v4.f32), also drains dK^T at the end
+//
+// Replaces flash_attn_2_cuda's backward (reference: 05-training-llama-405b/train_llm.py:87 +
+// loss.backward() at :237).
+#include "common.cuh"
+#include <math.h>
+
+namespace b2 {
+
+constexpr int QB = 128;  // query rows per step
+constexpr int KB = 64;   // kv rows per CTA
+constexpr int kBwdThreads = 320;
+
+template <int D>
+struct AttnBwdSmem {
+  static constexpr int kK = KB * D * 2;
+  static constexpr int kV = KB * D * 2;
+  static constexpr int kQ = QB * D * 2;
+  static constexpr int kDO = QB * D * 2;
+  static constexpr int kP = QB * KB * 2;   // 16 KB
+  static constexpr int kDS = QB * KB * 2;  // 16 KB
+  static constexpr int kTotal = kK + kV + 2 * (kQ + kDO) + 2 * (kP + kDS) + 256 + 1024;
+};
+
+struct AttnBwdParams {
+  float* dq_accum;  // [T, Hq*D] fp32, zeroed
+  __nv_bfloat16* dk;
+  __nv_bfloat16* dv;
+  const float* lse;    // [Hq, T]
+  const float* delta;  // [Hq, T]
+  const int* cu_seqlens;
+  int dk_stride, dv_stride;
+  int T, Hq, Hkv;
+  float scale, scale_log2;
+  int causal;
+};
+
+// delta[h, t] = sum_d dO[t, h, d] * O[t, h, d]
+__global__ void attn_bwd_delta_kernel(float* __restrict__ delta, const __nv_bfloat16* __restrict__ dO,
+                                      const __nv_bfloat16* __restrict__ O, int T, int Hq, int D,
+                                      int do_stride, int o_stride) {
+  const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp_global >= T * Hq) return;
+  const int t = warp_global / Hq, h = warp_global % Hq;
+  const __nv_bfloat16* a = dO + (size_t)t * do_stride + (size_t)h * D;
+  const __nv_bfloat16* b = O + (size_t)t * o_stride + (size_t)h * D;
+  float s = 0.f;
+  for (int i = lane * 2; i < D; i += 64) {
+    const float2 x = unpack_bf16(*reinterpret_cast<const uint32_t*>(a + i));
+    const float2 y = unpack_bf16(*reinterpret_cast<const uint32_t*>(b + i));
+    s += x.x * y.x + x.y * y.y;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) delta[(size_t)h * T + t] = s;
+}
+
+// dq[t, :] = bf16(dq_accum[t, :])
+__global__ void attn_bwd_convert_dq_kernel(__nv_bfloat16* __restrict__ dq,
+                                           const float* __restrict__ acc, int T, int cols,
+                                           int dq_stride) {
+  const int nvec = cols >> 2;
+  const size_t total = (size_t)T * nvec;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const size_t t = i / nvec;
+    const int c = (int)(i - t * nvec);
+    const float4 v = reinterpret_cast<const float4*>(acc + t * cols)[c];
+    uint2 o;
+    o.x = pack_bf16(v.x, v.y);
+    o.y = pack_bf16(v.z, v.w);
+    *reinterpret_cast<uint2*>(dq + t * (size_t)dq_stride + c * 4) = o;
+  }
+}
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c),
+               "f"(d)
+               : "memory");
+}
+
+template <int D>
+__global__ void __launch_bounds__(kBwdThreads, 1)
+attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
+                AttnBwdParams p) {
+  using SM = AttnBwdSmem<D>;
+  constexpr int kAtoms = D / 64;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint8_t* sK = smem;
+  uint8_t* sV = sK + SM::kK;
+  uint8_t* sQ = sV + SM::kV;            // 2 stages
+  uint8_t* sDO = sQ + 2 * SM::kQ;       // 2 stages
+  uint8_t* sP = sDO + 2 * SM::kDO;      // 2 buffers
+  uint8_t* sDS = sP + 2 * SM::kP;       // 2 buffers
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sDS + 2 * SM::kDS);
+  uint64_t* kv_full = bars;            // 1
+  uint64_t* qdo_full = bars + 1;       // 2
+  uint64_t* qdo_empty = bars + 3;      // 2
+  uint64_t* sdp_full = bars + 5;       // 2
+  uint64_t* sdp_free = bars + 7;       // 2
+  uint64_t* pds_full = bars + 9;       // 2
+  uint64_t* pds_empty = bars + 11;     // 2
+  uint64_t* dq_full = bars + 13;       // 1
+  uint64_t* dq_free = bars + 14;       // 1
+  uint64_t* done_bar = bars + 15;      // 1
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
+
+  const int warp = threadIdx.x >> 5;
+  const int doc = blockIdx.z;
+  const int kvh = blockIdx.y;
+  const int doc_start = p.cu_seqlens[doc];
+  const int doc_len = p.cu_seqlens[doc + 1] - doc_start;
+  const int num_kb = (doc_len + KB - 1) / KB;
+  const int jb = (int)blockIdx.x;  // small j = most work: launched first
+  if (jb >= num_kb) return;
+  const int kv0 = jb * KB;
+  const int num_qb = (doc_len + QB - 1) / QB;
+  const int i0 = p.causal ? kv0 / QB : 0;   // first query block that sees this kv block
+  const int nqi = num_qb - i0;
+  const int group = p.Hq / p.Hkv;
+  const int n_iter = group * nqi;
+
+  if (warp == 0 && elect_one()) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmK);
+    tma_prefetch_desc(&tmV);
+    tma_prefetch_desc(&tmDO);
+    mbar_init(kv_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&qdo_full[i], 1);
+      mbar_init(&qdo_empty[i], 1);
+      mbar_init(&sdp_full[i], 1);
+      mbar_init(&sdp_free[i], 4);
+      mbar_init(&pds_full[i], 4);
+      mbar_init(&pds_empty[i], 1);
+    }
+    mbar_init(dq_full, 1);
+    mbar_init(dq_free, 4);
+    mbar_init(done_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<1>(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tm_S[2] = {tmem_base, tmem_base + 64};
+  const uint32_t tm_dP[2] = {tmem_base + 128, tmem_base + 192};
+  const uint32_t tm_dQ = tmem_base + 256;
+  const uint32_t tm_dVt = tmem_base + 384;
+  const uint32_t tm_dKt = tmem_base + 448;
+
+  if (warp == 0) {
+    // ================= TMA producer =================
+    if (elect_one()) {
+      mbar_expect_tx(kv_full, SM::kK + SM::kV);
+#pragma unroll
+      for (int a = 0; a < kAtoms; ++a) {
+        tma_load_2d<1>(&tmK, kv_full, sK + a * (KB * 128), kvh * D + a * 64, doc_start + kv0,
+                       kEvictFirst);
+        tma_load_2d<1>(&tmV, kv_full, sV + a * (KB * 128), kvh * D + a * 64, doc_start + kv0,
+                       kEvictFirst);
+      }
+      for (int it = 0; it < n_iter; ++it) {
+        const int s = it & 1;
+        const int head = kvh * group + it / nqi;
+        const int row = doc_start + (i0 + it % nqi) * QB;
+        mbar_wait(&qdo_empty[s], ((it >> 1) & 1) ^ 1);
+        mbar_expect_tx(&qdo_full[s], SM::kQ + SM::kDO);
+#pragma unroll
+        for (int a = 0; a < kAtoms; ++a) {
+          tma_load_2d<1>(&tmQ, &qdo_full[s], sQ + s * SM::kQ + a * (QB * 128), head * D + a * 64, row,
+                         kEvictLast);
+          tma_load_2d<1>(&tmDO, &qdo_full[s], sDO + s * SM::kDO + a * (QB * 128), head * D + a * 64,
+                         row, kEvictLast);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    constexpr uint32_t idesc_s = make_idesc_bf16(QB, KB, false, false);   // S, dP: K-major x K-major
+    constexpr uint32_t idesc_t = make_idesc_bf16(128, KB, true, true);    // dV^T, dK^T: MN x MN
+    constexpr uint32_t idesc_q = make_idesc_bf16(QB, D, false, true);     // dQ: K-major x MN-major
+    // D = 64: the M = 128 transposed products read the single 64-row atom twice (LBO = 0); the
+    // duplicate accumulator lanes 64..127 are never read back.
+    constexpr uint32_t lbo_t = (D == 128) ? QB * 128 : 0;
+    auto issue_sdp = [&](int it) {
+      const int s = it & 1;
+      mbar_wait(&qdo_full[s], (it >> 1) & 1);
+      mbar_wait(&sdp_free[s], ((it >> 1) & 1) ^ 1);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t qa = smem_u32(sQ + s * SM::kQ), da = smem_u32(sDO + s * SM::kDO);
+        const uint32_t ka = smem_u32(sK), va = smem_u32(sV);
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk) {
+          const uint32_t offa = (kk >> 2) * (QB * 128) + (kk & 3) * 32;
+          const uint32_t offb = (kk >> 2) * (KB * 128) + (kk & 3) * 32;
+          umma_f16<1>(tm_S[s], make_smem_desc_sw128(qa + offa, 16, 1024),
+                      make_smem_desc_sw128(ka + offb, 16, 1024), idesc_s, kk != 0);
+        }
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk) {
+          const uint32_t offa = (kk >> 2) * (QB * 128) + (kk & 3) * 32;
+          const uint32_t offb = (kk >> 2) * (KB * 128) + (kk & 3) * 32;
+          umma_f16<1>(tm_dP[s], make_smem_desc_sw128(da + offa, 16, 1024),
+                      make_smem_desc_sw128(va + offb, 16, 1024), idesc_s, kk != 0);
+        }
+        umma_commit<1>(&sdp_full[s]);
+      }
+      __syncwarp();
+    };
+    mbar_wait(kv_full, 0);
+    if (n_iter > 0) issue_sdp(0);
+    for (int it = 0; it < n_iter; ++it) {
+      if (it + 1 < n_iter) issue_sdp(it + 1);
+      const int s = it & 1;
+      mbar_wait(&pds_full[s], (it >> 1) & 1);
+      mbar_wait(dq_free, (it & 1) ^ 1);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t qa = smem_u32(sQ + s * SM::kQ), da = smem_u32(sDO + s * SM::kDO);
+        const uint32_t pa = smem_u32(sP + s * SM::kP), dsa = smem_u32(sDS + s * SM::kDS);
+        const uint32_t ka = smem_u32(sK);
+        // dV^T[D, kv] += dO^T[D, q] P[q, kv]   (reduction over the 128 query rows)
+#pragma unroll
+        for (int kk = 0; kk < QB / 16; ++kk)
+          umma_f16<1>(tm_dVt, make_smem_desc_sw128(da + kk * 2048, lbo_t, 1024),
+                      make_smem_desc_sw128(pa + kk * 2048, 16, 1024), idesc_t, (it | kk) != 0);
+        // dK^T[D, kv] += Q^T[D, q] dS[q, kv]
+#pragma unroll
+        for (int kk = 0; kk < QB / 16; ++kk)
+          umma_f16<1>(tm_dKt, make_smem_desc_sw128(qa + kk * 2048, lbo_t, 1024),
+                      make_smem_desc_sw128(dsa + kk * 2048, 16, 1024), idesc_t, (it | kk) != 0);
+        // dQ[q, D] = dS[q, kv] K[kv, D]        (reduction over the 64 kv rows)
+#pragma unroll
+        for (int kk = 0; kk < KB / 16; ++kk)
+          umma_f16<1>(tm_dQ, make_smem_desc_sw128(dsa + kk * 32, 16, 1024),
+                      make_smem_desc_sw128(ka + kk * 2048, KB * 128, 1024), idesc_q, kk != 0);
+        umma_commit<1>(&qdo_empty[s]);
+        umma_commit<1>(&pds_empty[s]);
+        umma_commit<1>(dq_full);
+        if (it == n_iter - 1) umma_commit<1>(done_bar);
+      }
+      __syncwarp();
+    }
+  } else if (warp < 6) {
+    // ================= softmax warpgroup =================
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + (int)lane_id();
+    const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
+    for (int it = 0; it < n_iter; ++it) {
+      const int s = it & 1;
+      const int head = kvh * group + it / nqi;
+      const int q_idx = (i0 + it % nqi) * QB + row;
+      const bool valid_row = q_idx < doc_len;
+      float lse2 = 0.f, delta = 0.f;
+      if (valid_row) {
+        lse2 = p.lse[(size_t)head * p.T + doc_start + q_idx] * 1.4426950408889634f;
+        delta = p.delta[(size_t)head * p.T + doc_start + q_idx];
+      }
+      mbar_wait(&sdp_full[s], (it >> 1) & 1);
+      tc_fence_after();
+      uint32_t sr[KB], dr[KB];
+      {
+        uint32_t t0[32], t1[32];
+        tmem_ld_32x32b_x32(tm_S[s] + lane_off, t0);
+        tmem_ld_32x32b_x32(tm_S[s] + lane_off + 32, t1);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) { sr[i] = t0[i]; sr[32 + i] = t1[i]; }
+        tmem_ld_32x32b_x32(tm_dP[s] + lane_off, t0);
+        tmem_ld_32x32b_x32(tm_dP[s] + lane_off + 32, t1);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) { dr[i] = t0[i]; dr[32 + i] = t1[i]; }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane_id() == 0) mbar_arrive(&sdp_free[s]);
+      // last kv index this query row may attend
+      const int lim = valid_row ? (p.causal ? min(q_idx, doc_len - 1) : doc_len - 1) : -1;
+      uint32_t pp[KB / 2], dd[KB / 2];
+#pragma unroll
+      for (int i = 0; i < KB / 2; ++i) {
+        float pv[2], dv[2];
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int c = 2 * i + e;
+          const bool on = (kv0 + c) <= lim;
+          const float pe = on ? exp2f(__uint_as_float(sr[c]) * p.scale_log2 - lse2) : 0.f;
+          pv[e] = pe;
+          dv[e] = pe * (__uint_as_float(dr[c]) - delta) * p.scale;
+        }
+        pp[i] = pack_bf16(pv[0], pv[1]);
+        dd[i] = pack_bf16(dv[0], dv[1]);
+      }
+      mbar_wait(&pds_empty[s], ((it >> 1) & 1) ^ 1);
+      const uint32_t prow = smem_u32(sP + s * SM::kP) + row * 128;
+      const uint32_t drow = smem_u32(sDS + s * SM::kDS) + row * 128;
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        const uint32_t off = (c ^ (row & 7)) << 4;
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(prow + off), "r"(pp[4 * c]),
+                     "r"(pp[4 * c + 1]), "r"(pp[4 * c + 2]), "r"(pp[4 * c + 3])
+                     : "memory");
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(drow + off), "r"(dd[4 * c]),
+                     "r"(dd[4 * c + 1]), "r"(dd[4 * c + 2]), "r"(dd[4 * c + 3])
+                     : "memory");
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane_id() == 0) mbar_arrive(&pds_full[s]);
+    }
+    // ---- drain dV^T: lane = head-dim index d, columns = kv rows ----
+    if (n_iter > 0) {
+      mbar_wait(done_bar, 0);
+      tc_fence_after();
+      const int d = row;
+#pragma unroll
+      for (int c = 0; c < KB / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(tm_dVt + lane_off + c * 32, r);
+        tmem_ld_wait();
+        if (d < D) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const int kv = kv0 + c * 32 + i;
+            if (kv < doc_len)
+              p.dv[(size_t)(doc_start + kv) * p.dv_stride + (size_t)kvh * D + d] =
+                  __float2bfloat16_rn(__uint_as_float(r[i]));
+          }
+        }
+      }
+      tc_fence_before();
+    }
+  } else {
+    // ================= dQ warpgroup =================
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + (int)lane_id();
+    const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
+    for (int it = 0; it < n_iter; ++it) {
+      const int head = kvh * group + it / nqi;
+      const int q_idx = (i0 + it % nqi) * QB + row;
+      mbar_wait(dq_full, it & 1);
+      tc_fence_after();
+      uint32_t r[D];
+#pragma unroll
+      for (int c = 0; c < D / 32; ++c) {
+        uint32_t t[32];
+        tmem_ld_32x32b_x32(tm_dQ + lane_off + c * 32, t);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) r[c * 32 + i] = t[i];
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane_id() == 0) mbar_arrive(dq_free);
+      if (q_idx < doc_len) {
+        float* dst = p.dq_accum + (size_t)(doc_start + q_idx) * ((size_t)p.Hq * D) + (size_t)head * D;
+#pragma unroll
+        for (int c = 0; c < D / 4; ++c)
+          red_add_v4(dst + 4 * c, __uint_as_float(r[4 * c]), __uint_as_float(r[4 * c + 1]),
+                     __uint_as_float(r[4 * c + 2]), __uint_as_float(r[4 * c + 3]));
+      }
+    }
+    // ---- drain dK^T ----
+    if (n_iter > 0) {
+      mbar_wait(done_bar, 0);
+      tc_fence_after();
+      const int d = row;
+#pragma unroll
+      for (int c = 0; c < KB / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(tm_dKt + lane_off + c * 32, r);
+        tmem_ld_wait();
+        if (d < D) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const int kv = kv0 + c * 32 + i;
+            if (kv < doc_len)
+              p.dk[(size_t)(doc_start + kv) * p.dk_stride + (size_t)kvh * D + d] =
+                  __float2bfloat16_rn(__uint_as_float(r[i]));
+          }
+        }
+      }
+      tc_fence_before();
+    }
+  }
+
+  __syncwarp();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<1>(tmem_base, 512);
+  }
+}
+
+template <int D>
+static int launch_attn_bwd(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
+                           const CUtensorMap& tmDO, const AttnBwdParams& prm, int max_kblocks,
+                           int ndocs, cudaStream_t stream) {
+  using SM = AttnBwdSmem<D>;
+  auto kern = attn_bwd_kernel<D>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B2_CUDA_CHECK(
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::kTotal));
+    attr_set = true;
+  }
+  dim3 grid(max_kblocks, prm.Hkv, ndocs);
+  kern<<<grid, kBwdThreads, SM::kTotal, stream>>>(tmQ, tmK, tmV, tmDO, prm);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace b2
+
+extern "C" {
+
+// Gradients of b2_attn_fwd. dq/dk/dv are strided [T, heads*D] bf16 views (e.g. slices of one fused
+// dQKV buffer). Scratch supplied by the caller: dq_accum fp32 [T, Hq*D] (zeroed here, contiguous),
+// delta fp32 [Hq, T].
+int b2_attn_bwd(void* dq, void* dk, void* dv, float* dq_accum, float* delta, const void* dout,
+                const void* q, const void* k, const void* v, const void* o, const float* lse,
+                const int* cu_seqlens, int ndocs, int max_seqlen, int T, int Hq, int Hkv, int D,
+                int q_stride, int k_stride, int v_stride, int o_stride, int do_stride,
+                int dq_stride, int dk_stride, int dv_stride, float softmax_scale, int causal,
+                cudaStream_t stream) {
+  using namespace b2;
+  B2_REQUIRE(D == 64 || D == 128, "attn bwd: head_dim %d unsupported (64 or 128)", D);
+  B2_REQUIRE(Hq % Hkv == 0, "attn bwd: Hq=%d not a multiple of Hkv=%d", Hq, Hkv);
+  B2_REQUIRE(dq_stride % 4 == 0, "attn bwd: dq stride must be a multiple of 4");
+  if (T == 0 || ndocs == 0) return 0;
+  B2_CUDA_CHECK(cudaMemsetAsync(dq_accum, 0, (size_t)T * Hq * D * sizeof(float), stream));
+  {
+    const int warps = T * Hq;
+    const int threads = 256;
+    const int blocks = (warps * 32 + threads - 1) / threads;
+    attn_bwd_delta_kernel<<<blocks, threads, 0, stream>>>(
+        delta, static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(o), T, Hq,
+        D, do_stride, o_stride);
+    B2_CUDA_CHECK(cudaGetLastError());
+  }
+  CUtensorMap tmQ, tmK, tmV, tmDO;
+  int rc;
+  if ((rc = make_tmap_2d_bf16(&tmQ, q, T, (uint64_t)Hq * D, q_stride, QB, 64))) return rc;
+  if ((rc = make_tmap_2d_bf16(&tmDO, dout, T, (uint64_t)Hq * D, do_stride, QB, 64))) return rc;
+  if ((rc = make_tmap_2d_bf16(&tmK, k, T, (uint64_t)Hkv * D, k_stride, KB, 64))) return rc;
+  if ((rc = make_tmap_2d_bf16(&tmV, v, T, (uint64_t)Hkv * D, v_stride, KB, 64))) return rc;
+  AttnBwdParams prm;
+  prm.dq_accum = dq_accum;
+  prm.dk = static_cast<__nv_bfloat16*>(dk);
+  prm.dv = static_cast<__nv_bfloat16*>(dv);
+  prm.lse = lse;
+  prm.delta = delta;
+  prm.cu_seqlens = cu_seqlens;
+  prm.dk_stride = dk_stride;
+  prm.dv_stride = dv_stride;
+  prm.T = T;
+  prm.Hq = Hq;
+  prm.Hkv = Hkv;
+  prm.scale = softmax_scale;
+  prm.scale_log2 = softmax_scale * 1.4426950408889634f;
+  prm.causal = causal;
+  const int max_kb = (max_seqlen + KB - 1) / KB;
+  if (D == 64) rc = launch_attn_bwd<64>(tmQ, tmK, tmV, tmDO, prm, max_kb, ndocs, stream);
+  else rc = launch_attn_bwd<128>(tmQ, tmK, tmV, tmDO, prm, max_kb, ndocs, stream);
+  if (rc) return rc;
+  {
+    const int cols = Hq * D;
+    const size_t work = (size_t)T * (cols / 4);
+    int blocks = (int)((work + 255) / 256);
+    const int cap = sm_count() * 16;
+    if (blocks > cap) blocks = cap;
+    attn_bwd_convert_dq_kernel<<<blocks, 256, 0, stream>>>(static_cast<__nv_bfloat16*>(dq), dq_accum,
+                                                           T, cols, dq_stride);
+    B2_CUDA_CHECK(cudaGetLastError());
+  }
+  return 0;
+}
+
+}  // extern "C"

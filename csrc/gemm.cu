@@ -425,6 +425,8 @@ static int dispatch_layout(void* C, const void* A, const void* B, int M, int N, 
   } else if (!a_mn && b_mn) {
     switch (epilogue) {
       case EPI_NONE: B2_GEMM_CASE(true, false, EPI_NONE);
+      case EPI_BIAS: B2_GEMM_CASE(true, false, EPI_BIAS);
+      case EPI_BIAS_GELU: B2_GEMM_CASE(true, false, EPI_BIAS_GELU);
       case EPI_ACCUM: B2_GEMM_CASE(true, false, EPI_ACCUM);
     }
   } else if (a_mn && b_mn) {

@@ -48,13 +48,10 @@ class _Linear(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, bias, w_is_kn):
         # w_is_kn: weight stored [in, out] (GPT-2 Conv1D) instead of [out, in]
+        # x is 2-D [T, in]; the output is a fresh (non-view) tensor so callers may modify it in place
         ctx.w_is_kn = w_is_kn
-        x2 = x.reshape(-1, x.shape[-1])
-        ctx.save_for_backward(x2, w, bias)
-        ctx.x_shape = x.shape
-        n_out = w.shape[1] if w_is_kn else w.shape[0]
-        y = gemm(x2, w, b_mn=w_is_kn, epilogue=EPI_BIAS if bias is not None else EPI_NONE, bias=bias)
-        return y.view(*x.shape[:-1], n_out)
+        ctx.save_for_backward(x, w, bias)
+        return gemm(x, w, b_mn=w_is_kn, epilogue=EPI_BIAS if bias is not None else EPI_NONE, bias=bias)
 
     @staticmethod
     def backward(ctx, dy):
@@ -65,7 +62,7 @@ class _Linear(torch.autograd.Function):
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
             # dx[M, in] = dy[M, out] * W ; W as the "B" operand is [in, out]-logical
-            dx = gemm(dy2, w, b_mn=not ctx.w_is_kn).view(ctx.x_shape)
+            dx = gemm(dy2, w, b_mn=not ctx.w_is_kn)
         if ctx.needs_input_grad[1]:
             if ctx.w_is_kn:   # dW[in, out] = x^T dy
                 a, b = x2, dy2
@@ -100,5 +97,9 @@ def linear_ref(x, w, bias=None, w_is_kn=False):
 def linear(x: torch.Tensor, w: torch.Tensor, bias=None, w_is_kn: bool = False) -> torch.Tensor:
     """y = x W^T + b for ``w`` [out, in]; with ``w_is_kn`` the weight is [in, out] (Conv1D layout)."""
     if use_kernels(x):
-        return _Linear.apply(x, w, bias, w_is_kn)
+        x2 = x.reshape(-1, x.shape[-1])
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        y = _Linear.apply(x2, w, bias, w_is_kn)
+        return y if x.dim() == 2 else y.view(*x.shape[:-1], y.shape[-1])
     return linear_ref(x, w, bias, w_is_kn)
