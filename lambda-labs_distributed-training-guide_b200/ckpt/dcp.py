@@ -1,0 +1,124 @@
+"""Sharded checkpoints in the ``torch.distributed.checkpoint`` (DCP) directory layout.
+
+The reference writes ``exp_dir/checkpoint/`` (``.metadata`` + ``__<rank>_<n>.distcp``) with keys
+``model.<fqn>`` and ``optimizer.*`` from every rank (``04-fully-sharded-data-parallel/train_llm.py:122,
+249-263``; Stateful objects in ``06-tensor-parallel/train_llm.py:177-189,283-295``). Here every rank
+contributes a dim-0 chunk of each HF-named parameter (and of its two AdamW moments) as a ``DTensor``
+over the data-parallel mesh, so the files are readable by stock DCP tooling (``dcp_to_torch_save`` ...)
+and by the reference's own ``load`` with the same FQNs. Flat-shard boundaries do not fall on parameter
+rows, so saving / loading re-chunks one unit at a time through the strategy's collectives.
+"""
+from __future__ import annotations
+
+from pathlib import Path
+from typing import Dict
+
+import torch
+import torch.distributed as dist
+
+
+def _chunk_bounds(rows: int, world: int, rank: int):
+    per = (rows + world - 1) // world
+    lo = min(rank * per, rows)
+    return lo, min(lo + per, rows)
+
+
+def _as_dtensor(full: torch.Tensor, mesh, rank: int, world: int):
+    """Local dim-0 chunk of ``full`` wrapped as a DTensor of the global shape."""
+    from torch.distributed.tensor import DTensor, Shard
+
+    if full.dim() == 0:
+        full = full.reshape(1)
+    lo, hi = _chunk_bounds(full.shape[0], world, rank)
+    local = full[lo:hi].detach().clone().contiguous()
+    return DTensor.from_local(local, mesh, [Shard(0)], run_check=False, shape=full.shape,
+                              stride=full.contiguous().stride())
+
+
+def _chunk(full: torch.Tensor, mesh, rank: int, world: int):
+    if world == 1:
+        return full.detach().clone()
+    return _as_dtensor(full, mesh, rank, world)
+
+
+def build_sharded_state(strategy, mesh):
+    """Walk the strategy one unit at a time and keep only this rank's dim-0 chunk of every HF-named
+    tensor (parameters and AdamW moments), so the full model never has to exist on one rank."""
+    rank, world = strategy.rank, strategy.world_size
+    state = {"model": {}, "optimizer": {"state": {}, "param_groups": strategy.optimizer_param_groups()}}
+    for i in range(strategy.num_units()):
+        for kind in ("param", "exp_avg", "exp_avg_sq"):
+            for name, full in strategy.unit_named_full(i, kind).items():
+                if kind == "param":
+                    state["model"][name] = _chunk(full, mesh, rank, world)
+                else:
+                    st = state["optimizer"]["state"].setdefault(name, {"step": torch.tensor(float(strategy.optimizer_step_count()))})
+                    st[kind] = _chunk(full, mesh, rank, world)
+    return state
+
+
+def save_sharded(exp_dir: Path, strategy, state: dict = None, lr_scheduler=None):
+    """Every rank calls this (flavour C/D). Rank 0 also writes ``lr_scheduler.pt`` and ``state.json``."""
+    from torch.distributed.checkpoint import save
+
+    from .state import save_state
+
+    exp_dir = Path(exp_dir)
+    rank, world = strategy.rank, strategy.world_size
+    strategy.barrier()
+    sharded = build_sharded_state(strategy, _mesh(strategy))
+    save(sharded, checkpoint_id=exp_dir / "checkpoint", no_dist=not dist.is_initialized())
+    if rank == 0:
+        if lr_scheduler is not None:
+            torch.save(lr_scheduler.state_dict(), exp_dir / "lr_scheduler.pt")
+        if state is not None:
+            save_state(exp_dir, state)
+    strategy.barrier()
+
+
+def load_sharded(exp_dir: Path, strategy):
+    """Inverse of :func:`save_sharded`: DCP fills the chunk containers in place, then the strategy folds
+    them back into its own sharding unit by unit."""
+    from torch.distributed.checkpoint import load
+
+    exp_dir = Path(exp_dir)
+    sharded = build_sharded_state(strategy, _mesh(strategy))
+    load(sharded, checkpoint_id=exp_dir / "checkpoint", no_dist=not dist.is_initialized())
+    opt_state = sharded["optimizer"]["state"]
+    for i in range(strategy.num_units()):
+        for kind in ("param", "exp_avg", "exp_avg_sq"):
+            names = list(strategy.unit_named_full(i, kind, names_only=True))
+            if kind == "param":
+                tensors = {n: _to_full(sharded["model"][n]) for n in names}
+            else:
+                tensors = {n: _to_full(opt_state[n][kind]) for n in names}
+            strategy.unit_store_named(i, kind, tensors)
+    steps = [float(_to_full(st["step"])) for st in opt_state.values() if "step" in st]
+    strategy.set_optimizer_step_count(int(steps[0]) if steps else 0)
+    strategy.barrier()
+
+
+def _to_full(t):
+    try:
+        from torch.distributed.tensor import DTensor
+
+        if isinstance(t, DTensor):
+            return t.full_tensor()
+    except ImportError:
+        pass
+    return t
+
+
+_MESH = {}
+
+
+def _mesh(strategy):
+    world = strategy.world_size
+    if world == 1:
+        return None
+    key = (strategy.device.type, world)
+    if key not in _MESH:
+        from torch.distributed.device_mesh import init_device_mesh
+
+        _MESH[key] = init_device_mesh(strategy.device.type, (world,), mesh_dim_names=("dp",))
+    return _MESH[key]

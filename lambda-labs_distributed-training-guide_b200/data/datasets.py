@@ -1,0 +1,133 @@
+"""Training data: synthetic fixed-length tokens (offline benchmarks) and the reference's text pipeline.
+
+``load_and_preprocess_data`` follows the reference function of the same name
+(``01-single-gpu/train_llm.py:194-247``): tokenize the ``text`` column (or the first column), concatenate
+everything, cut into ``seq_length`` blocks dropping the remainder, ``labels = input_ids``; ``seq_length``
+falls back to the tokenizer's ``model_max_length`` and is clamped to ``min(1024, max_position_embeddings)``
+when it exceeds the model's positions (``:218-220``).
+
+Dataset names:
+  ``synthetic`` / ``synthetic:<n_samples>``  random tokens of the model's vocabulary (no files needed)
+  a local ``.txt`` / ``.jsonl`` / directory    read with ``datasets`` when importable, else plain Python
+  anything else                                ``datasets.load_dataset(name)`` (needs a populated HF cache)
+"""
+from __future__ import annotations
+
+import json
+import multiprocessing
+import os
+from itertools import chain
+from pathlib import Path
+
+import torch
+from torch.utils.data import Dataset
+
+
+class SyntheticTokens(Dataset):
+    """Deterministic random token rows; sample ``i`` depends only on ``(seed, i)``."""
+
+    def __init__(self, vocab_size: int, seq_length: int, n_samples: int = 4096, seed: int = 0):
+        self.vocab_size, self.seq_length, self.n, self.seed = vocab_size, seq_length, n_samples, seed
+
+    def __len__(self):
+        return self.n
+
+    def __getitem__(self, i):
+        g = torch.Generator().manual_seed(self.seed * 1_000_003 + int(i))
+        ids = torch.randint(0, self.vocab_size, (self.seq_length,), generator=g)
+        return {"input_ids": ids, "attention_mask": torch.ones_like(ids), "labels": ids.clone()}
+
+
+class TokenBlocks(Dataset):
+    """Fixed-length blocks cut from one long token stream."""
+
+    def __init__(self, tokens: torch.Tensor, seq_length: int):
+        n = (tokens.numel() // seq_length) * seq_length
+        self.blocks = tokens[:n].view(-1, seq_length)
+
+    def __len__(self):
+        return self.blocks.shape[0]
+
+    def __getitem__(self, i):
+        ids = self.blocks[i]
+        return {"input_ids": ids, "attention_mask": torch.ones_like(ids), "labels": ids.clone()}
+
+
+class ByteTokenizer:
+    """Offline fallback when no HF tokenizer files are available: UTF-8 bytes + EOS."""
+
+    model_max_length = 1024
+    eos_token_id = 256
+    vocab_size = 257
+
+    def __call__(self, texts):
+        if isinstance(texts, str):
+            texts = [texts]
+        return {"input_ids": [list(t.encode("utf-8")) + [self.eos_token_id] for t in texts]}
+
+
+def resolve_seq_length(requested, tokenizer_max, max_position_embeddings):
+    seq_length = requested or tokenizer_max
+    if seq_length > max_position_embeddings:
+        seq_length = min(1024, max_position_embeddings)
+    return seq_length
+
+
+def _load_tokenizer(model_name: str):
+    try:
+        from transformers import AutoTokenizer
+
+        return AutoTokenizer.from_pretrained(model_name, local_files_only=not os.environ.get("HF_ALLOW_NETWORK"))
+    except Exception:
+        return ByteTokenizer()
+
+
+def _read_local_texts(path: Path):
+    files = sorted(path.rglob("*")) if path.is_dir() else [path]
+    for f in files:
+        if f.suffix == ".txt":
+            yield f.read_text()
+        elif f.suffix in (".jsonl", ".json"):
+            for line in f.read_text().splitlines():
+                if line.strip():
+                    row = json.loads(line)
+                    yield row["text"] if "text" in row else next(iter(row.values()))
+
+
+def group_texts(examples: dict, seq_length: int) -> dict:
+    """Concatenate then chunk (the reference's inner ``group_texts``, ``01-.../train_llm.py:223-236``)."""
+    concatenated = {k: list(chain(*examples[k])) for k in examples.keys()}
+    total_length = len(concatenated[list(examples.keys())[0]])
+    if total_length > seq_length:
+        total_length = (total_length // seq_length) * seq_length
+    result = {k: [t[i:i + seq_length] for i in range(0, total_length, seq_length)] for k, t in concatenated.items()}
+    result["labels"] = result["input_ids"].copy()
+    return result
+
+
+def load_and_preprocess_data(dataset_name: str, model_name: str, config, seq_length=None, seed: int = 0):
+    """Returns a map-style dataset of ``{"input_ids", "attention_mask", "labels"}`` rows."""
+    if dataset_name.startswith("synthetic"):
+        n = int(dataset_name.split(":")[1]) if ":" in dataset_name else 4096
+        sl = resolve_seq_length(seq_length, 1024, config.max_position_embeddings)
+        return SyntheticTokens(config.vocab_size, sl, n, seed)
+    tokenizer = _load_tokenizer(model_name)
+    sl = resolve_seq_length(seq_length, min(getattr(tokenizer, "model_max_length", 1024), 1 << 20),
+                            config.max_position_embeddings)
+    p = Path(dataset_name)
+    if p.exists():
+        ids = []
+        for text in _read_local_texts(p):
+            ids.extend(tokenizer([text])["input_ids"][0])
+        return TokenBlocks(torch.tensor(ids, dtype=torch.long), sl)
+    import datasets  # hub / cache datasets, exactly the reference flow
+
+    data = datasets.load_dataset(dataset_name, trust_remote_code=True)
+    column_names = data["train"].column_names
+    text_column = "text" if "text" in column_names else column_names[0]
+    tokenized = data.map(lambda ex: tokenizer(ex[text_column]), batched=True, remove_columns=column_names,
+                         num_proc=multiprocessing.cpu_count(), load_from_cache_file=True,
+                         desc="Running tokenizer on dataset")
+    lm = tokenized.map(lambda ex: group_texts(ex, sl), batched=True, num_proc=multiprocessing.cpu_count(),
+                       load_from_cache_file=True, desc=f"Grouping texts in chunks of {sl}")
+    return lm["train"].with_format("torch")

@@ -94,3 +94,65 @@ class Strategy:
 
     def load_model_state_dict(self, sd):
         self.model.load_hf_state_dict(sd)
+
+    # ---- checkpoint surface (ckpt/dcp.py walks units through these) --------------------------------
+    def num_units(self) -> int:
+        return len(self.units)
+
+    def optimizer_param_groups(self):
+        g = {k: v for k, v in self.optimizer.param_groups[0].items() if k != "params"}
+        g["betas"] = list(g["betas"])
+        return [g]
+
+    def optimizer_step_count(self) -> int:
+        return self.optimizer._step
+
+    def set_optimizer_step_count(self, n: int):
+        self.optimizer._step = n
+
+    def _unit_full_flat(self, i: int, kind: str) -> torch.Tensor:
+        """Full (unsharded) flat tensor of unit ``i``: parameters or one AdamW moment."""
+        if kind == "param":
+            return self.units[i].flat_param
+        return (self.optimizer.exp_avg if kind == "exp_avg" else self.optimizer.exp_avg_sq)[i]
+
+    def _unit_store_flat(self, i: int, kind: str, full: torch.Tensor):
+        self._unit_full_flat(i, kind).copy_(full)
+
+    def _named_views(self, i: int, flat: torch.Tensor):
+        """HF-named views of a flat tensor laid out like unit ``i``."""
+        u = self.units[i]
+        saved = [p.data for p in u.params]
+        for p, o in zip(u.params, u.offsets):
+            p.data = flat[o:o + p.numel()].view(p.shape)
+        lo = flat.data_ptr()
+        hi = lo + flat.numel() * flat.element_size()
+        out = {}
+        for k, v in self.model.hf_state_dict().items():
+            if lo <= v.data_ptr() < hi and not (k == "lm_head.weight" and self.cfg.tie_word_embeddings):
+                out[k] = v
+        for p, d in zip(u.params, saved):
+            p.data = d
+        return out
+
+    @torch.no_grad()
+    def unit_named_full(self, i: int, kind: str, names_only: bool = False):
+        if names_only:
+            u = self.units[i]
+            probe = torch.empty(u.numel, dtype=self.dtype, device="meta") if False else None
+            return self._named_views(i, self._names_probe(i)).keys()
+        return self._named_views(i, self._unit_full_flat(i, kind))
+
+    def _names_probe(self, i: int):
+        u = self.units[i]
+        if not hasattr(self, "_probe") or self._probe.numel() < u.numel:
+            self._probe = torch.empty(max(x.numel for x in self.units), dtype=self.dtype, device=self.device)
+        return self._probe[:u.numel]
+
+    @torch.no_grad()
+    def unit_store_named(self, i: int, kind: str, tensors):
+        u = self.units[i]
+        flat = torch.zeros(u.numel, dtype=self.dtype, device=self.device)
+        for name, view in self._named_views(i, flat).items():
+            view.copy_(tensors[name].to(device=self.device, dtype=self.dtype))
+        self._unit_store_flat(i, kind, flat)

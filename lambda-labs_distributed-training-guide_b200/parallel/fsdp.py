@@ -367,6 +367,38 @@ class FSDP(Strategy):
     def model_state_dict(self):
         return self.gather_full_state_dict()
 
+    # ---- checkpoint surface --------------------------------------------------------------------------
+    def _shard_of(self, i, kind):
+        if kind == "param":
+            return self.shard_param[i]
+        return (self.optimizer.exp_avg if kind == "exp_avg" else self.optimizer.exp_avg_sq)[i]
+
+    def _unit_full_flat(self, i, kind):
+        if self.is_cuda:
+            torch.cuda.synchronize(self.device)
+        shard = self._shard_of(i, kind)
+        if self.resident:
+            return shard
+        u = self.units[i]
+        n = u.numel // self.W
+        full = torch.empty(u.numel, dtype=self.dtype, device=self.device)
+        mine = shard.to(self.device)
+        if self.W > 1:
+            self.comm.all_gather(full, mine)
+        else:
+            full.copy_(mine)
+        if self.is_cuda:
+            torch.cuda.synchronize(self.device)
+        return full
+
+    def _unit_store_flat(self, i, kind, full):
+        shard = self._shard_of(i, kind)
+        if self.resident:
+            shard.copy_(full)
+            return
+        n = self.units[i].numel // self.W
+        shard.copy_(full[self.R * n:(self.R + 1) * n])
+
 
 class _Layout(FlatUnit):
     """A FlatUnit whose storage is transient: ``repoint``/``assign_grads`` attach it to pool buffers."""
