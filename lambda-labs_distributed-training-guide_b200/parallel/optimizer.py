@@ -50,6 +50,7 @@ class FlatAdamW(torch.optim.Optimizer):
     def begin_step(self):
         """Advance the step counter once per optimizer step (bias correction is shared by all units)."""
         self._step += 1
+        self._opt_called = True  # lets torch LR schedulers see that an optimizer step happened
 
     def step_unit(self, i: int, max_blocks: int = 0, grad: Optional[torch.Tensor] = None,
                   param: Optional[torch.Tensor] = None):

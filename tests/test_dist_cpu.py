@@ -1,0 +1,171 @@
+"""Multi-process (gloo, world 2) checks of the host-side parallel logic on CPU: DDP (+ZeRO-1), FSDP
+(+offload, +activation checkpointing, +no_sync) must reproduce the single-process loss curve on the
+same global batch; DCP sharded checkpoints must round-trip; rank-ordering helpers must order."""
+import os
+import socket
+import tempfile
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, fn_name, args, ret):
+    fn = globals()[fn_name]
+    _worker_impl(rank, world, port, lambda r, w: fn(r, w, *args), ret)
+
+
+def _worker_impl(rank, world, port, fn, ret):
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        ret[rank] = fn(rank, world)
+    finally:
+        dist.destroy_process_group()
+
+
+def run_dist(fn_name, *args, world=2):
+    ret = mp.Manager().dict()
+    mp.spawn(_worker, args=(world, _free_port(), fn_name, args, ret), nprocs=world, join=True)
+    return [ret[r] for r in range(world)]
+
+
+def _batches(cfg, n, B, S, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    return [torch.randint(0, cfg.vocab_size, (B, S), generator=g) for _ in range(n)]
+
+
+def _single_losses(strategy, kw, steps=3):
+    from b200train.models import load_config
+    from b200train.parallel import make_strategy
+
+    cfg = load_config("llama-tiny")
+    eng = make_strategy(strategy, cfg, "cpu", lr=1e-3, dtype=torch.float32, **kw)
+    out = []
+    for ids in _batches(cfg, steps, 4, 32):
+        out.append(eng.train_step({"input_ids": ids, "labels": ids}).item())
+    return out
+
+
+def w_losses(rank, world, strategy, kw, steps):
+    from b200train.models import load_config
+    from b200train.parallel import make_strategy
+
+    cfg = load_config("llama-tiny")
+    eng = make_strategy(strategy, cfg, "cpu", lr=1e-3, dtype=torch.float32, **kw)
+    out = []
+    for ids in _batches(cfg, steps, 4, 32):
+        mine = ids[rank * 2:(rank + 1) * 2]
+        loss = eng.train_step({"input_ids": mine, "labels": mine})
+        t = loss.detach().clone()
+        dist.all_reduce(t)
+        out.append((t / world).item())
+    return out
+
+
+def _dist_losses(strategy, kw, steps=3):
+    return run_dist("w_losses", strategy, kw, steps)[0]
+
+
+@pytest.mark.parametrize("strategy,kw", [
+    ("ddp", dict(zero1=False)),
+    ("ddp", dict(zero1=True)),
+    ("fsdp", dict()),
+    ("fsdp", dict(cpu_offload=True)),
+    ("fsdp", dict(activation_checkpointing=True, reshard_after_forward=False)),
+])
+def test_matches_single_process(strategy, kw):
+    ref = _single_losses(strategy, {k: v for k, v in kw.items()})
+    got = _dist_losses(strategy, kw)
+    for a, b in zip(ref, got):
+        assert abs(a - b) < 2e-3, (ref, got)
+
+
+def w_no_sync(rank, world):
+    if True:
+        from b200train.models import load_config
+        from b200train.parallel import make_strategy
+
+        cfg = load_config("llama-tiny")
+        a = make_strategy("fsdp", cfg, "cpu", lr=1e-3, dtype=torch.float32)
+        b = make_strategy("fsdp", cfg, "cpu", lr=1e-3, dtype=torch.float32)
+        ids = _batches(cfg, 1, 8, 32)[0][rank * 4:(rank + 1) * 4]
+        # a: one step on 4 rows; b: two micro-steps of 2 rows with no_sync on the first
+        a.train_step({"input_ids": ids, "labels": ids})
+        b.zero_grad()
+        with b.no_sync():
+            out = b.forward({"input_ids": ids[:2], "labels": ids[:2]})
+            b.backward(out.loss / 2)
+        out = b.forward({"input_ids": ids[2:], "labels": ids[2:]})
+        b.backward(out.loss / 2)
+        b.optimizer_step()
+        la = a.train_step({"input_ids": ids, "labels": ids}).item()
+        lb = b.train_step({"input_ids": ids, "labels": ids}).item()
+        return la, lb
+
+
+def test_fsdp_no_sync_accumulation():
+    la, lb = run_dist("w_no_sync")[0]
+    assert abs(la - lb) < 2e-3, (la, lb)
+
+
+def w_dcp(rank, world, tmp):
+    if True:
+        from pathlib import Path
+
+        from b200train.ckpt.dcp import load_sharded, save_sharded
+        from b200train.models import load_config
+        from b200train.parallel import make_strategy
+
+        cfg = load_config("llama-tiny")
+        eng = make_strategy("fsdp", cfg, "cpu", lr=1e-3, dtype=torch.float32)
+        ids = _batches(cfg, 1, 4, 32)[0][rank * 2:(rank + 1) * 2]
+        for _ in range(2):
+            eng.train_step({"input_ids": ids, "labels": ids})
+        save_sharded(Path(tmp), eng, state={"epoch": 0, "global_step": 2, "epoch_step": 2, "running_loss": 0.0},
+                     lr_scheduler=eng.lr_scheduler)
+        nxt = eng.train_step({"input_ids": ids, "labels": ids}).item()
+        eng2 = make_strategy("fsdp", cfg, "cpu", lr=1e-3, dtype=torch.float32, seed=7)
+        load_sharded(Path(tmp), eng2)
+        eng2.lr_scheduler.load_state_dict(torch.load(Path(tmp) / "lr_scheduler.pt"))
+        got = eng2.train_step({"input_ids": ids, "labels": ids}).item()
+        files = sorted(p.name for p in (Path(tmp) / "checkpoint").iterdir())
+        return nxt, got, files
+
+
+def test_dcp_sharded_roundtrip():
+    tmp = tempfile.mkdtemp()
+    nxt, got, files = run_dist("w_dcp", tmp)[0]
+    assert abs(nxt - got) < 1e-5, (nxt, got)
+    assert ".metadata" in files and "__0_0.distcp" in files and "__1_0.distcp" in files, files
+    assert os.path.exists(os.path.join(tmp, "state.json"))
+
+
+def w_order(rank, world, tmp):
+    if True:
+        import time
+
+        from b200train.cli.train_llm import rank0_first
+
+        with rank0_first():
+            if rank == 0:
+                time.sleep(0.3)
+            with open(os.path.join(tmp, "order.txt"), "a") as f:
+                f.write(f"{rank}\n")
+        return True
+
+
+def test_rank_ordered_runs_first_rank_first():
+    tmp = tempfile.mkdtemp()
+    run_dist("w_order", tmp)
+    assert open(os.path.join(tmp, "order.txt")).read().split()[0] == "0"
