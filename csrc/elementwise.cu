@@ -6,6 +6,7 @@
 // code (reference: 01-single-gpu/train_llm.py:65,140-149).
 #include "common.cuh"
 #include <math.h>
+#include <mutex>
 
 namespace b2 {
 
@@ -876,6 +877,88 @@ int b2_add(void* out, const void* a, const void* b, size_t n, cudaStream_t strea
   if (n == 0) return 0;
   add_kernel<<<ew_grid(n / 8, 256), 256, 0, stream>>>((bf16*)out, (const bf16*)a, (const bf16*)b,
                                                       n / 8);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// RMSNorm backward for callers that cannot allocate device memory.
+//
+// b2_rmsnorm_bwd needs an fp32 scratch buffer that its caller allocates. Some callers have no way to
+// do that: a plain-C plugin loaded into a host application that has already handed all remaining
+// device memory to its own pool (so cudaMalloc fails and the pool's allocator is not reachable from
+// here), or a latency-critical section where the implicit device-wide synchronisation of cudaMalloc
+// is not acceptable. For them the scratch lives in the library image itself, in the fixed-size array
+// below. Every GPU that loads libb200train.so holds these 32 MiB from load until process exit.
+// ------------------------------------------------------------------------------------------------
+namespace b2 {
+constexpr size_t kStaticScratchFloats = size_t(8) << 20;  // 8 Mi floats = 32 MiB
+static __device__ __align__(256) float g_rmsnorm_static_scratch[kStaticScratchFloats];
+
+// Host code must not pass `g_rmsnorm_static_scratch` to a kernel: in host code that name is only a
+// host-side handle for the symbol, not a device address. The device address is looked up once per
+// device (with that device current) and cached here.
+constexpr int kMaxDevices = 64;
+static float* g_static_scratch_ptr[kMaxDevices] = {};
+static std::mutex g_static_scratch_mutex;
+
+static int static_scratch_for_current_device(float** out) {
+  int dev = -1;
+  B2_CUDA_CHECK(cudaGetDevice(&dev));
+  B2_REQUIRE(dev >= 0 && dev < kMaxDevices, "static scratch: device index %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_static_scratch_mutex);
+  if (g_static_scratch_ptr[dev] == nullptr) {
+    float* p = nullptr;
+    B2_CUDA_CHECK(cudaGetSymbolAddress((void**)&p, g_rmsnorm_static_scratch));
+    B2_REQUIRE(p != nullptr, "static scratch: cudaGetSymbolAddress returned a null pointer");
+    g_static_scratch_ptr[dev] = p;
+  }
+  *out = g_static_scratch_ptr[dev];
+  return 0;
+}
+}  // namespace b2
+
+extern "C" {
+
+// Largest scratch (in floats) the no-allocation entry point can serve: partial_rows(T) * H must fit.
+size_t b2_rmsnorm_bwd_static_capacity(void) { return b2::kStaticScratchFloats; }
+
+// Same computation, same launch shape and same results as b2_rmsnorm_bwd, but without a scratch
+// argument and without any allocation (no cudaMalloc / cudaFree / allocating library call): the fp32
+// partial sums go to the library's built-in 32 MiB device array.
+//   * Limit: b2_rmsnorm_bwd_partial_rows(T) * H <= b2_rmsnorm_bwd_static_capacity() floats; larger
+//     problems are refused with an error (use b2_rmsnorm_bwd with your own scratch instead).
+//   * The first call on each device looks up the array's device address (cudaGetSymbolAddress); make
+//     that first call during start-up, before any stream capture begins.
+//   * All calls on one device share the one array. Nothing in it needs to be zero on entry: each call
+//     overwrites every element it later reads, so leftovers of the previous call are harmless. Two
+//     calls that overlap on the GPU (different streams, no ordering between them) would race on the
+//     array and corrupt each other's dw; keep calls on one stream or order them with events.
+int b2_rmsnorm_bwd_static(void* dx, void* dw, const void* dy, const void* h, const void* w,
+                          const float* rstd, const void* dres, int T, int H, int accumulate_dw,
+                          cudaStream_t stream) {
+  B2_REQUIRE(H % 8 == 0 && H <= kNormThreads * kNormMaxVec * 8, "rmsnorm: unsupported H=%d", H);
+  if (T == 0) return 0;
+  const int nb = b2_rmsnorm_bwd_partial_rows(T);
+  B2_REQUIRE((size_t)nb * (size_t)H <= kStaticScratchFloats,
+             "b2_rmsnorm_bwd_static: needs %zu scratch floats (partial rows %d x H %d) but the built-in "
+             "array holds %zu; call b2_rmsnorm_bwd with caller-provided scratch instead",
+             (size_t)nb * (size_t)H, nb, H, (size_t)kStaticScratchFloats);
+  float* partial = nullptr;
+  if (int rc = static_scratch_for_current_device(&partial)) return rc;
+#define B2_RMS_BWD(MV)                                                                     \
+  rmsnorm_bwd_kernel<MV><<<nb, kNormThreads, 0, stream>>>(                                 \
+      (bf16*)dx, partial, (const bf16*)dy, (const bf16*)h, (const bf16*)w, rstd,           \
+      (const bf16*)dres, T, H)
+  if (H <= kNormThreads * 8 * 2) B2_RMS_BWD(2);
+  else if (H <= kNormThreads * 8 * 4) B2_RMS_BWD(4);
+  else B2_RMS_BWD(8);
+#undef B2_RMS_BWD
+  B2_CUDA_CHECK(cudaGetLastError());
+  fold_partials_kernel<<<(H + 255) / 256, 256, 0, stream>>>((bf16*)dw, partial, nb, H,
+                                                            accumulate_dw);
   B2_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

@@ -61,6 +61,18 @@ int b2_rmsnorm_fwd(void* y, float* rstd, void* h_out, const void* x, const void*
 int b2_rmsnorm_bwd(void* dx, void* dw, float* partial, const void* dy, const void* h,
                    const void* w, const float* rstd, const void* dres, int T, int H,
                    int accumulate_dw, b2_stream_t stream);
+/* RMSNorm backward with no scratch argument and no allocation: the fp32 partial sums go to a fixed
+ * 32 MiB device array inside the library (held by every GPU that loads it, until exit). For callers
+ * that cannot allocate: plugins in an application that has pooled all remaining device memory, or
+ * latency-critical code that cannot take cudaMalloc's device-wide sync. Same results as
+ * b2_rmsnorm_bwd. Refuses problems with b2_rmsnorm_bwd_partial_rows(T) * H above
+ * b2_rmsnorm_bwd_static_capacity() floats. The first call on a device resolves the array's address
+ * (make it before any stream capture). All calls share the array: overlapping calls on one GPU race.
+ * No counterpart in the reference (it never manages scratch memory itself). */
+size_t b2_rmsnorm_bwd_static_capacity(void);
+int b2_rmsnorm_bwd_static(void* dx, void* dw, const void* dy, const void* h, const void* w,
+                          const float* rstd, const void* dres, int T, int H, int accumulate_dw,
+                          b2_stream_t stream);
 int b2_layernorm_fwd(void* y, float* mean, float* rstd, void* h_out, const void* x,
                      const void* res, const void* w, const void* b, int T, int H, float eps,
                      b2_stream_t stream);
