@@ -87,7 +87,7 @@ class FSDP(Strategy):
         tied = cfg.tie_word_embeddings
 
         # ---- model skeleton on the meta device; units define the flat layout -------------------
-        self.model = build_model(cfg, dtype=dtype, device="meta", init=False)
+        self.model = self._build_meta_model(cfg, dtype)
         self.units: List[_Layout] = [_Layout(name, params, self.W) for name, params in self.model.units()]
         n_units = len(self.units)
         max_numel = max(u.numel for u in self.units)
@@ -107,7 +107,7 @@ class FSDP(Strategy):
             n = u.numel // self.W
             full = (torch.empty(u.numel, dtype=dtype, device=self.device) if self.resident
                     else self.param_pool.bufs[0][:u.numel])
-            swap.update(u.materialize(self.model, full, seed, ui, cfg))
+            swap.update(u.materialize(self.model, full, self._init_seed(seed), ui, cfg))
             if self.resident:
                 self.shard_param.append(full)
                 self.shard_grad.append(torch.zeros(u.numel, dtype=dtype, device=self.device))
@@ -139,6 +139,16 @@ class FSDP(Strategy):
                                    pin=self.is_cuda and cpu_offload)
         self.lr_scheduler = make_lr_scheduler(self.optimizer, lr)
         self.comm.barrier()
+
+    # ---- extension points (the 2D strategy plugs a tensor-parallel model in here) ----------------------
+    def _build_meta_model(self, cfg, dtype):
+        return build_model(cfg, dtype=dtype, device="meta", init=False)
+
+    def _init_seed(self, seed):
+        return seed
+
+    def pre_reduce(self, i):
+        """Called when unit ``i``'s gradients are complete, before they are reduced over this group."""
 
     # ------------------------------------------------------------------------------------------------
     @property
@@ -251,6 +261,7 @@ class FSDP(Strategy):
     def post_backward(self, i):
         u = self.units[i]
         u.finalize_grads()
+        self.pre_reduce(i)
         if self.resident:
             if self.fuse_optimizer and self.sync_grads:
                 self._fused_step(i, self._record())
@@ -453,6 +464,9 @@ class _Layout(FlatUnit):
             q = torch.nn.Parameter(torch.empty(0, dtype=full.dtype, device=full.device), requires_grad=True)
             q.data = full[o:o + p.numel()].view(p.shape)
             q._b2_unit = self
+            for k, v in vars(p).items():   # carry strategy tags (e.g. tp-replicated) over to the real parameter
+                if k.startswith("_b2_tp"):
+                    setattr(q, k, v)
             swap[id(p)] = q
             new_params.append(q)
         self.params = new_params
