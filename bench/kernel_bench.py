@@ -172,7 +172,10 @@ def bench_elementwise(results):
 if __name__ == "__main__":
     quick = "--quick" in sys.argv
     results = {"peaks": PEAKS, "gemm": {}, "attention": {}, "elementwise": {}}
-    for fn in (bench_gemm, bench_attention, bench_elementwise):
+    fns = (bench_gemm, bench_attention, bench_elementwise)
+    if "--no-gemm" in sys.argv:
+        fns = fns[1:]
+    for fn in fns:
         try:
             fn(results, quick) if fn is bench_gemm else fn(results)
         except Exception as e:

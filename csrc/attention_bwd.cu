@@ -7,14 +7,14 @@
 //     P    = exp2(S*c - lse), dS = P * (dP - delta) * scale        (softmax warpgroup, registers)
 //     dV^T += dO_i^T P             [D x 64]     TMEM accumulator over all steps
 //     dK^T += Q_i^T  dS            [D x 64]     TMEM accumulator over all steps
-//     dQ_i  = dS K_j               [128 x D]    TMEM -> fp32 red.global.add into dq_accum
+//     dQ_i  = dS K_j               [128 x D]    TMEM -> smem -> cp.reduce.async.bulk.tensor (fp32 add) into dq_accum
 // dV and dK are accumulated transposed so that every MMA has M = 128 (full tensor-core rate); the same
 // 128B-swizzled smem tile serves as a K-major operand ([rows, 64] atoms) and as the MN-major operand of
 // the transposed product, so Q, dO, K, P and dS are each stored once.
 //   warp 0     TMA producer (K_j, V_j once; 2-stage ring of Q_i / dO_i)
 //   warp 1     MMA issuer
 //   warps 2-5  softmax warpgroup (one thread per query row)
-//   warps 6-9  dQ warpgroup (TMEM -> red.global.add.v4.f32), also drains dK^T at the end
+//   warps 6-9  dQ warpgroup (TMEM -> swizzled smem -> TMA reduce-add into dq_accum), drains dK^T at the end
 //
 // Replaces flash_attn_2_cuda's backward (reference: 05-training-llama-405b/train_llm.py:87 +
 // loss.backward() at :237).
@@ -35,7 +35,8 @@ struct AttnBwdSmem {
   static constexpr int kDO = QB * D * 2;
   static constexpr int kP = QB * KB * 2;   // 16 KB
   static constexpr int kDS = QB * KB * 2;  // 16 KB
-  static constexpr int kTotal = kK + kV + 2 * (kQ + kDO) + 2 * (kP + kDS) + 256 + 1024;
+  static constexpr int kDQStage = QB * 32 * 4;  // 128 rows x 32 fp32 columns = 16 KB
+  static constexpr int kTotal = kK + kV + 2 * (kQ + kDO) + (kP + kDS) + 2 * kDQStage + 256 + 1024;
 };
 
 struct AttnBwdParams {
@@ -46,7 +47,7 @@ struct AttnBwdParams {
   const float* delta;  // [Hq, T]
   const int* cu_seqlens;
   int dk_stride, dv_stride;
-  int T, Hq, Hkv;
+  int T, Hq, Hkv, ndocs;
   float scale, scale_log2;
   int causal;
 };
@@ -90,17 +91,21 @@ __global__ void attn_bwd_convert_dq_kernel(__nv_bfloat16* __restrict__ dq,
   }
 }
 
-__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
-  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c),
-               "f"(d)
-               : "memory");
+// smem tile -> global tensor, element-wise fp32 add performed by the TMA unit / L2
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* m, const void* src, int c0,
+                                                  int c1) {
+  asm volatile(
+      "cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];" ::
+          "l"(reinterpret_cast<uint64_t>(m)),
+      "r"(smem_u32(src)), "r"(c0), "r"(c1)
+      : "memory");
 }
 
 template <int D>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
-                AttnBwdParams p) {
+                const __grid_constant__ CUtensorMap tmDQ, AttnBwdParams p) {
   using SM = AttnBwdSmem<D>;
   constexpr int kAtoms = D / 64;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -110,28 +115,32 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   uint8_t* sV = sK + SM::kK;
   uint8_t* sQ = sV + SM::kV;            // 2 stages
   uint8_t* sDO = sQ + 2 * SM::kQ;       // 2 stages
-  uint8_t* sP = sDO + 2 * SM::kDO;      // 2 buffers
-  uint8_t* sDS = sP + 2 * SM::kP;       // 2 buffers
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sDS + 2 * SM::kDS);
+  uint8_t* sP = sDO + 2 * SM::kDO;
+  uint8_t* sDS = sP + SM::kP;
+  uint8_t* sDQ = sDS + SM::kDS;         // 2 staging buffers for the TMA reduce-add of dQ
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sDQ + 2 * SM::kDQStage);
   uint64_t* kv_full = bars;            // 1
   uint64_t* qdo_full = bars + 1;       // 2
   uint64_t* qdo_empty = bars + 3;      // 2
   uint64_t* sdp_full = bars + 5;       // 2
   uint64_t* sdp_free = bars + 7;       // 2
-  uint64_t* pds_full = bars + 9;       // 2
-  uint64_t* pds_empty = bars + 11;     // 2
+  uint64_t* pds_full = bars + 9;       // 1 (+1 unused)
+  uint64_t* pds_empty = bars + 11;     // 1 (+1 unused)
   uint64_t* dq_full = bars + 13;       // 1
   uint64_t* dq_free = bars + 14;       // 1
   uint64_t* done_bar = bars + 15;      // 1
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
 
   const int warp = threadIdx.x >> 5;
-  const int doc = blockIdx.z;
-  const int kvh = blockIdx.y;
+  // linear block id -> (kv block, kv head, document) with the kv block slowest: causal blocks with a
+  // small index do the most work and are launched first
+  const int per_kb = p.Hkv * p.ndocs;
+  const int jb = (int)blockIdx.x / per_kb;
+  const int kvh = ((int)blockIdx.x % per_kb) % p.Hkv;
+  const int doc = ((int)blockIdx.x % per_kb) / p.Hkv;
   const int doc_start = p.cu_seqlens[doc];
   const int doc_len = p.cu_seqlens[doc + 1] - doc_start;
   const int num_kb = (doc_len + KB - 1) / KB;
-  const int jb = (int)blockIdx.x;  // small j = most work: launched first
   if (jb >= num_kb) return;
   const int kv0 = jb * KB;
   const int num_qb = (doc_len + QB - 1) / QB;
@@ -145,6 +154,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     tma_prefetch_desc(&tmK);
     tma_prefetch_desc(&tmV);
     tma_prefetch_desc(&tmDO);
+    tma_prefetch_desc(&tmDQ);
     mbar_init(kv_full, 1);
     for (int i = 0; i < 2; ++i) {
       mbar_init(&qdo_full[i], 1);
@@ -235,12 +245,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     for (int it = 0; it < n_iter; ++it) {
       if (it + 1 < n_iter) issue_sdp(it + 1);
       const int s = it & 1;
-      mbar_wait(&pds_full[s], (it >> 1) & 1);
+      mbar_wait(&pds_full[0], it & 1);
       mbar_wait(dq_free, (it & 1) ^ 1);
       tc_fence_after();
       if (elect_one()) {
         const uint32_t qa = smem_u32(sQ + s * SM::kQ), da = smem_u32(sDO + s * SM::kDO);
-        const uint32_t pa = smem_u32(sP + s * SM::kP), dsa = smem_u32(sDS + s * SM::kDS);
+        const uint32_t pa = smem_u32(sP), dsa = smem_u32(sDS);
         const uint32_t ka = smem_u32(sK);
         // dV^T[D, kv] += dO^T[D, q] P[q, kv]   (reduction over the 128 query rows)
 #pragma unroll
@@ -258,7 +268,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           umma_f16<1>(tm_dQ, make_smem_desc_sw128(dsa + kk * 32, 16, 1024),
                       make_smem_desc_sw128(ka + kk * 2048, KB * 128, 1024), idesc_q, kk != 0);
         umma_commit<1>(&qdo_empty[s]);
-        umma_commit<1>(&pds_empty[s]);
+        umma_commit<1>(&pds_empty[0]);
         umma_commit<1>(dq_full);
         if (it == n_iter - 1) umma_commit<1>(done_bar);
       }
@@ -281,56 +291,51 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
       mbar_wait(&sdp_full[s], (it >> 1) & 1);
       tc_fence_after();
-      uint32_t sr[KB], dr[KB];
-      {
-        uint32_t t0[32], t1[32];
-        tmem_ld_32x32b_x32(tm_S[s] + lane_off, t0);
-        tmem_ld_32x32b_x32(tm_S[s] + lane_off + 32, t1);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) { sr[i] = t0[i]; sr[32 + i] = t1[i]; }
-        tmem_ld_32x32b_x32(tm_dP[s] + lane_off, t0);
-        tmem_ld_32x32b_x32(tm_dP[s] + lane_off + 32, t1);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) { dr[i] = t0[i]; dr[32 + i] = t1[i]; }
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane_id() == 0) mbar_arrive(&sdp_free[s]);
       // last kv index this query row may attend
       const int lim = valid_row ? (p.causal ? min(q_idx, doc_len - 1) : doc_len - 1) : -1;
-      uint32_t pp[KB / 2], dd[KB / 2];
+      const uint32_t prow = smem_u32(sP) + row * 128;
+      const uint32_t drow = smem_u32(sDS) + row * 128;
 #pragma unroll
-      for (int i = 0; i < KB / 2; ++i) {
-        float pv[2], dv[2];
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-          const int c = 2 * i + e;
-          const bool on = (kv0 + c) <= lim;
-          const float pe = on ? exp2f(__uint_as_float(sr[c]) * p.scale_log2 - lse2) : 0.f;
-          pv[e] = pe;
-          dv[e] = pe * (__uint_as_float(dr[c]) - delta) * p.scale;
+      for (int hf = 0; hf < KB / 32; ++hf) {
+        uint32_t sr[32], dr[32];
+        tmem_ld_32x32b_x32(tm_S[s] + lane_off + hf * 32, sr);
+        tmem_ld_32x32b_x32(tm_dP[s] + lane_off + hf * 32, dr);
+        tmem_ld_wait();
+        if (hf == KB / 32 - 1) {  // both halves are in registers: the S / dP buffers may be refilled
+          tc_fence_before();
+          __syncwarp();
+          if (lane_id() == 0) mbar_arrive(&sdp_free[s]);
         }
-        pp[i] = pack_bf16(pv[0], pv[1]);
-        dd[i] = pack_bf16(dv[0], dv[1]);
-      }
-      mbar_wait(&pds_empty[s], ((it >> 1) & 1) ^ 1);
-      const uint32_t prow = smem_u32(sP + s * SM::kP) + row * 128;
-      const uint32_t drow = smem_u32(sDS + s * SM::kDS) + row * 128;
+        uint32_t pp[16], dd[16];
 #pragma unroll
-      for (int c = 0; c < 8; ++c) {
-        const uint32_t off = (c ^ (row & 7)) << 4;
-        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(prow + off), "r"(pp[4 * c]),
-                     "r"(pp[4 * c + 1]), "r"(pp[4 * c + 2]), "r"(pp[4 * c + 3])
-                     : "memory");
-        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(drow + off), "r"(dd[4 * c]),
-                     "r"(dd[4 * c + 1]), "r"(dd[4 * c + 2]), "r"(dd[4 * c + 3])
-                     : "memory");
+        for (int i = 0; i < 16; ++i) {
+          float pv[2], dv[2];
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const int c = 2 * i + e;
+            const bool on = (kv0 + hf * 32 + c) <= lim;
+            const float pe = on ? exp2f(__uint_as_float(sr[c]) * p.scale_log2 - lse2) : 0.f;
+            pv[e] = pe;
+            dv[e] = pe * (__uint_as_float(dr[c]) - delta) * p.scale;
+          }
+          pp[i] = pack_bf16(pv[0], pv[1]);
+          dd[i] = pack_bf16(dv[0], dv[1]);
+        }
+        if (hf == 0) mbar_wait(&pds_empty[0], (it & 1) ^ 1);  // previous step's MMAs finished reading P / dS
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const uint32_t off = ((hf * 4 + c) ^ (row & 7)) << 4;
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(prow + off), "r"(pp[4 * c]),
+                       "r"(pp[4 * c + 1]), "r"(pp[4 * c + 2]), "r"(pp[4 * c + 3])
+                       : "memory");
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(drow + off), "r"(dd[4 * c]),
+                       "r"(dd[4 * c + 1]), "r"(dd[4 * c + 2]), "r"(dd[4 * c + 3])
+                       : "memory");
+        }
       }
       fence_proxy_async_smem();
       __syncwarp();
-      if (lane_id() == 0) mbar_arrive(&pds_full[s]);
+      if (lane_id() == 0) mbar_arrive(&pds_full[0]);
     }
     // ---- drain dV^T: lane = head-dim index d, columns = kv rows ----
     if (n_iter > 0) {
@@ -359,31 +364,46 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const int quarter = warp & 3;
     const int row = quarter * 32 + (int)lane_id();
     const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
+    const bool dq_leader = threadIdx.x == 6 * 32;
+    uint32_t stage_ctr = 0;
     for (int it = 0; it < n_iter; ++it) {
       const int head = kvh * group + it / nqi;
-      const int q_idx = (i0 + it % nqi) * QB + row;
       mbar_wait(dq_full, it & 1);
       tc_fence_after();
-      uint32_t r[D];
-#pragma unroll
+      const int q_row0 = doc_start + (i0 + it % nqi) * QB;
+#pragma unroll 1
       for (int c = 0; c < D / 32; ++c) {
-        uint32_t t[32];
-        tmem_ld_32x32b_x32(tm_dQ + lane_off + c * 32, t);
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(tm_dQ + lane_off + c * 32, r);
         tmem_ld_wait();
+        if (c == D / 32 - 1) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane_id() == 0) mbar_arrive(dq_free);
+        }
+        // stage 128 rows x 32 fp32 (128 B per row, 128B swizzle) and add it into dq_accum with one
+        // TMA reduce; rows past the document end hold exact zeros (P = dS = 0 there)
+        uint8_t* sb = sDQ + (stage_ctr & 1) * SM::kDQStage;
+        if (dq_leader) tma_store_wait_read<1>();
+        named_bar_sync(2, 128);
+        const uint32_t row_addr = smem_u32(sb) + row * 128;
 #pragma unroll
-        for (int i = 0; i < 32; ++i) r[c * 32 + i] = t[i];
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane_id() == 0) mbar_arrive(dq_free);
-      if (q_idx < doc_len) {
-        float* dst = p.dq_accum + (size_t)(doc_start + q_idx) * ((size_t)p.Hq * D) + (size_t)head * D;
-#pragma unroll
-        for (int c = 0; c < D / 4; ++c)
-          red_add_v4(dst + 4 * c, __uint_as_float(r[4 * c]), __uint_as_float(r[4 * c + 1]),
-                     __uint_as_float(r[4 * c + 2]), __uint_as_float(r[4 * c + 3]));
+        for (int j = 0; j < 8; ++j) {
+          const uint32_t addr = row_addr + ((j ^ (row & 7)) << 4);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(r[4 * j]),
+                       "r"(r[4 * j + 1]), "r"(r[4 * j + 2]), "r"(r[4 * j + 3])
+                       : "memory");
+        }
+        fence_proxy_async_smem();
+        named_bar_sync(2, 128);
+        if (dq_leader) {
+          tma_reduce_add_2d(&tmDQ, sb, head * D + c * 32, q_row0);
+          tma_store_commit();
+        }
+        ++stage_ctr;
       }
     }
+    if (dq_leader) tma_store_wait<0>();
     // ---- drain dK^T ----
     if (n_iter > 0) {
       mbar_wait(done_bar, 0);
@@ -418,8 +438,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 
 template <int D>
 static int launch_attn_bwd(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
-                           const CUtensorMap& tmDO, const AttnBwdParams& prm, int max_kblocks,
-                           int ndocs, cudaStream_t stream) {
+                           const CUtensorMap& tmDO, const CUtensorMap& tmDQ,
+                           const AttnBwdParams& prm, int max_kblocks, int ndocs,
+                           cudaStream_t stream) {
   using SM = AttnBwdSmem<D>;
   auto kern = attn_bwd_kernel<D>;
   static bool attr_set = false;
@@ -428,8 +449,8 @@ static int launch_attn_bwd(const CUtensorMap& tmQ, const CUtensorMap& tmK, const
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::kTotal));
     attr_set = true;
   }
-  dim3 grid(max_kblocks, prm.Hkv, ndocs);
-  kern<<<grid, kBwdThreads, SM::kTotal, stream>>>(tmQ, tmK, tmV, tmDO, prm);
+  dim3 grid(max_kblocks * prm.Hkv * ndocs);
+  kern<<<grid, kBwdThreads, SM::kTotal, stream>>>(tmQ, tmK, tmV, tmDO, tmDQ, prm);
   B2_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
@@ -462,8 +483,9 @@ int b2_attn_bwd(void* dq, void* dk, void* dv, float* dq_accum, float* delta, con
         D, do_stride, o_stride);
     B2_CUDA_CHECK(cudaGetLastError());
   }
-  CUtensorMap tmQ, tmK, tmV, tmDO;
+  CUtensorMap tmQ, tmK, tmV, tmDO, tmDQ;
   int rc;
+  if ((rc = make_tmap_2d_f32(&tmDQ, dq_accum, T, (uint64_t)Hq * D, (uint64_t)Hq * D, QB, 32))) return rc;
   if ((rc = make_tmap_2d_bf16(&tmQ, q, T, (uint64_t)Hq * D, q_stride, QB, 64))) return rc;
   if ((rc = make_tmap_2d_bf16(&tmDO, dout, T, (uint64_t)Hq * D, do_stride, QB, 64))) return rc;
   if ((rc = make_tmap_2d_bf16(&tmK, k, T, (uint64_t)Hkv * D, k_stride, KB, 64))) return rc;
@@ -480,12 +502,13 @@ int b2_attn_bwd(void* dq, void* dk, void* dv, float* dq_accum, float* delta, con
   prm.T = T;
   prm.Hq = Hq;
   prm.Hkv = Hkv;
+  prm.ndocs = ndocs;
   prm.scale = softmax_scale;
   prm.scale_log2 = softmax_scale * 1.4426950408889634f;
   prm.causal = causal;
   const int max_kb = (max_seqlen + KB - 1) / KB;
-  if (D == 64) rc = launch_attn_bwd<64>(tmQ, tmK, tmV, tmDO, prm, max_kb, ndocs, stream);
-  else rc = launch_attn_bwd<128>(tmQ, tmK, tmV, tmDO, prm, max_kb, ndocs, stream);
+  if (D == 64) rc = launch_attn_bwd<64>(tmQ, tmK, tmV, tmDO, tmDQ, prm, max_kb, ndocs, stream);
+  else rc = launch_attn_bwd<128>(tmQ, tmK, tmV, tmDO, tmDQ, prm, max_kb, ndocs, stream);
   if (rc) return rc;
   {
     const int cols = Hq * D;

@@ -1,0 +1,336 @@
+// NVLink / NVSwitch peer-memory collectives for one node (one process per GPU).
+//
+// Every rank maps every other rank's symmetric buffers into its address space (allocation and handle
+// exchange happen in parallel/peer.py); the kernels below move data with plain 16-byte loads from
+// peer pointers, reduce in fp32 registers, and synchronise ranks through flags in a symmetric signal
+// pad (st.release.sys / ld.acquire.sys), so a collective is a single kernel per GPU with no NCCL call.
+//
+//   b2_peer_barrier                 all ranks reach a point (replaces dist.barrier, N12)
+//   b2_peer_all_gather              pull the peers' shards into a local full buffer (FSDP N4, ZeRO-1 N3)
+//   b2_peer_reduce_scatter          read slice r of every peer's full buffer, sum, scale (FSDP N5, DDP N2)
+//   b2_peer_reduce_scatter_adamw    the same reduction feeding AdamW on the owned parameter shard in
+//                                   registers: the reduced gradient shard never touches memory
+//   b2_peer_all_reduce              two-phase all-reduce on a symmetric buffer (DDP buckets, TP norm grads)
+//
+// Reference: the NCCL collectives issued implicitly by DistributedDataParallel / FullyShardedDataParallel
+// / ZeroRedundancyOptimizer (02-distributed-data-parallel/train_llm.py:65,81-83,
+// 04-fully-sharded-data-parallel/train_llm.py:87-95) and the separate optimizer.step() at :213.
+#include "common.cuh"
+
+namespace b2 {
+
+constexpr int kMaxPeers = 16;
+struct PeerPtrs {
+  void* p[kMaxPeers];
+};
+
+struct alignas(16) V4 { uint32_t u[4]; };
+
+__device__ __forceinline__ V4 ld_peer(const V4* ptr) {
+  V4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.u[0]), "=r"(r.u[1]), "=r"(r.u[2]), "=r"(r.u[3])
+               : "l"(ptr));
+  return r;
+}
+// peer data that another GPU may have just written: must not use the non-coherent path
+__device__ __forceinline__ V4 ld_peer_coherent(const V4* ptr) {
+  V4 r;
+  asm volatile("ld.global.relaxed.sys.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.u[0]), "=r"(r.u[1]), "=r"(r.u[2]), "=r"(r.u[3])
+               : "l"(ptr)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ void st_flag_sys(uint32_t* ptr, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(ptr), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_flag_sys(const uint32_t* ptr) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(ptr) : "memory");
+  return v;
+}
+
+// Signal pad layout per rank: uint32 flags[channel][kMaxPeers]. A barrier on `channel` with sequence
+// number `epoch` (monotonically increasing per channel): rank r stores epoch into slot [channel][r] of
+// every peer's pad, then waits until all slots of its own pad reach epoch.
+__device__ __forceinline__ void signal_peers(const PeerPtrs& pads, int rank, int W, int channel,
+                                             uint32_t epoch) {
+  if (threadIdx.x < W) {
+    uint32_t* pad = static_cast<uint32_t*>(pads.p[threadIdx.x]);
+    st_flag_sys(pad + channel * kMaxPeers + rank, epoch);
+  }
+}
+__device__ __forceinline__ void wait_peers(const PeerPtrs& pads, int rank, int W, int channel,
+                                           uint32_t epoch) {
+  if (threadIdx.x < W) {
+    const uint32_t* pad = static_cast<const uint32_t*>(pads.p[rank]);
+    while ((int32_t)(ld_flag_sys(pad + channel * kMaxPeers + threadIdx.x) - epoch) < 0) {
+    }
+  }
+  __syncthreads();
+}
+
+__global__ void peer_barrier_kernel(PeerPtrs pads, int rank, int W, int channel, uint32_t epoch) {
+  __threadfence_system();
+  signal_peers(pads, rank, W, channel, epoch);
+  wait_peers(pads, rank, W, channel, epoch);
+}
+
+// dst[peer * n .. ] = peer's shard, for every peer (own shard copied locally unless it already
+// aliases dst). n16 = shard size in 16-byte units.
+__global__ void peer_all_gather_kernel(V4* __restrict__ dst, PeerPtrs src, size_t n16, int rank,
+                                       int W, int skip_self) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (int k = 0; k < W; ++k) {
+    const int peer = (rank + k) % W;  // start with the local shard, then walk the ring
+    if (peer == rank && skip_self) continue;
+    const V4* s = static_cast<const V4*>(src.p[peer]);
+    V4* d = dst + (size_t)peer * n16;
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i + 3 * stride < n16; i += 4 * stride) {
+      const V4 a = ld_peer(s + i), b = ld_peer(s + i + stride), c = ld_peer(s + i + 2 * stride),
+               e = ld_peer(s + i + 3 * stride);
+      d[i] = a;
+      d[i + stride] = b;
+      d[i + 2 * stride] = c;
+      d[i + 3 * stride] = e;
+    }
+    for (; i < n16; i += stride) d[i] = ld_peer(s + i);
+  }
+}
+
+__device__ __forceinline__ void acc_bf16x8(float (&acc)[8], const V4& v) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float2 f = unpack_bf16(v.u[j]);
+    acc[2 * j] += f.x;
+    acc[2 * j + 1] += f.y;
+  }
+}
+
+// counter-based "last block out" used to publish the completion flag once per kernel
+__device__ __forceinline__ bool last_block_done(unsigned int* counter) {
+  __shared__ bool is_last;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned int prev = atomicAdd(counter, 1u);
+    is_last = (prev == gridDim.x - 1);
+    if (is_last) *counter = 0;  // ready for the next launch (launches on one stream are ordered)
+  }
+  __syncthreads();
+  return is_last;
+}
+
+enum { kChanIn = 0, kChanOut = 1 };
+
+// out_shard[i] = scale * sum_peers full_peer[rank * n + i]   (bf16 in/out, fp32 accumulate)
+// If adam != 0 the reduced value is consumed by AdamW on (p, m, v) instead of being stored.
+struct AdamArgs {
+  __nv_bfloat16 *p, *m, *v;
+  float decay, beta1, beta2, eps, step_size, inv_bc2_sqrt;
+};
+
+template <bool kAdam>
+__global__ void __launch_bounds__(256)
+peer_reduce_scatter_kernel(V4* __restrict__ out_shard, PeerPtrs full, size_t n16, int rank, int W,
+                           float scale, PeerPtrs pads, int chan_base, uint32_t epoch,
+                           unsigned int* counter, AdamArgs adam) {
+  // every rank has finished producing its full buffer
+  if (blockIdx.x == 0) {
+    __threadfence_system();
+    signal_peers(pads, rank, W, chan_base + kChanIn, epoch);
+  }
+  wait_peers(pads, rank, W, chan_base + kChanIn, epoch);
+
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) {
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    V4 vals[kMaxPeers / 2];
+    // issue the loads of up to 8 peers before reducing (latency of NVLink loads ~2 us)
+    for (int base = 0; base < W; base += kMaxPeers / 2) {
+#pragma unroll
+      for (int k = 0; k < kMaxPeers / 2; ++k)
+        if (base + k < W) {
+          const int peer = (rank + base + k) % W;
+          vals[k] = ld_peer_coherent(static_cast<const V4*>(full.p[peer]) + (size_t)rank * n16 + i);
+        }
+#pragma unroll
+      for (int k = 0; k < kMaxPeers / 2; ++k)
+        if (base + k < W) acc_bf16x8(acc, vals[k]);
+    }
+    if constexpr (!kAdam) {
+      V4 o;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) o.u[j] = pack_bf16(acc[2 * j] * scale, acc[2 * j + 1] * scale);
+      out_shard[i] = o;
+    } else {
+      V4 pv = reinterpret_cast<V4*>(adam.p)[i], mv = reinterpret_cast<V4*>(adam.m)[i],
+         vv = reinterpret_cast<V4*>(adam.v)[i];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float2 pf = unpack_bf16(pv.u[j]), mf = unpack_bf16(mv.u[j]), vf = unpack_bf16(vv.u[j]);
+        const float g0 = acc[2 * j] * scale, g1 = acc[2 * j + 1] * scale;
+        mf.x = adam.beta1 * mf.x + (1.f - adam.beta1) * g0;
+        mf.y = adam.beta1 * mf.y + (1.f - adam.beta1) * g1;
+        vf.x = adam.beta2 * vf.x + (1.f - adam.beta2) * g0 * g0;
+        vf.y = adam.beta2 * vf.y + (1.f - adam.beta2) * g1 * g1;
+        pf.x = pf.x * adam.decay -
+               adam.step_size * __fdividef(mf.x, sqrtf(vf.x) * adam.inv_bc2_sqrt + adam.eps);
+        pf.y = pf.y * adam.decay -
+               adam.step_size * __fdividef(mf.y, sqrtf(vf.y) * adam.inv_bc2_sqrt + adam.eps);
+        pv.u[j] = pack_bf16(pf.x, pf.y);
+        mv.u[j] = pack_bf16(mf.x, mf.y);
+        vv.u[j] = pack_bf16(vf.x, vf.y);
+      }
+      reinterpret_cast<V4*>(adam.p)[i] = pv;
+      reinterpret_cast<V4*>(adam.m)[i] = mv;
+      reinterpret_cast<V4*>(adam.v)[i] = vv;
+    }
+  }
+  // every rank has finished reading the full buffers: they may be overwritten
+  if (last_block_done(counter)) {
+    __threadfence_system();
+    signal_peers(pads, rank, W, chan_base + kChanOut, epoch);
+    wait_peers(pads, rank, W, chan_base + kChanOut, epoch);
+  }
+}
+
+// In-place all-reduce of a symmetric buffer: phase 1 reduces slice `rank` from all peers into the
+// local copy, phase 2 (after a barrier) pulls the other reduced slices.
+__global__ void __launch_bounds__(256)
+peer_all_reduce_kernel(PeerPtrs buf, size_t n16_slice, int rank, int W, float scale, PeerPtrs pads,
+                       int chan_base, uint32_t epoch, unsigned int* counter) {
+  if (blockIdx.x == 0) {
+    __threadfence_system();
+    signal_peers(pads, rank, W, chan_base + kChanIn, epoch);
+  }
+  wait_peers(pads, rank, W, chan_base + kChanIn, epoch);
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  V4* mine = static_cast<V4*>(buf.p[rank]);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16_slice; i += stride) {
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int k = 0; k < W; ++k) {
+      const int peer = (rank + k) % W;
+      acc_bf16x8(acc, ld_peer_coherent(static_cast<const V4*>(buf.p[peer]) + (size_t)rank * n16_slice + i));
+    }
+    V4 o;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) o.u[j] = pack_bf16(acc[2 * j] * scale, acc[2 * j + 1] * scale);
+    mine[(size_t)rank * n16_slice + i] = o;
+  }
+  // all ranks have written their reduced slice (grid-wide + cross-rank barrier)
+  __shared__ bool released;
+  if (last_block_done(counter)) {
+    __threadfence_system();
+    signal_peers(pads, rank, W, chan_base + kChanOut, epoch);
+  }
+  wait_peers(pads, rank, W, chan_base + kChanOut, epoch);
+  (void)released;
+  for (int k = 1; k < W; ++k) {
+    const int peer = (rank + k) % W;
+    const V4* s = static_cast<const V4*>(buf.p[peer]) + (size_t)peer * n16_slice;
+    V4* d = mine + (size_t)peer * n16_slice;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16_slice; i += stride)
+      d[i] = ld_peer_coherent(s + i);
+  }
+}
+
+static int clamp_blocks(size_t work16, int max_blocks) {
+  size_t b = (work16 + 255) / 256;
+  int cap = max_blocks > 0 ? max_blocks : 64;
+  if (b > (size_t)cap) b = cap;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+static PeerPtrs to_ptrs(void* const* arr, int W) {
+  PeerPtrs p;
+  for (int i = 0; i < kMaxPeers; ++i) p.p[i] = i < W ? arr[i] : nullptr;
+  return p;
+}
+
+}  // namespace b2
+
+using namespace b2;
+
+extern "C" {
+
+int b2_peer_barrier(void* const* pads, int rank, int W, int channel, unsigned int epoch,
+                    cudaStream_t stream) {
+  B2_REQUIRE(W >= 1 && W <= kMaxPeers, "peer collectives support up to %d ranks (got %d)", kMaxPeers, W);
+  peer_barrier_kernel<<<1, 32, 0, stream>>>(to_ptrs(pads, W), rank, W, channel, epoch);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// dst: local full buffer [W * shard_bytes]; srcs[r]: rank r's shard (peer-mapped pointers).
+int b2_peer_all_gather(void* dst, void* const* srcs, size_t shard_bytes, int rank, int W,
+                       int skip_self, int max_blocks, cudaStream_t stream) {
+  B2_REQUIRE(W >= 1 && W <= kMaxPeers, "peer collectives support up to %d ranks (got %d)", kMaxPeers, W);
+  B2_REQUIRE(shard_bytes % 16 == 0, "all_gather: shard size %zu not a multiple of 16 bytes", shard_bytes);
+  if (shard_bytes == 0) return 0;
+  const size_t n16 = shard_bytes / 16;
+  peer_all_gather_kernel<<<clamp_blocks(n16, max_blocks), 256, 0, stream>>>(
+      static_cast<V4*>(dst), to_ptrs(srcs, W), n16, rank, W, skip_self);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// out_shard[shard_elems] (bf16) = scale * sum over ranks of fulls[r][rank * shard_elems + i].
+// counter: one zero-initialised uint32 in local device memory, reused across calls on one stream.
+int b2_peer_reduce_scatter(void* out_shard, void* const* fulls, size_t shard_elems, int rank, int W,
+                           float scale, void* const* pads, int chan_base, unsigned int epoch,
+                           unsigned int* counter, int max_blocks, cudaStream_t stream) {
+  B2_REQUIRE(W >= 1 && W <= kMaxPeers, "peer collectives support up to %d ranks (got %d)", kMaxPeers, W);
+  B2_REQUIRE(shard_elems % 8 == 0, "reduce_scatter: shard of %zu elements is not a multiple of 8", shard_elems);
+  const size_t n16 = shard_elems / 8;
+  AdamArgs none = {};
+  peer_reduce_scatter_kernel<false><<<clamp_blocks(n16, max_blocks), 256, 0, stream>>>(
+      static_cast<V4*>(out_shard), to_ptrs(fulls, W), n16, rank, W, scale, to_ptrs(pads, W),
+      chan_base, epoch, counter, none);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// Reduce-scatter fused with the sharded AdamW update: p/m/v are this rank's shard (shard_elems).
+int b2_peer_reduce_scatter_adamw(void* p, void* m, void* v, void* const* fulls, size_t shard_elems,
+                                 int rank, int W, float grad_scale, float lr, float beta1,
+                                 float beta2, float eps, float wd, int step, void* const* pads,
+                                 int chan_base, unsigned int epoch, unsigned int* counter,
+                                 int max_blocks, cudaStream_t stream) {
+  B2_REQUIRE(W >= 1 && W <= kMaxPeers, "peer collectives support up to %d ranks (got %d)", kMaxPeers, W);
+  B2_REQUIRE(shard_elems % 8 == 0, "reduce_scatter: shard of %zu elements is not a multiple of 8", shard_elems);
+  const size_t n16 = shard_elems / 8;
+  AdamArgs a;
+  a.p = static_cast<__nv_bfloat16*>(p);
+  a.m = static_cast<__nv_bfloat16*>(m);
+  a.v = static_cast<__nv_bfloat16*>(v);
+  a.decay = 1.f - lr * wd;
+  a.beta1 = beta1;
+  a.beta2 = beta2;
+  a.eps = eps;
+  a.step_size = lr / (1.f - powf(beta1, (float)step));
+  a.inv_bc2_sqrt = 1.f / sqrtf(1.f - powf(beta2, (float)step));
+  peer_reduce_scatter_kernel<true><<<clamp_blocks(n16, max_blocks), 256, 0, stream>>>(
+      nullptr, to_ptrs(fulls, W), n16, rank, W, grad_scale, to_ptrs(pads, W), chan_base, epoch,
+      counter, a);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// In-place all-reduce (scale * sum) of symmetric buffers bufs[r] of `elems` bf16 (elems % (8*W) == 0).
+int b2_peer_all_reduce(void* const* bufs, size_t elems, int rank, int W, float scale,
+                       void* const* pads, int chan_base, unsigned int epoch, unsigned int* counter,
+                       int max_blocks, cudaStream_t stream) {
+  B2_REQUIRE(W >= 1 && W <= kMaxPeers, "peer collectives support up to %d ranks (got %d)", kMaxPeers, W);
+  B2_REQUIRE(elems % (8 * (size_t)W) == 0, "all_reduce: %zu elements not a multiple of 8*W", elems);
+  const size_t n16_slice = elems / 8 / W;
+  peer_all_reduce_kernel<<<clamp_blocks(n16_slice, max_blocks), 256, 0, stream>>>(
+      to_ptrs(bufs, W), n16_slice, rank, W, scale, to_ptrs(pads, W), chan_base, epoch, counter);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

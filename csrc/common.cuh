@@ -366,6 +366,9 @@ int make_tmap_2d_bf16(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t
 // 3-D view used for MN-major operands: dims (64, rows, cols/64), box (64, box_rows, box_chunks)
 int make_tmap_mn_bf16(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols,
                       uint64_t row_stride_elems, uint32_t box_rows, uint32_t box_chunks);
+// 2-D fp32 row-major tensor, box [box_rows, box_cols] with box_cols * 4 == 128 bytes, 128B swizzle
+int make_tmap_2d_f32(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols,
+                     uint64_t row_stride_elems, uint32_t box_rows, uint32_t box_cols);
 int sm_count();
 
 }  // namespace b2

@@ -195,16 +195,24 @@ rmsnorm_bwd_kernel(__nv_bfloat16* __restrict__ dx, float* __restrict__ partial,
   }
 }
 
-// out[h] (+)= sum_b partial[b, h]
-__global__ void fold_partials_kernel(__nv_bfloat16* __restrict__ out,
-                                     const float* __restrict__ partial, int nblocks, int H,
-                                     int accumulate) {
-  const int hcol = blockIdx.x * blockDim.x + threadIdx.x;
-  if (hcol >= H) return;
+// out[h] (+)= sum_b partial[b, h].  Block = 32 columns x 8 row slices (coalesced 128 B row reads).
+__global__ void __launch_bounds__(256)
+fold_partials_kernel(__nv_bfloat16* __restrict__ out, const float* __restrict__ partial,
+                     int nblocks, int H, int accumulate) {
+  __shared__ float red[8][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int hcol = blockIdx.x * 32 + tx;
   float s = 0.f;
-  for (int b = 0; b < nblocks; ++b) s += partial[(size_t)b * H + hcol];
-  if (accumulate) s += __bfloat162float(out[hcol]);
-  out[hcol] = __float2bfloat16_rn(s);
+  if (hcol < H)
+    for (int b = ty; b < nblocks; b += 8) s += partial[(size_t)b * H + hcol];
+  red[ty][tx] = s;
+  __syncthreads();
+  if (ty == 0 && hcol < H) {
+#pragma unroll
+    for (int k = 1; k < 8; ++k) s += red[k][tx];
+    if (accumulate) s += __bfloat162float(out[hcol]);
+    out[hcol] = __float2bfloat16_rn(s);
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -624,27 +632,55 @@ ce_bwd_kernel(__nv_bfloat16* __restrict__ dlogits, const __nv_bfloat16* __restri
 // params: fp32 math per element, decoupled weight decay, bias correction). `grad_scale` folds the
 // 1/world factor of a data-parallel mean into the update.
 // ------------------------------------------------------------------------------------------------
-__global__ void adamw_kernel(__nv_bfloat16* __restrict__ p, __nv_bfloat16* __restrict__ m,
-                             __nv_bfloat16* __restrict__ v, const __nv_bfloat16* __restrict__ g,
-                             size_t n, float lr, float beta1, float beta2, float eps, float wd,
-                             float bc1, float bc2_sqrt, float grad_scale) {
+__device__ __forceinline__ void adamw_vec(float (&pf)[8], float (&mf)[8], float (&vf)[8],
+                                          const float (&gf)[8], float decay, float beta1,
+                                          float beta2, float eps, float step_size,
+                                          float inv_bc2_sqrt, float grad_scale) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float gr = gf[j] * grad_scale;
+    mf[j] = beta1 * mf[j] + (1.f - beta1) * gr;
+    vf[j] = beta2 * vf[j] + (1.f - beta2) * gr * gr;
+    const float denom = sqrtf(vf[j]) * inv_bc2_sqrt + eps;
+    pf[j] = pf[j] * decay - step_size * __fdividef(mf[j], denom);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+adamw_kernel(__nv_bfloat16* __restrict__ p, __nv_bfloat16* __restrict__ m,
+             __nv_bfloat16* __restrict__ v, const __nv_bfloat16* __restrict__ g, size_t n, float lr,
+             float beta1, float beta2, float eps, float wd, float bc1, float bc2_sqrt,
+             float grad_scale) {
   const size_t nvec = n >> 3;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec;
-       i += (size_t)gridDim.x * blockDim.x) {
+  const float decay = 1.f - lr * wd, step_size = lr / bc1, inv_bc2_sqrt = 1.f / bc2_sqrt;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  // two independent 16-byte vectors per thread per trip: 8 loads in flight before any math
+  for (; i + stride < nvec; i += 2 * stride) {
+    const size_t i1 = i + stride;
+    const BF8 p0 = reinterpret_cast<const BF8*>(p)[i], p1 = reinterpret_cast<const BF8*>(p)[i1];
+    const BF8 m0 = reinterpret_cast<const BF8*>(m)[i], m1 = reinterpret_cast<const BF8*>(m)[i1];
+    const BF8 v0 = reinterpret_cast<const BF8*>(v)[i], v1 = reinterpret_cast<const BF8*>(v)[i1];
+    const BF8 g0 = reinterpret_cast<const BF8*>(g)[i], g1 = reinterpret_cast<const BF8*>(g)[i1];
+    float pf[8], mf[8], vf[8], gf[8];
+    bf8_to_f(p0, pf); bf8_to_f(m0, mf); bf8_to_f(v0, vf); bf8_to_f(g0, gf);
+    adamw_vec(pf, mf, vf, gf, decay, beta1, beta2, eps, step_size, inv_bc2_sqrt, grad_scale);
+    reinterpret_cast<BF8*>(p)[i] = f_to_bf8(pf);
+    reinterpret_cast<BF8*>(m)[i] = f_to_bf8(mf);
+    reinterpret_cast<BF8*>(v)[i] = f_to_bf8(vf);
+    bf8_to_f(p1, pf); bf8_to_f(m1, mf); bf8_to_f(v1, vf); bf8_to_f(g1, gf);
+    adamw_vec(pf, mf, vf, gf, decay, beta1, beta2, eps, step_size, inv_bc2_sqrt, grad_scale);
+    reinterpret_cast<BF8*>(p)[i1] = f_to_bf8(pf);
+    reinterpret_cast<BF8*>(m)[i1] = f_to_bf8(mf);
+    reinterpret_cast<BF8*>(v)[i1] = f_to_bf8(vf);
+  }
+  if (i < nvec) {
     float pf[8], mf[8], vf[8], gf[8];
     bf8_to_f(reinterpret_cast<const BF8*>(p)[i], pf);
     bf8_to_f(reinterpret_cast<const BF8*>(m)[i], mf);
     bf8_to_f(reinterpret_cast<const BF8*>(v)[i], vf);
     bf8_to_f(reinterpret_cast<const BF8*>(g)[i], gf);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float gr = gf[j] * grad_scale;
-      pf[j] *= (1.f - lr * wd);
-      mf[j] = beta1 * mf[j] + (1.f - beta1) * gr;
-      vf[j] = beta2 * vf[j] + (1.f - beta2) * gr * gr;
-      const float denom = sqrtf(vf[j]) / bc2_sqrt + eps;
-      pf[j] -= (lr / bc1) * (mf[j] / denom);
-    }
+    adamw_vec(pf, mf, vf, gf, decay, beta1, beta2, eps, step_size, inv_bc2_sqrt, grad_scale);
     reinterpret_cast<BF8*>(p)[i] = f_to_bf8(pf);
     reinterpret_cast<BF8*>(m)[i] = f_to_bf8(mf);
     reinterpret_cast<BF8*>(v)[i] = f_to_bf8(vf);
@@ -724,8 +760,8 @@ int b2_rmsnorm_bwd(void* dx, void* dw, float* partial, const void* dy, const voi
   else B2_RMS_BWD(8);
 #undef B2_RMS_BWD
   B2_CUDA_CHECK(cudaGetLastError());
-  fold_partials_kernel<<<(H + 255) / 256, 256, 0, stream>>>((bf16*)dw, partial, nb, H,
-                                                            accumulate_dw);
+  fold_partials_kernel<<<(H + 31) / 32, 256, 0, stream>>>((bf16*)dw, partial, nb, H,
+                                                          accumulate_dw);
   B2_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
@@ -957,8 +993,8 @@ int b2_rmsnorm_bwd_static(void* dx, void* dw, const void* dy, const void* h, con
   else B2_RMS_BWD(8);
 #undef B2_RMS_BWD
   B2_CUDA_CHECK(cudaGetLastError());
-  fold_partials_kernel<<<(H + 255) / 256, 256, 0, stream>>>((bf16*)dw, partial, nb, H,
-                                                            accumulate_dw);
+  fold_partials_kernel<<<(H + 31) / 32, 256, 0, stream>>>((bf16*)dw, partial, nb, H,
+                                                          accumulate_dw);
   B2_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

@@ -353,6 +353,23 @@ int make_tmap_mn_bf16(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t
   return 0;
 }
 
+int make_tmap_2d_f32(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols,
+                     uint64_t row_stride_elems, uint32_t box_rows, uint32_t box_cols) {
+  EncodeTiledFn enc = get_encode();
+  B2_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
+  B2_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "TMA base %p not 16B aligned", ptr);
+  B2_REQUIRE((row_stride_elems * 4) % 16 == 0, "TMA row stride not 16B multiple");
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {row_stride_elems * 4};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(ptr), dims, strides,
+                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  B2_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(f32) failed: %d", (int)r);
+  return 0;
+}
+
 int sm_count() {
   static int n = 0;
   if (n == 0) {

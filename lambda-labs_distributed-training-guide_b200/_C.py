@@ -51,6 +51,11 @@ def _declare(lib):
         "b2_ce_bwd": [P, P, P, P, I, I, I, I, I, F, P, P],
         "b2_adamw": [P, P, P, P, Z, F, F, F, F, F, I, F, I, P],
         "b2_add": [P, P, P, Z, P],
+        "b2_peer_barrier": [P, I, I, I, ctypes.c_uint, P],
+        "b2_peer_all_gather": [P, P, Z, I, I, I, I, P],
+        "b2_peer_reduce_scatter": [P, P, Z, I, I, F, P, I, ctypes.c_uint, P, I, P],
+        "b2_peer_reduce_scatter_adamw": [P, P, P, P, Z, I, I, F, F, F, F, F, F, I, P, I, ctypes.c_uint, P, I, P],
+        "b2_peer_all_reduce": [P, Z, I, I, F, P, I, ctypes.c_uint, P, I, P],
     }
     for name, argtypes in sig.items():
         fn = getattr(lib, name, None)

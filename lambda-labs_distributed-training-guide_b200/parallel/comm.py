@@ -69,7 +69,18 @@ class Comm:
         return t
 
     def barrier(self):
-        pass
+        """Host-blocking barrier (filesystem coordination, start-up)."""
+
+    def stream_barrier(self):
+        """Device-side barrier ordered on the current stream (no host blocking). NCCL collectives already
+        synchronise the ranks they touch, so the default is a no-op."""
+
+    def empty(self, numel: int, dtype=torch.bfloat16, device=None) -> torch.Tensor:
+        """Allocate a buffer that may take part in collectives (symmetric memory for peer comm)."""
+        return torch.empty(numel, dtype=dtype, device=device)
+
+    def reduce_scatter_adamw(self, *a, **k) -> bool:
+        return False
 
 
 class TorchComm(Comm):

@@ -42,7 +42,9 @@ class DDP(Strategy):
         self.is_cuda = self.device.type == "cuda"
         self.sync_grads = True
         self.model = self._build_local_model()
-        self.units = [FlatUnit(name, params, pad_to=self.W) for name, params in self.model.units()]
+        self.units = [FlatUnit(name, params, pad_to=8 * self.W,
+                               alloc=lambda k: self.comm.empty(k, dtype, self.device))
+                      for name, params in self.model.units()]
         for u in self.units:  # N1: every replica starts from rank 0's weights
             self.comm.broadcast(u.flat_param, 0)
         self.optimizer = FlatAdamW(self.units, lr=lr, shard=(self.R, self.W) if self.zero1 else None)
@@ -135,6 +137,7 @@ class DDP(Strategy):
             return
         u = self.units[i]
         n = u.numel // self.W
+        self.comm.stream_barrier()  # every owner finished updating its slice
         self.comm.all_gather(u.flat_param, u.flat_param[self.R * n:(self.R + 1) * n])
 
     # ---- phases ---------------------------------------------------------------------------------------

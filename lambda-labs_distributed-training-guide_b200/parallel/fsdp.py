@@ -40,8 +40,9 @@ class _BufferPool:
     address, so tensors autograd saved in forward stay valid when the unit is re-gathered in backward).
     Each slot remembers the CUDA event after which it may be overwritten."""
 
-    def __init__(self, n: int, numel: int, dtype, device, dedicated_first: bool = False):
-        self.bufs = [torch.empty(numel, dtype=dtype, device=device) for _ in range(n)]
+    def __init__(self, n: int, numel: int, dtype, device, dedicated_first: bool = False, alloc=None):
+        alloc = alloc or (lambda k: torch.empty(k, dtype=dtype, device=device))
+        self.bufs = [alloc(numel) for _ in range(n)]
         self.events = [None] * n
         self.owner = [None] * n
         self.n = n
@@ -98,7 +99,10 @@ class FSDP(Strategy):
             # without resharding every unit keeps its gathered copy for the whole step
             self.param_pool = _BufferPool((3 + int(tied)) if self.reshard else n_units, max_numel, dtype,
                                           self.device, dedicated_first=tied and self.reshard)
-            self.grad_pool = _BufferPool(2 + int(tied), max_numel, dtype, self.device, dedicated_first=tied)
+            # gradient buffers are read by the peers' reduce-scatter: allocate them through the comm
+            self.grad_pool = _BufferPool(2 + int(tied), max_numel, dtype, self.device, dedicated_first=tied,
+                                         alloc=(None if cpu_offload else
+                                                lambda k: self.comm.empty(k, dtype, self.device)))
         host = dict(device="cpu", pin_memory=self.is_cuda) if cpu_offload else dict(device=self.device)
         self.shard_param: List[torch.Tensor] = []
         self.shard_grad: List[torch.Tensor] = []
@@ -112,7 +116,7 @@ class FSDP(Strategy):
                 self.shard_param.append(full)
                 self.shard_grad.append(torch.zeros(u.numel, dtype=dtype, device=self.device))
             else:
-                shard = torch.empty(n, dtype=dtype, **host)
+                shard = torch.empty(n, dtype=dtype, **host) if cpu_offload else self.comm.empty(n, dtype, self.device)
                 shard.copy_(full[self.R * n:(self.R + 1) * n])
                 self.shard_param.append(shard)
                 self.shard_grad.append(torch.zeros(n, dtype=dtype, **host))
@@ -290,6 +294,19 @@ class FSDP(Strategy):
             full.add_(self._local_acc.pop(i))
         ready = self._record()
         slot = self._grad_slot.pop(i)
+        if self.fuse_optimizer and self.W > 1:
+            # one kernel: pull + reduce the peers' gradient slices and apply AdamW to the owned shard
+            with self._on(self.comm_stream):
+                self._wait(ready, self.comm_stream)
+                if not self._stepped:
+                    self.optimizer.begin_step()
+                g = self.optimizer.param_groups[0]
+                if self.comm.reduce_scatter_adamw(self.shard_param[i], self.optimizer.exp_avg[i],
+                                                  self.optimizer.exp_avg_sq[i], full, g["lr"], g["betas"][0],
+                                                  g["betas"][1], g["eps"], g["weight_decay"], self.optimizer._step):
+                    self._stepped.add(i)
+                    self.grad_pool.release(slot, self._record(self.comm_stream))
+                    return
         with self._on(self.comm_stream):
             self._wait(ready, self.comm_stream)
             if self.cpu_offload:
@@ -319,6 +336,13 @@ class FSDP(Strategy):
                 self._opt_events[i] = self._record(self.comm_stream)
 
     # ---- phases ---------------------------------------------------------------------------------------
+    def forward(self, batch):
+        if not self.resident and self.W > 1:
+            # every rank's parameter shards are final (optimizer of the previous step) before any pull
+            with self._on(self.comm_stream):
+                self.comm.stream_barrier()
+        return self.model(**batch)
+
     def backward(self, loss):
         loss.backward()
         self.post_backward(0)  # the embedding unit has no differentiable input to fire it

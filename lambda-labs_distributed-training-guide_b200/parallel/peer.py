@@ -1,0 +1,159 @@
+"""Peer-memory (NVLink / NVSwitch) communicator for the ranks of one node.
+
+Buffers that take part in collectives are carved out of *symmetric arenas*: CUDA allocations that every
+rank of the group maps into its own address space (``torch.distributed._symmetric_memory`` does the VMM
+allocation and the handle exchange -- plumbing only; every byte moved afterwards is moved by the
+kernels in ``csrc/comm.cu`` with loads from the mapped peer pointers and flags in a symmetric signal pad).
+
+``PeerComm`` implements the :class:`Comm` surface used by the DDP / FSDP strategies plus the fused
+``reduce_scatter_adamw``. Tensors passed to its collectives must come from :meth:`empty` (strategies
+allocate shards and gradient buffers through ``comm.empty``); anything else falls back to NCCL.
+
+Reference: the implicit NCCL all-gather / reduce-scatter / all-reduce of FSDP and DDP
+(``04-fully-sharded-data-parallel/train_llm.py:87-95``, ``02-distributed-data-parallel/train_llm.py:65``).
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from .. import _C
+from .comm import TorchComm
+
+_ARENA_MIN_BYTES = 256 << 20
+_ALIGN = 256
+CHAN_RS, CHAN_AR, CHAN_BARRIER = 0, 2, 4
+
+
+class _Arena:
+    def __init__(self, nbytes: int, device, group):
+        import torch.distributed._symmetric_memory as symm
+
+        self.buf = symm.empty(nbytes, dtype=torch.uint8, device=device)
+        self.hdl = symm.rendezvous(self.buf, group=group if group is not None else dist.group.WORLD)
+        self.base = self.buf.data_ptr()
+        self.peer_bases = [int(p) for p in self.hdl.buffer_ptrs]
+        self.nbytes = nbytes
+        self.used = 0
+
+    def take(self, nbytes: int) -> Optional[torch.Tensor]:
+        start = (self.used + _ALIGN - 1) // _ALIGN * _ALIGN
+        if start + nbytes > self.nbytes:
+            return None
+        self.used = start + nbytes
+        return self.buf[start:start + nbytes]
+
+
+class PeerComm(TorchComm):
+    def __init__(self, group=None, device=None):
+        super().__init__(group)
+        if self.backend != "nccl":
+            raise RuntimeError("PeerComm needs CUDA ranks (nccl process group)")
+        if self.world > 16:
+            raise RuntimeError("peer-memory collectives support up to 16 ranks on one node")
+        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        self.arenas: List[_Arena] = []
+        pad = self.empty(64 * 16, torch.int32)   # signal pad: [channel][16 ranks]
+        pad.zero_()
+        self._pad = pad
+        self._pad_ptrs = self._peer_array(pad)
+        self._epochs = {}
+        self._counters = {}
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=self.group)          # pads are zeroed everywhere before the first signal
+
+    # ---- symmetric allocation ---------------------------------------------------------------------
+    def empty(self, numel: int, dtype=torch.bfloat16, device=None) -> torch.Tensor:
+        nbytes = numel * torch.empty((), dtype=dtype).element_size()
+        for a in self.arenas:
+            t = a.take(nbytes)
+            if t is not None:
+                return t.view(dtype)
+        # every rank allocates the same sequence of sizes, so arenas line up across ranks
+        arena = _Arena(max(_ARENA_MIN_BYTES, nbytes + _ALIGN), self.device, self.group)
+        self.arenas.append(arena)
+        return arena.take(nbytes).view(dtype)
+
+    def _locate(self, t: torch.Tensor):
+        p = t.data_ptr()
+        for a in self.arenas:
+            if a.base <= p < a.base + a.nbytes:
+                return a, p - a.base
+        return None, 0
+
+    def is_symmetric(self, t: torch.Tensor) -> bool:
+        return self._locate(t)[0] is not None
+
+    def _peer_array(self, t: torch.Tensor):
+        a, off = self._locate(t)
+        if a is None:
+            return None
+        arr = (ctypes.c_void_p * self.world)(*[b + off for b in a.peer_bases])
+        return arr
+
+    def _epoch(self, chan: int) -> int:
+        e = self._epochs.get(chan, 0) + 1
+        self._epochs[chan] = e
+        return e & 0xFFFFFFFF
+
+    def _counter(self) -> torch.Tensor:
+        key = torch.cuda.current_stream(self.device).cuda_stream
+        c = self._counters.get(key)
+        if c is None:
+            c = torch.zeros(1, dtype=torch.int32, device=self.device)
+            self._counters[key] = c
+        return c
+
+    def _stream(self):
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    # ---- collectives --------------------------------------------------------------------------------
+    def stream_barrier(self):
+        if self.world == 1:
+            return
+        _C.call("b2_peer_barrier", self._pad_ptrs, self.rank, self.world, CHAN_BARRIER,
+                self._epoch(CHAN_BARRIER), self._stream())
+
+    def all_gather(self, full, shard, max_blocks: int = 48):
+        """``full`` is local; ``shard`` must be symmetric. Source shards must be stable: the caller
+        orders them against their last writer with :meth:`barrier` (FSDP does this once per step)."""
+        srcs = self._peer_array(shard) if self.world > 1 else None
+        if srcs is None:
+            return super().all_gather(full, shard)
+        n = shard.numel() * shard.element_size()
+        skip_self = int(full.data_ptr() + self.rank * n == shard.data_ptr())
+        _C.call("b2_peer_all_gather", full.data_ptr(), srcs, n, self.rank, self.world, skip_self, max_blocks,
+                self._stream())
+
+    def reduce_scatter(self, shard, full, average=True, max_blocks: int = 48):
+        fulls = self._peer_array(full) if self.world > 1 else None
+        if fulls is None or shard.dtype != torch.bfloat16:
+            return super().reduce_scatter(shard, full, average)
+        _C.call("b2_peer_reduce_scatter", shard.data_ptr(), fulls, shard.numel(), self.rank, self.world,
+                (1.0 / self.world) if average else 1.0, self._pad_ptrs, CHAN_RS, self._epoch(CHAN_RS),
+                self._counter().data_ptr(), max_blocks, self._stream())
+
+    def reduce_scatter_adamw(self, p, m, v, full_grad, lr, beta1, beta2, eps, wd, step, average=True,
+                             max_blocks: int = 64) -> bool:
+        """Fused gradient reduce-scatter + AdamW on the owned shard. Returns False when the buffers are not
+        eligible (caller then runs the two steps separately)."""
+        fulls = self._peer_array(full_grad) if self.world > 1 else None
+        if fulls is None or p.dtype != torch.bfloat16:
+            return False
+        _C.call("b2_peer_reduce_scatter_adamw", p.data_ptr(), m.data_ptr(), v.data_ptr(), fulls, p.numel(),
+                self.rank, self.world, (1.0 / self.world) if average else 1.0, lr, beta1, beta2, eps, wd, step,
+                self._pad_ptrs, CHAN_RS, self._epoch(CHAN_RS), self._counter().data_ptr(), max_blocks,
+                self._stream())
+        return True
+
+    def all_reduce(self, t, average=True, max_blocks: int = 48):
+        bufs = self._peer_array(t) if self.world > 1 else None
+        if bufs is None or t.dtype != torch.bfloat16 or t.numel() % (8 * self.world):
+            return super().all_reduce(t, average)
+        _C.call("b2_peer_all_reduce", bufs, t.numel(), self.rank, self.world,
+                (1.0 / self.world) if average else 1.0, self._pad_ptrs, CHAN_AR, self._epoch(CHAN_AR),
+                self._counter().data_ptr(), max_blocks, self._stream())
+        return t

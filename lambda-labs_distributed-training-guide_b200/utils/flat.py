@@ -25,7 +25,8 @@ def _round_up(n, a):
 class FlatUnit:
     """Flat storage for a list of parameters (deduplicated by identity, so tied weights appear once)."""
 
-    def __init__(self, name: str, params: Iterable[nn.Parameter], pad_to: int = 1, with_grad: bool = True):
+    def __init__(self, name: str, params: Iterable[nn.Parameter], pad_to: int = 1, with_grad: bool = True,
+                 alloc=None):
         self.name = name
         self.params: List[nn.Parameter] = []
         seen = set()
@@ -43,8 +44,10 @@ class FlatUnit:
             self.offsets.append(off)
             off += _round_up(p.numel(), ALIGN)
         self.numel = _round_up(off, ALIGN * max(1, pad_to))
-        self.flat_param = torch.zeros(self.numel, dtype=self.dtype, device=self.device)
-        self.flat_grad = torch.zeros(self.numel, dtype=self.dtype, device=self.device) if with_grad else None
+        # ``alloc(numel)`` lets a communicator place the buffers in symmetric (peer-mapped) memory
+        alloc = alloc or (lambda k: torch.empty(k, dtype=self.dtype, device=self.device))
+        self.flat_param = alloc(self.numel).zero_()
+        self.flat_grad = alloc(self.numel).zero_() if with_grad else None
         # direct: kernels write gradients in place and flag them; otherwise autograd accumulates into
         # the flat views and zero_grad has to clear the buffer (CPU / reference-math path)
         self.direct = self.device.type == "cuda" and self.dtype == torch.bfloat16
