@@ -1,0 +1,195 @@
+"""CPU unit tests of the plumbing: CLI defaults, resume semantics, cosine schedule, packed collator,
+timers, metrics keys, cluster monitor parser, config presets, optimizer parity, model parity vs HF."""
+import importlib.util
+import json
+import math
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+import torch
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def test_parser_defaults_match_reference_contract():
+    from b200train.cli.train_llm import get_parser
+
+    a = get_parser("01-single-gpu").parse_args(["-e", "x", "-d", "d", "-m", "m"])
+    assert (a.save_dir, a.seed, a.num_epochs, a.lr, a.batch_size, a.log_freq, a.ckpt_freq, a.seq_length) == \
+        ("../outputs", 0, 100, 3e-5, 1, 100, 500, 1024)
+    a = get_parser("04-fsdp").parse_args(["-e", "x", "-d", "d", "-m", "m"])
+    assert a.numel_to_wrap == 100_000_000 and a.cpu_offload == "off"
+    a = get_parser("05-405b").parse_args(["-e", "x", "-d", "d", "-m", "m"])
+    assert a.cpu_offload == "on"
+    a = get_parser("07-2d-parallel").parse_args(["-e", "x", "-d", "d", "-m", "m"])
+    assert a.tp == 8 and a.seq_length is None
+    a = get_parser("00-rime").parse_args(["-e", "x"])
+    assert a.num_epochs == 1 and a.log_freq == 50 and a.seq_length == 8192
+    with pytest.raises(SystemExit):
+        get_parser("01-single-gpu").parse_args(["-d", "d", "-m", "m"])
+
+
+def test_cosine_schedule_matches_closed_form():
+    from b200train.utils.schedule import cosine_lr, make_lr_scheduler, scale_lr
+
+    p = torch.nn.Parameter(torch.zeros(1))
+    opt = torch.optim.SGD([p], lr=3e-5)
+    sched = make_lr_scheduler(opt, 3e-5)
+    for step in range(1, 1200):
+        opt.step()
+        sched.step()
+        if step in (1, 10, 500, 1000):
+            assert math.isclose(sched.get_last_lr()[0], cosine_lr(step, 3e-5), rel_tol=1e-6)
+    assert math.isclose(cosine_lr(1000, 3e-5), 3e-7, rel_tol=1e-9)   # eta_min = lr * 1e-2
+    assert scale_lr(1e-3, 8, 32) == 4e-3 and math.isclose(scale_lr(1e-3, 8, 32, "sqrt"), 2e-3)
+
+
+def test_state_json_roundtrip_and_resume_replay(tmp_path):
+    from b200train.cli.train_llm import main
+
+    common = ["-e", "r", "-d", "synthetic:32", "-m", "llama-tiny", "--save-dir", str(tmp_path), "--device", "cpu",
+              "-b", "2", "-s", "32", "--log-freq", "2", "--ckpt-freq", "4", "--num-epochs", "1", "--wandb-mode", "off"]
+    s1 = main("01-single-gpu", common + ["--max-steps", "6"])
+    saved = json.loads((tmp_path / "r" / "state.json").read_text())
+    assert set(saved) == {"epoch", "global_step", "epoch_step", "running_loss"}
+    assert saved["global_step"] == 4 and saved["epoch_step"] == 4       # last checkpoint, not last step
+    for f in ("model.pt", "optimizer.pt", "lr_scheduler.pt", "metrics.jsonl"):
+        assert (tmp_path / "r" / f).exists()
+    s2 = main("01-single-gpu", common + ["--max-steps", "3"])            # resumes at 4, replays the sampler
+    assert s2["global_step"] == 7 and s2["epoch_step"] == 7
+    rec = json.loads((tmp_path / "r" / "metrics.jsonl").read_text().splitlines()[0])
+    for k in ("global_step", "lr", "running_loss", "epoch", "epoch_progress", "num_batches_remaining", "total_gb",
+              "curr_alloc_gb", "peak_alloc_gb", "curr_resv_gb", "peak_resv_gb", "tok/s", "time/total", "time/data",
+              "time/forward", "time/backward", "time/update"):
+        assert k in rec, k
+
+
+def test_resume_continues_identically(tmp_path):
+    """6 straight steps == 4 steps + checkpoint + resume + 2 steps (model, optimizer, scheduler, data order)."""
+    from b200train.cli.train_llm import main
+
+    def args(name, extra):
+        return ["-e", name, "-d", "synthetic:32", "-m", "llama-tiny", "--save-dir", str(tmp_path), "--device", "cpu",
+                "-b", "2", "-s", "32", "--log-freq", "1", "--ckpt-freq", "4", "--num-epochs", "1", "--wandb-mode", "off",
+                "--lr", "1e-3"] + extra
+
+    main("01-single-gpu", args("a", ["--max-steps", "6"]))
+    main("01-single-gpu", args("b", ["--max-steps", "4"]))
+    main("01-single-gpu", args("b", ["--max-steps", "2"]))
+    la = [json.loads(l)["running_loss"] for l in (tmp_path / "a" / "metrics.jsonl").read_text().splitlines()]
+    lb = [json.loads(l)["running_loss"] for l in (tmp_path / "b" / "metrics.jsonl").read_text().splitlines()]
+    assert len(la) == len(lb) == 6
+    for x, y in zip(la, lb):
+        assert abs(x - y) < 1e-5, (la, lb)
+
+
+def test_packed_collator_positions_and_mask():
+    from b200train.data import block_diagonal_causal_mask, cu_seqlens_from_positions, packed_positions, pad_and_collate
+
+    eos = 128_262
+    x = torch.tensor([5, 6, eos, 7, 8, 9, eos, 1, 2])
+    keep = x.clone()
+    pos, lengths = packed_positions(x)
+    assert pos.tolist() == [0, 1, 2, 0, 1, 2, 3, 0, 1] and lengths.tolist() == [3, 4, 2]
+    assert torch.equal(x, keep)                                   # the caller's row is not mutated
+    mask = block_diagonal_causal_mask(lengths, torch.float32)
+    assert mask[4, 3] == 0 and mask[4, 2] == float("-inf") and mask[3, 4] == float("-inf")
+    batch = pad_and_collate([{"input_ids": x}, {"input_ids": x}])
+    assert batch["position_ids"].shape == (2, 9) and torch.equal(batch["labels"], batch["input_ids"])
+    assert cu_seqlens_from_positions(batch["position_ids"]).tolist() == [0, 3, 7, 9, 12, 16, 18]
+
+
+def test_group_texts_and_seq_length_clamp():
+    from b200train.data import group_texts, resolve_seq_length
+
+    out = group_texts({"input_ids": [[1, 2, 3], [4, 5], [6, 7, 8, 9]]}, 4)
+    assert out["input_ids"] == [[1, 2, 3, 4], [5, 6, 7, 8]] and out["labels"] == out["input_ids"]
+    assert resolve_seq_length(None, 2048, 4096) == 2048
+    assert resolve_seq_length(8192, 2048, 4096) == 1024           # > max positions -> min(1024, max)
+    assert resolve_seq_length(8192, 2048, 512) == 512
+
+
+def test_local_timer_cpu_branch_and_mem_stats():
+    from b200train.obs import LocalTimer, get_mem_stats, make_timers
+
+    t = LocalTimer(torch.device("cpu"))
+    with t:
+        sum(range(1000))
+    assert len(t.measurements) == 1 and t.avg_elapsed_ms() >= 0
+    t.reset()
+    assert t.measurements == []
+    assert set(make_timers("cpu", with_waiting=True)) == {"data", "forward", "backward", "update", "waiting"}
+    assert set(get_mem_stats("cpu")) == {"total_gb", "curr_alloc_gb", "peak_alloc_gb", "curr_resv_gb", "peak_resv_gb"}
+
+
+def test_top_cluster_parser():
+    spec = importlib.util.spec_from_file_location("top_cluster", ROOT / "top-cluster.py")
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    text = "100, 690.5, 700.0, 78000, 81559\n98, 700.0, 700.0, 79000, 81559\n1234\n1235\n"
+    s = mod.parse_node_output(text)
+    assert s["ngpus"] == 2 and s["nprocs"] == 2 and abs(s["util"] - 99) < 1e-6 and s["power"] > 98
+    table = mod.render({"a": s, "b": {"error": "timeout"}})
+    assert "cluster" in table and "unreachable" in table
+
+
+def test_config_presets_match_hf_parameter_counts():
+    from b200train.models import load_config
+
+    assert load_config("gpt2").num_parameters() == 124_439_808
+    assert load_config("meta-llama/Llama-3.1-8B").num_parameters() == 8_030_261_248
+    assert load_config("llama-3.1-70b").num_parameters() == 70_553_706_496
+    assert load_config("llama-3.1-405b").num_parameters() == 405_853_388_800
+    assert abs(load_config("llama-3.1-8b").flops_per_token(4096) / 1e9 - 51.47) < 0.05
+
+
+def test_adamw_reference_matches_torch():
+    from b200train.ops.optim import adamw_step
+
+    p = torch.randn(1000)
+    g = torch.randn(1000) * 0.01
+    ref = torch.nn.Parameter(p.clone())
+    opt = torch.optim.AdamW([ref], lr=1e-3)
+    m, v = torch.zeros_like(p), torch.zeros_like(p)
+    for step in range(1, 4):
+        ref.grad = g.clone()
+        opt.step()
+        adamw_step(p, g, m, v, 1e-3, step=step)
+    assert torch.allclose(p, ref.detach(), atol=1e-6)
+
+
+@pytest.mark.parametrize("name", ["llama-tiny", "gpt2-tiny"])
+def test_model_matches_hf_implementation(name):
+    """Same weights, same tokens -> same loss as the HF module the reference instantiates."""
+    transformers = pytest.importorskip("transformers")
+    from b200train.models import build_model, load_config, to_hf_dict
+
+    cfg = load_config(name)
+    ours = build_model(cfg, dtype=torch.float32, device="cpu", seed=0)
+    hf_cfg = transformers.AutoConfig.for_model(**to_hf_dict(cfg))
+    hf_cfg._attn_implementation = "eager"
+    hf = transformers.AutoModelForCausalLM.from_config(hf_cfg).float().eval()
+    sd = {k: v.clone() for k, v in ours.hf_state_dict().items()}
+    missing, unexpected = hf.load_state_dict(sd, strict=False)
+    assert not [m for m in missing if "inv_freq" not in m and "attn.bias" not in m and "masked_bias" not in m], missing
+    ids = torch.randint(0, cfg.vocab_size, (2, 48))
+    with torch.no_grad():
+        a = ours(input_ids=ids, labels=ids).loss.item()
+        b = hf(input_ids=ids, labels=ids).loss.item()
+    assert abs(a - b) < 2e-4, (a, b)
+
+
+def test_elastic_toy_restarts_and_resumes(tmp_path):
+    """torchrun --max-restarts: a rank fails once at step 3, the gang restarts and finishes from step 3."""
+    state = tmp_path / "toy-state.json"
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--max-restarts=2",
+           "--master-addr", "127.0.0.1", "--master-port", "29733", "--log-dir", str(tmp_path / "logs"),
+           str(ROOT / "related-topics" / "elastic-training" / "toy.py"), "--state-file", str(state),
+           "--total-steps", "6", "--fail-at-step", "3", "--fail-rank", "1"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=240, env={**os.environ, "OMP_NUM_THREADS": "1"})
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert json.loads(state.read_text())["num_steps"] == 6
+    assert "resuming at step 3" in (r.stdout + r.stderr)

@@ -1,0 +1,90 @@
+"""Peer-memory collectives (csrc/comm.cu) against NCCL on identical inputs. Needs >= 2 GPUs; spawns one
+process per GPU."""
+import os
+import socket
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, ret):
+    import torch.distributed as dist
+
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device(f"cuda:{rank}"))
+    try:
+        from b200train.ops.optim import adamw_step
+        from b200train.parallel.peer import PeerComm
+
+        comm = PeerComm(None, f"cuda:{rank}")
+        n = 1 << 20
+        g = torch.Generator(device="cuda").manual_seed(100 + rank)
+        errs = {}
+        for it in range(3):  # repeated calls exercise the epoch / counter protocol
+            full = comm.empty(n * world)
+            full.copy_(torch.randn(n * world, device="cuda", generator=g).to(torch.bfloat16))
+            ref_full = full.clone()
+            # reduce-scatter (mean)
+            shard = comm.empty(n)
+            comm.reduce_scatter(shard, full, average=True)
+            ref = torch.empty(n, dtype=torch.bfloat16, device="cuda")
+            dist.reduce_scatter_tensor(ref, ref_full, op=dist.ReduceOp.AVG)
+            torch.cuda.synchronize()
+            errs[f"rs{it}"] = (shard.float() - ref.float()).abs().max().item()
+            # all-gather of the reduced shards
+            out = torch.empty(n * world, dtype=torch.bfloat16, device="cuda")
+            comm.stream_barrier()
+            comm.all_gather(out, shard)
+            ref_out = torch.empty_like(out)
+            dist.all_gather_into_tensor(ref_out, ref)
+            torch.cuda.synchronize()
+            errs[f"ag{it}"] = (out.float() - ref_out.float()).abs().max().item()
+            # all-reduce in place
+            ar = comm.empty(n * world)
+            ar.copy_(ref_full)
+            comm.all_reduce(ar, average=True)
+            ref_ar = ref_full.clone()
+            dist.all_reduce(ref_ar, op=dist.ReduceOp.AVG)
+            torch.cuda.synchronize()
+            errs[f"ar{it}"] = (ar.float() - ref_ar.float()).abs().max().item()
+            # fused reduce-scatter + AdamW vs separate steps
+            p = (torch.randn(n, device="cuda", generator=g) * 0.1).to(torch.bfloat16)
+            m = torch.zeros_like(p)
+            v = torch.zeros_like(p)
+            p2, m2, v2 = p.clone(), m.clone(), v.clone()
+            full.copy_(ref_full)
+            torch.cuda.synchronize()
+            dist.barrier()
+            assert comm.reduce_scatter_adamw(p, m, v, full, 1e-3, 0.9, 0.999, 1e-8, 0.01, it + 1)
+            adamw_step(p2, ref, m2, v2, 1e-3, step=it + 1)
+            torch.cuda.synchronize()
+            errs[f"rsadam{it}"] = (p.float() - p2.float()).abs().max().item()
+            dist.barrier()
+        ret[rank] = errs
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs at least 2 GPUs")
+def test_peer_collectives_match_nccl():
+    import torch.multiprocessing as mp
+
+    world = min(torch.cuda.device_count(), 8)
+    ret = mp.Manager().dict()
+    mp.spawn(_worker, args=(world, _free_port(), ret), nprocs=world, join=True)
+    for r in range(world):
+        for k, e in ret[r].items():
+            tol = 2e-3 if k.startswith("rsadam") else 2e-2
+            assert e <= tol, (r, k, e, dict(ret[r]))
