@@ -57,8 +57,9 @@ def main():
 
     res["nccl_ag_ms"] = timed(lambda: dist.all_gather_into_tensor(full, shard))
     res["nccl_rs_ms"] = timed(lambda: dist.reduce_scatter_tensor(out_shard, full_sym, op=dist.ReduceOp.AVG))
+    res["peer_ag_ce_ms"] = timed(lambda: comm.all_gather(full, shard, copy_engine=True))
     for mb in (16, 32, 64, 128):
-        res[f"peer_ag_ms_b{mb}"] = timed(lambda: comm.all_gather(full, shard, max_blocks=mb))
+        res[f"peer_ag_ms_b{mb}"] = timed(lambda: comm.all_gather(full, shard, max_blocks=mb, copy_engine=False))
         res[f"peer_rs_ms_b{mb}"] = timed(lambda: comm.reduce_scatter(out_shard, full_sym, max_blocks=mb))
         res[f"peer_rs_adamw_ms_b{mb}"] = timed(
             lambda: comm.reduce_scatter_adamw(p, m, v, full_sym, 1e-4, 0.9, 0.999, 1e-8, 0.01, 3, max_blocks=mb))
@@ -87,12 +88,15 @@ def main():
     res["gemm+nccl_ag_rs_ms"] = timed(overlapped(lambda: (dist.all_gather_into_tensor(full, shard),
                                                          dist.reduce_scatter_tensor(out_shard, full_sym,
                                                                                     op=dist.ReduceOp.AVG))))
-    for mb in (16, 32, 64):
-        res[f"gemm+peer_ag_rs_ms_b{mb}"] = timed(overlapped(lambda: (comm.all_gather(full, shard, max_blocks=mb),
+    res["gemm+peer_agce_rs_ms_b64"] = timed(overlapped(lambda: (comm.all_gather(full, shard, copy_engine=True),
+                                                                comm.reduce_scatter(out_shard, full_sym,
+                                                                                    max_blocks=64))))
+    for mb in (32, 64, 128):
+        res[f"gemm+peer_ag_rs_ms_b{mb}"] = timed(overlapped(lambda: (comm.all_gather(full, shard, max_blocks=mb, copy_engine=False),
                                                                      comm.reduce_scatter(out_shard, full_sym,
                                                                                          max_blocks=mb))))
         res[f"gemm+peer_ag_rsadamw_ms_b{mb}"] = timed(overlapped(
-            lambda: (comm.all_gather(full, shard, max_blocks=mb),
+            lambda: (comm.all_gather(full, shard, max_blocks=mb, copy_engine=False),
                      comm.reduce_scatter_adamw(p, m, v, full_sym, 1e-4, 0.9, 0.999, 1e-8, 0.01, 3, max_blocks=mb))))
     if rank == 0:
         for k, val in res.items():

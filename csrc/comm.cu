@@ -79,8 +79,13 @@ __global__ void peer_barrier_kernel(PeerPtrs pads, int rank, int W, int channel,
 
 // dst[peer * n .. ] = peer's shard, for every peer (own shard copied locally unless it already
 // aliases dst). n16 = shard size in 16-byte units.
-__global__ void peer_all_gather_kernel(V4* __restrict__ dst, PeerPtrs src, size_t n16, int rank,
-                                       int W, int skip_self) {
+// 256 threads x <= 85 registers: a comm block fits beside a resident GEMM CTA (256 x <= 168 registers,
+// all of the SM's shared memory), so collectives really overlap the persistent GEMMs
+constexpr int kCommThreads = 256;
+
+__global__ void __launch_bounds__(kCommThreads, 3)
+peer_all_gather_kernel(V4* __restrict__ dst, PeerPtrs src, size_t n16, int rank, int W,
+                       int skip_self) {
   const size_t stride = (size_t)gridDim.x * blockDim.x;
   for (int k = 0; k < W; ++k) {
     const int peer = (rank + k) % W;  // start with the local shard, then walk the ring
@@ -88,13 +93,13 @@ __global__ void peer_all_gather_kernel(V4* __restrict__ dst, PeerPtrs src, size_
     const V4* s = static_cast<const V4*>(src.p[peer]);
     V4* d = dst + (size_t)peer * n16;
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    for (; i + 3 * stride < n16; i += 4 * stride) {
-      const V4 a = ld_peer(s + i), b = ld_peer(s + i + stride), c = ld_peer(s + i + 2 * stride),
-               e = ld_peer(s + i + 3 * stride);
-      d[i] = a;
-      d[i + stride] = b;
-      d[i + 2 * stride] = c;
-      d[i + 3 * stride] = e;
+    // 8 independent 16-byte loads in flight per thread: NVLink round trips are ~4 us
+    for (; i + 7 * stride < n16; i += 8 * stride) {
+      V4 t[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) t[u] = ld_peer(s + i + u * stride);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) d[i + u * stride] = t[u];
     }
     for (; i < n16; i += stride) d[i] = ld_peer(s + i);
   }
@@ -133,7 +138,39 @@ struct AdamArgs {
 };
 
 template <bool kAdam>
-__global__ void __launch_bounds__(256)
+__device__ __forceinline__ void rs_finish(float (&acc)[8], size_t i, float scale, V4* out_shard,
+                                          const AdamArgs& adam, V4 pv, V4 mv, V4 vv) {
+  if constexpr (!kAdam) {
+    V4 o;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) o.u[j] = pack_bf16(acc[2 * j] * scale, acc[2 * j + 1] * scale);
+    out_shard[i] = o;
+  } else {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float2 pf = unpack_bf16(pv.u[j]), mf = unpack_bf16(mv.u[j]), vf = unpack_bf16(vv.u[j]);
+      const float g0 = acc[2 * j] * scale, g1 = acc[2 * j + 1] * scale;
+      mf.x = adam.beta1 * mf.x + (1.f - adam.beta1) * g0;
+      mf.y = adam.beta1 * mf.y + (1.f - adam.beta1) * g1;
+      vf.x = adam.beta2 * vf.x + (1.f - adam.beta2) * g0 * g0;
+      vf.y = adam.beta2 * vf.y + (1.f - adam.beta2) * g1 * g1;
+      pf.x = pf.x * adam.decay -
+             adam.step_size * __fdividef(mf.x, sqrtf(vf.x) * adam.inv_bc2_sqrt + adam.eps);
+      pf.y = pf.y * adam.decay -
+             adam.step_size * __fdividef(mf.y, sqrtf(vf.y) * adam.inv_bc2_sqrt + adam.eps);
+      pv.u[j] = pack_bf16(pf.x, pf.y);
+      mv.u[j] = pack_bf16(mf.x, mf.y);
+      vv.u[j] = pack_bf16(vf.x, vf.y);
+    }
+    reinterpret_cast<V4*>(adam.p)[i] = pv;
+    reinterpret_cast<V4*>(adam.m)[i] = mv;
+    reinterpret_cast<V4*>(adam.v)[i] = vv;
+  }
+}
+
+// U vectors per thread per trip, all W peer loads of all U vectors issued before any reduction
+template <bool kAdam, int U>
+__global__ void __launch_bounds__(kCommThreads, 3)
 peer_reduce_scatter_kernel(V4* __restrict__ out_shard, PeerPtrs full, size_t n16, int rank, int W,
                            float scale, PeerPtrs pads, int chan_base, uint32_t epoch,
                            unsigned int* counter, AdamArgs adam) {
@@ -144,49 +181,47 @@ peer_reduce_scatter_kernel(V4* __restrict__ out_shard, PeerPtrs full, size_t n16
   }
   wait_peers(pads, rank, W, chan_base + kChanIn, epoch);
 
+  constexpr int kPeersPerTrip = 8 / U;  // U * kPeersPerTrip = 8 loads in flight
   const size_t stride = (size_t)gridDim.x * blockDim.x;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) {
-    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    V4 vals[kMaxPeers / 2];
-    // issue the loads of up to 8 peers before reducing (latency of NVLink loads ~2 us)
-    for (int base = 0; base < W; base += kMaxPeers / 2) {
+  for (size_t i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n16; i0 += U * stride) {
+    float acc[U][8];
+    V4 pv[U], mv[U], vv[U];
 #pragma unroll
-      for (int k = 0; k < kMaxPeers / 2; ++k)
-        if (base + k < W) {
-          const int peer = (rank + base + k) % W;
-          vals[k] = ld_peer_coherent(static_cast<const V4*>(full.p[peer]) + (size_t)rank * n16 + i);
+    for (int u = 0; u < U; ++u) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[u][j] = 0.f;
+      if constexpr (kAdam) {  // optimizer state loads travel together with the peer loads
+        const size_t i = i0 + u * stride;
+        if (i < n16) {
+          pv[u] = reinterpret_cast<V4*>(adam.p)[i];
+          mv[u] = reinterpret_cast<V4*>(adam.m)[i];
+          vv[u] = reinterpret_cast<V4*>(adam.v)[i];
+        }
+      }
+    }
+    for (int base = 0; base < W; base += kPeersPerTrip) {
+      V4 vals[U][kPeersPerTrip];
+#pragma unroll
+      for (int k = 0; k < kPeersPerTrip; ++k)
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const size_t i = i0 + u * stride;
+          if (base + k < W && i < n16) {
+            const int peer = (rank + base + k) % W;
+            vals[u][k] =
+                ld_peer_coherent(static_cast<const V4*>(full.p[peer]) + (size_t)rank * n16 + i);
+          }
         }
 #pragma unroll
-      for (int k = 0; k < kMaxPeers / 2; ++k)
-        if (base + k < W) acc_bf16x8(acc, vals[k]);
+      for (int k = 0; k < kPeersPerTrip; ++k)
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+          if (base + k < W && i0 + u * stride < n16) acc_bf16x8(acc[u], vals[u][k]);
     }
-    if constexpr (!kAdam) {
-      V4 o;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) o.u[j] = pack_bf16(acc[2 * j] * scale, acc[2 * j + 1] * scale);
-      out_shard[i] = o;
-    } else {
-      V4 pv = reinterpret_cast<V4*>(adam.p)[i], mv = reinterpret_cast<V4*>(adam.m)[i],
-         vv = reinterpret_cast<V4*>(adam.v)[i];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        float2 pf = unpack_bf16(pv.u[j]), mf = unpack_bf16(mv.u[j]), vf = unpack_bf16(vv.u[j]);
-        const float g0 = acc[2 * j] * scale, g1 = acc[2 * j + 1] * scale;
-        mf.x = adam.beta1 * mf.x + (1.f - adam.beta1) * g0;
-        mf.y = adam.beta1 * mf.y + (1.f - adam.beta1) * g1;
-        vf.x = adam.beta2 * vf.x + (1.f - adam.beta2) * g0 * g0;
-        vf.y = adam.beta2 * vf.y + (1.f - adam.beta2) * g1 * g1;
-        pf.x = pf.x * adam.decay -
-               adam.step_size * __fdividef(mf.x, sqrtf(vf.x) * adam.inv_bc2_sqrt + adam.eps);
-        pf.y = pf.y * adam.decay -
-               adam.step_size * __fdividef(mf.y, sqrtf(vf.y) * adam.inv_bc2_sqrt + adam.eps);
-        pv.u[j] = pack_bf16(pf.x, pf.y);
-        mv.u[j] = pack_bf16(mf.x, mf.y);
-        vv.u[j] = pack_bf16(vf.x, vf.y);
-      }
-      reinterpret_cast<V4*>(adam.p)[i] = pv;
-      reinterpret_cast<V4*>(adam.m)[i] = mv;
-      reinterpret_cast<V4*>(adam.v)[i] = vv;
+    for (int u = 0; u < U; ++u) {
+      const size_t i = i0 + u * stride;
+      if (i < n16) rs_finish<kAdam>(acc[u], i, scale, out_shard, adam, pv[u], mv[u], vv[u]);
     }
   }
   // every rank has finished reading the full buffers: they may be overwritten
@@ -195,6 +230,23 @@ peer_reduce_scatter_kernel(V4* __restrict__ out_shard, PeerPtrs full, size_t n16
     signal_peers(pads, rank, W, chan_base + kChanOut, epoch);
     wait_peers(pads, rank, W, chan_base + kChanOut, epoch);
   }
+}
+
+template <bool kAdam>
+static int launch_rs(int W, int blocks, cudaStream_t stream, V4* out, PeerPtrs full, size_t n16,
+                     int rank, float scale, PeerPtrs pads, int chan_base, uint32_t epoch,
+                     unsigned int* counter, AdamArgs a) {
+  if (W <= 2 && !kAdam)
+    peer_reduce_scatter_kernel<kAdam, 4><<<blocks, kCommThreads, 0, stream>>>(
+        out, full, n16, rank, W, scale, pads, chan_base, epoch, counter, a);
+  else if (W <= 4)
+    peer_reduce_scatter_kernel<kAdam, 2><<<blocks, kCommThreads, 0, stream>>>(
+        out, full, n16, rank, W, scale, pads, chan_base, epoch, counter, a);
+  else
+    peer_reduce_scatter_kernel<kAdam, 1><<<blocks, kCommThreads, 0, stream>>>(
+        out, full, n16, rank, W, scale, pads, chan_base, epoch, counter, a);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
 }
 
 // In-place all-reduce of a symmetric buffer: phase 1 reduces slice `rank` from all peers into the
@@ -238,7 +290,7 @@ peer_all_reduce_kernel(PeerPtrs buf, size_t n16_slice, int rank, int W, float sc
 }
 
 static int clamp_blocks(size_t work16, int max_blocks) {
-  size_t b = (work16 + 255) / 256;
+  size_t b = (work16 + kCommThreads - 1) / kCommThreads;
   int cap = max_blocks > 0 ? max_blocks : 64;
   if (b > (size_t)cap) b = cap;
   if (b < 1) b = 1;
@@ -272,9 +324,23 @@ int b2_peer_all_gather(void* dst, void* const* srcs, size_t shard_bytes, int ran
   B2_REQUIRE(shard_bytes % 16 == 0, "all_gather: shard size %zu not a multiple of 16 bytes", shard_bytes);
   if (shard_bytes == 0) return 0;
   const size_t n16 = shard_bytes / 16;
-  peer_all_gather_kernel<<<clamp_blocks(n16, max_blocks), 256, 0, stream>>>(
+  peer_all_gather_kernel<<<clamp_blocks(n16, max_blocks), kCommThreads, 0, stream>>>(
       static_cast<V4*>(dst), to_ptrs(srcs, W), n16, rank, W, skip_self);
   B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// Same gather driven by the copy engines: one cudaMemcpyAsync per peer from the mapped peer pointer
+// (DMA over NVLink, no SM time). The source shards must already be final (see b2_peer_barrier).
+int b2_peer_all_gather_ce(void* dst, void* const* srcs, size_t shard_bytes, int rank, int W,
+                          int skip_self, cudaStream_t stream) {
+  B2_REQUIRE(W >= 1 && W <= kMaxPeers, "peer collectives support up to %d ranks (got %d)", kMaxPeers, W);
+  for (int k = 0; k < W; ++k) {
+    const int peer = (rank + k) % W;
+    if (peer == rank && skip_self) continue;
+    B2_CUDA_CHECK(cudaMemcpyAsync(static_cast<char*>(dst) + (size_t)peer * shard_bytes, srcs[peer],
+                                  shard_bytes, cudaMemcpyDeviceToDevice, stream));
+  }
   return 0;
 }
 
@@ -287,11 +353,9 @@ int b2_peer_reduce_scatter(void* out_shard, void* const* fulls, size_t shard_ele
   B2_REQUIRE(shard_elems % 8 == 0, "reduce_scatter: shard of %zu elements is not a multiple of 8", shard_elems);
   const size_t n16 = shard_elems / 8;
   AdamArgs none = {};
-  peer_reduce_scatter_kernel<false><<<clamp_blocks(n16, max_blocks), 256, 0, stream>>>(
-      static_cast<V4*>(out_shard), to_ptrs(fulls, W), n16, rank, W, scale, to_ptrs(pads, W),
-      chan_base, epoch, counter, none);
-  B2_CUDA_CHECK(cudaGetLastError());
-  return 0;
+  return launch_rs<false>(W, clamp_blocks(n16, max_blocks), stream, static_cast<V4*>(out_shard),
+                          to_ptrs(fulls, W), n16, rank, scale, to_ptrs(pads, W), chan_base, epoch,
+                          counter, none);
 }
 
 // Reduce-scatter fused with the sharded AdamW update: p/m/v are this rank's shard (shard_elems).
@@ -313,11 +377,8 @@ int b2_peer_reduce_scatter_adamw(void* p, void* m, void* v, void* const* fulls, 
   a.eps = eps;
   a.step_size = lr / (1.f - powf(beta1, (float)step));
   a.inv_bc2_sqrt = 1.f / sqrtf(1.f - powf(beta2, (float)step));
-  peer_reduce_scatter_kernel<true><<<clamp_blocks(n16, max_blocks), 256, 0, stream>>>(
-      nullptr, to_ptrs(fulls, W), n16, rank, W, grad_scale, to_ptrs(pads, W), chan_base, epoch,
-      counter, a);
-  B2_CUDA_CHECK(cudaGetLastError());
-  return 0;
+  return launch_rs<true>(W, clamp_blocks(n16, max_blocks), stream, nullptr, to_ptrs(fulls, W), n16,
+                         rank, grad_scale, to_ptrs(pads, W), chan_base, epoch, counter, a);
 }
 
 // In-place all-reduce (scale * sum) of symmetric buffers bufs[r] of `elems` bf16 (elems % (8*W) == 0).

@@ -77,7 +77,10 @@ class FSDP(Strategy):
         self.W, self.R = self.comm.world, self.comm.rank
         self.cpu_offload = cpu_offload
         self.act_ckpt = activation_checkpointing
+        # fuse_optimizer: False | True / "kernel" (reduce-scatter + AdamW in one peer-memory kernel when the
+        # communicator provides it) | "stream" (AdamW kernel queued right behind the reduce-scatter)
         self.fuse_optimizer = fuse_optimizer and not cpu_offload
+        self.fuse_in_kernel = fuse_optimizer in (True, "kernel")
         self.is_cuda = self.device.type == "cuda"
         self.numel_to_wrap = numel_to_wrap
         self.sync_grads = True
@@ -294,7 +297,7 @@ class FSDP(Strategy):
             full.add_(self._local_acc.pop(i))
         ready = self._record()
         slot = self._grad_slot.pop(i)
-        if self.fuse_optimizer and self.W > 1:
+        if self.fuse_optimizer and self.fuse_in_kernel and self.W > 1:
             # one kernel: pull + reduce the peers' gradient slices and apply AdamW to the owned shard
             with self._on(self.comm_stream):
                 self._wait(ready, self.comm_stream)

@@ -15,6 +15,7 @@ Reference: the implicit NCCL all-gather / reduce-scatter / all-reduce of FSDP an
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import List, Optional
 
 import torch
@@ -56,6 +57,8 @@ class PeerComm(TorchComm):
             raise RuntimeError("peer-memory collectives support up to 16 ranks on one node")
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         self.arenas: List[_Arena] = []
+        # pure copies (parameter all-gather) can ride the DMA engines instead of SM load/store loops
+        self.copy_engine = os.environ.get("B200TRAIN_AG", "ce") == "ce"
         pad = self.empty(64 * 16, torch.int32)   # signal pad: [channel][16 ranks]
         pad.zero_()
         self._pad = pad
@@ -117,7 +120,7 @@ class PeerComm(TorchComm):
         _C.call("b2_peer_barrier", self._pad_ptrs, self.rank, self.world, CHAN_BARRIER,
                 self._epoch(CHAN_BARRIER), self._stream())
 
-    def all_gather(self, full, shard, max_blocks: int = 48):
+    def all_gather(self, full, shard, max_blocks: int = 64, copy_engine: Optional[bool] = None):
         """``full`` is local; ``shard`` must be symmetric. Source shards must be stable: the caller
         orders them against their last writer with :meth:`barrier` (FSDP does this once per step)."""
         srcs = self._peer_array(shard) if self.world > 1 else None
@@ -125,10 +128,14 @@ class PeerComm(TorchComm):
             return super().all_gather(full, shard)
         n = shard.numel() * shard.element_size()
         skip_self = int(full.data_ptr() + self.rank * n == shard.data_ptr())
+        if self.copy_engine if copy_engine is None else copy_engine:
+            _C.call("b2_peer_all_gather_ce", full.data_ptr(), srcs, n, self.rank, self.world, skip_self,
+                    self._stream())
+            return
         _C.call("b2_peer_all_gather", full.data_ptr(), srcs, n, self.rank, self.world, skip_self, max_blocks,
                 self._stream())
 
-    def reduce_scatter(self, shard, full, average=True, max_blocks: int = 48):
+    def reduce_scatter(self, shard, full, average=True, max_blocks: int = 64):
         fulls = self._peer_array(full) if self.world > 1 else None
         if fulls is None or shard.dtype != torch.bfloat16:
             return super().reduce_scatter(shard, full, average)
@@ -137,7 +144,7 @@ class PeerComm(TorchComm):
                 self._counter().data_ptr(), max_blocks, self._stream())
 
     def reduce_scatter_adamw(self, p, m, v, full_grad, lr, beta1, beta2, eps, wd, step, average=True,
-                             max_blocks: int = 64) -> bool:
+                             max_blocks: int = 128) -> bool:
         """Fused gradient reduce-scatter + AdamW on the owned shard. Returns False when the buffers are not
         eligible (caller then runs the two steps separately)."""
         fulls = self._peer_array(full_grad) if self.world > 1 else None
@@ -149,7 +156,7 @@ class PeerComm(TorchComm):
                 self._stream())
         return True
 
-    def all_reduce(self, t, average=True, max_blocks: int = 48):
+    def all_reduce(self, t, average=True, max_blocks: int = 64):
         bufs = self._peer_array(t) if self.world > 1 else None
         if bufs is None or t.dtype != torch.bfloat16 or t.numel() % (8 * self.world):
             return super().all_reduce(t, average)
