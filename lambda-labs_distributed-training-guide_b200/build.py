@@ -28,7 +28,7 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo", "-O3", "-std=c++17",
     "--expt-relaxed-constexpr",
-    "-Xcompiler", "-fPIC",
+    "-Xcompiler", "-fPIC", "-Xcompiler", "-fopenmp",
     "-I", str(INCLUDE), "-I", str(CSRC),
 ]
 
@@ -93,7 +93,8 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     link_dig = _digest([OBJ_DIR / (s.stem + ".sha") for s in srcs])
     if todo or not LIB_PATH.exists() or not link_stamp.exists() or link_stamp.read_text() != link_dig:
         objs = [str(OBJ_DIR / (s.stem + ".o")) for s in srcs]
-        cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", str(LIB_PATH), *objs]
+        cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-Xcompiler", "-fopenmp",
+               "-o", str(LIB_PATH), *objs, "-lgomp"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")

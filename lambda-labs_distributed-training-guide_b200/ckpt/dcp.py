@@ -41,19 +41,71 @@ def _chunk(full: torch.Tensor, mesh, rank: int, world: int):
     return _as_dtensor(full, mesh, rank, world)
 
 
+def _chunk_2d(local: torch.Tensor, strategy, name: str):
+    """(dp, tp) mesh: ``local`` is this tp rank's slice of the global tensor (already complete over dp).
+    tp shards ``tp_dim`` of the global tensor; dp shards a different dim (or dim 0 of replicated 1-D
+    tensors) when the strategy shards over dp, else it replicates."""
+    from torch.distributed.tensor import DTensor, Replicate, Shard
+
+    m = strategy.mesh
+    tp_dim = strategy.model.tp_shard_dim(name)
+    if local.dim() == 0:
+        local = local.reshape(1)
+    gshape = list(local.shape)
+    if tp_dim is not None:
+        gshape[tp_dim] *= m.tp
+    placements = [Replicate(), Shard(tp_dim) if tp_dim is not None else Replicate()]
+    piece = local
+    if strategy.shards_over_dp and m.dp > 1:
+        dp_dim = 0 if tp_dim != 0 else 1
+        lo, hi = _chunk_bounds(local.shape[dp_dim], m.dp, m.dp_rank)
+        piece = local.narrow(dp_dim, lo, hi - lo)
+        placements[0] = Shard(dp_dim)
+    piece = piece.detach().clone().contiguous()
+    stride = torch.empty(gshape, device="meta").stride()
+    return DTensor.from_local(piece, _mesh2d(strategy), placements, run_check=False, shape=torch.Size(gshape),
+                              stride=stride)
+
+
+def _local_from_2d(t, strategy, name: str):
+    """Inverse of :func:`_chunk_2d`: this tp rank's slice, complete over dp."""
+    from torch.distributed.tensor import DTensor, Replicate, Shard
+
+    if not isinstance(t, DTensor):
+        return t
+    tp_dim = strategy.model.tp_shard_dim(name)
+    return t.redistribute(placements=[Replicate(), Shard(tp_dim) if tp_dim is not None else Replicate()]).to_local()
+
+
+_MESH2D = {}
+
+
+def _mesh2d(strategy):
+    m = strategy.mesh
+    key = (strategy.device.type, m.dp, m.tp)
+    if key not in _MESH2D:
+        from torch.distributed.device_mesh import init_device_mesh
+
+        _MESH2D[key] = init_device_mesh(strategy.device.type, (m.dp, m.tp), mesh_dim_names=("dp", "tp"))
+    return _MESH2D[key]
+
+
 def build_sharded_state(strategy, mesh):
     """Walk the strategy one unit at a time and keep only this rank's dim-0 chunk of every HF-named
     tensor (parameters and AdamW moments), so the full model never has to exist on one rank."""
     rank, world = strategy.rank, strategy.world_size
+    two_d = hasattr(strategy, "mesh") and world > 1
     state = {"model": {}, "optimizer": {"state": {}, "param_groups": strategy.optimizer_param_groups()}}
     for i in range(strategy.num_units()):
         for kind in ("param", "exp_avg", "exp_avg_sq"):
             for name, full in strategy.unit_named_full(i, kind).items():
+                piece = _chunk_2d(full, strategy, name) if two_d else _chunk(full, mesh, rank, world)
                 if kind == "param":
-                    state["model"][name] = _chunk(full, mesh, rank, world)
+                    state["model"][name] = piece
                 else:
-                    st = state["optimizer"]["state"].setdefault(name, {"step": torch.tensor(float(strategy.optimizer_step_count()))})
-                    st[kind] = _chunk(full, mesh, rank, world)
+                    st = state["optimizer"]["state"].setdefault(
+                        name, {"step": torch.tensor(float(strategy.optimizer_step_count()))})
+                    st[kind] = piece
     return state
 
 
@@ -66,7 +118,7 @@ def save_sharded(exp_dir: Path, strategy, state: dict = None, lr_scheduler=None)
     exp_dir = Path(exp_dir)
     rank, world = strategy.rank, strategy.world_size
     strategy.barrier()
-    sharded = build_sharded_state(strategy, _mesh(strategy))
+    sharded = build_sharded_state(strategy, None if hasattr(strategy, "mesh") else _mesh(strategy))
     save(sharded, checkpoint_id=exp_dir / "checkpoint", no_dist=not dist.is_initialized())
     if rank == 0:
         if lr_scheduler is not None:
@@ -82,16 +134,18 @@ def load_sharded(exp_dir: Path, strategy):
     from torch.distributed.checkpoint import load
 
     exp_dir = Path(exp_dir)
-    sharded = build_sharded_state(strategy, _mesh(strategy))
+    two_d = hasattr(strategy, "mesh") and strategy.world_size > 1
+    sharded = build_sharded_state(strategy, None if hasattr(strategy, "mesh") else _mesh(strategy))
     load(sharded, checkpoint_id=exp_dir / "checkpoint", no_dist=not dist.is_initialized())
     opt_state = sharded["optimizer"]["state"]
     for i in range(strategy.num_units()):
         for kind in ("param", "exp_avg", "exp_avg_sq"):
             names = list(strategy.unit_named_full(i, kind, names_only=True))
+            unpack = (lambda t, n: _local_from_2d(t, strategy, n)) if two_d else (lambda t, n: _to_full(t))
             if kind == "param":
-                tensors = {n: _to_full(sharded["model"][n]) for n in names}
+                tensors = {n: unpack(sharded["model"][n], n) for n in names}
             else:
-                tensors = {n: _to_full(opt_state[n][kind]) for n in names}
+                tensors = {n: unpack(opt_state[n][kind], n) for n in names}
             strategy.unit_store_named(i, kind, tensors)
     steps = [float(_to_full(st["step"])) for st in opt_state.values() if "step" in st]
     strategy.set_optimizer_step_count(int(steps[0]) if steps else 0)

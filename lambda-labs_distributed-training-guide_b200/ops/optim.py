@@ -32,6 +32,25 @@ def adamw_step(p, g, m, v, lr, beta1=0.9, beta2=0.999, eps=1e-8, wd=0.01, step=1
     if use_kernels(p) and p.dtype == torch.bfloat16:
         _C.call("b2_adamw", p.data_ptr(), m.data_ptr(), v.data_ptr(), g.data_ptr(), p.numel(), lr, beta1,
                 beta2, eps, wd, step, grad_scale, max_blocks, stream(p))
+    elif (p.device.type == "cpu" and p.dtype == torch.bfloat16 and _cpu_kernel_ok()
+          and all(t.is_contiguous() for t in (p, g, m, v))):
+        # offloaded shards: native OpenMP loop over the (pinned) host buffers
+        _C.call("b2_cpu_adamw_bf16", p.data_ptr(), m.data_ptr(), v.data_ptr(), g.data_ptr(), p.numel(), lr, beta1,
+                beta2, eps, wd, step, grad_scale)
     else:
         with torch.no_grad():
             adamw_step_ref(p, g, m, v, lr, beta1, beta2, eps, wd, step, grad_scale)
+
+
+_CPU_OK = None
+
+
+def _cpu_kernel_ok() -> bool:
+    """The host AdamW lives in the same library as the CUDA kernels; it is usable wherever that loads."""
+    global _CPU_OK
+    if _CPU_OK is None:
+        try:
+            _CPU_OK = hasattr(_C.load(), "b2_cpu_adamw_bf16")
+        except Exception:
+            _CPU_OK = False
+    return _CPU_OK

@@ -81,6 +81,7 @@ def _init_tp_model(model: TPLlamaForCausalLM, cfg, device, dtype, seed):
 
 class TensorParallel(Strategy):
     name = "tp"
+    shards_over_dp = False  # replicas over dp: checkpoints shard over tp only
 
     def __init__(self, cfg, device, lr=3e-5, seed=0, dtype=torch.bfloat16, tp: Optional[int] = None,
                  activation_checkpointing: bool = False):
@@ -145,6 +146,7 @@ class TwoD(FSDP):
     """FSDP over the dp coordinate of tp-local units (chapter 07)."""
 
     name = "2d"
+    shards_over_dp = True
 
     def __init__(self, cfg, device, lr=3e-5, seed=0, dtype=torch.bfloat16, tp: int = 2, **kw):
         self.mesh = Mesh2D(tp)

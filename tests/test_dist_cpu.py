@@ -202,3 +202,35 @@ def test_2d_runs_and_learns():
     """2D (dp=2 x tp=2 on 4 processes): FSDP over dp of tp-local units; loss must fall."""
     got = run_dist("w_tp_losses", "2d", 2, 4, True, world=4)[0]
     assert got[-1] < got[0] - 0.3, got
+
+
+def w_dcp_2d(rank, world, tmp, strategy):
+    from pathlib import Path
+
+    from b200train.ckpt.dcp import load_sharded, save_sharded
+    from b200train.models import load_config
+    from b200train.parallel import make_strategy
+
+    cfg = load_config("llama-tiny")
+    eng = make_strategy(strategy, cfg, "cpu", lr=1e-3, dtype=torch.float32, tp=2)
+    dp_rank, dp = eng.data_parallel_coords()
+    ids = _batches(cfg, 1, 4, 32)[0]
+    per = 4 // dp
+    mine = ids[dp_rank * per:(dp_rank + 1) * per]
+    for _ in range(2):
+        eng.train_step({"input_ids": mine, "labels": mine})
+    save_sharded(Path(tmp), eng, state={"epoch": 0, "global_step": 2, "epoch_step": 2, "running_loss": 0.0},
+                 lr_scheduler=eng.lr_scheduler)
+    nxt = eng.train_step({"input_ids": mine, "labels": mine}).item()
+    eng2 = make_strategy(strategy, cfg, "cpu", lr=1e-3, dtype=torch.float32, tp=2, seed=11)
+    load_sharded(Path(tmp), eng2)
+    eng2.lr_scheduler.load_state_dict(torch.load(Path(tmp) / "lr_scheduler.pt"))
+    got = eng2.train_step({"input_ids": mine, "labels": mine}).item()
+    return nxt, got
+
+
+@pytest.mark.parametrize("strategy,world", [("tp", 2), ("2d", 4)])
+def test_dcp_roundtrip_tensor_parallel(strategy, world):
+    tmp = tempfile.mkdtemp()
+    nxt, got = run_dist("w_dcp_2d", tmp, strategy, world=world)[0]
+    assert abs(nxt - got) < 1e-5, (nxt, got)
