@@ -39,8 +39,11 @@ def _worker(rank, world, port, ret):
             # reduce-scatter (mean)
             shard = comm.empty(n)
             comm.reduce_scatter(shard, full, average=True)
-            ref = torch.empty(n, dtype=torch.bfloat16, device="cuda")
-            dist.reduce_scatter_tensor(ref, ref_full, op=dist.ReduceOp.AVG)
+            # oracle: exact fp32 mean through NCCL (a bf16 NCCL reduction rounds at every hop)
+            exact = ref_full.float()
+            dist.all_reduce(exact, op=dist.ReduceOp.SUM)
+            exact /= world
+            ref = exact[rank * n:(rank + 1) * n].to(torch.bfloat16)
             torch.cuda.synchronize()
             errs[f"rs{it}"] = (shard.float() - ref.float()).abs().max().item()
             # all-gather of the reduced shards
@@ -55,8 +58,7 @@ def _worker(rank, world, port, ret):
             ar = comm.empty(n * world)
             ar.copy_(ref_full)
             comm.all_reduce(ar, average=True)
-            ref_ar = ref_full.clone()
-            dist.all_reduce(ref_ar, op=dist.ReduceOp.AVG)
+            ref_ar = exact.to(torch.bfloat16)
             torch.cuda.synchronize()
             errs[f"ar{it}"] = (ar.float() - ref_ar.float()).abs().max().item()
             # fused reduce-scatter + AdamW vs separate steps
