@@ -59,6 +59,11 @@ class Comm:
     def all_gather(self, full: torch.Tensor, shard: torch.Tensor):
         full.copy_(shard)
 
+    def all_gather_inplace(self, full: torch.Tensor):
+        """Every rank owns slice ``rank`` of its ``full`` buffer; fill the other slices from their owners."""
+        n = full.numel() // self.world
+        self.all_gather(full, full[self.rank * n:(self.rank + 1) * n])
+
     def reduce_scatter(self, shard: torch.Tensor, full: torch.Tensor, average: bool = True):
         shard.copy_(full)
 

@@ -136,9 +136,8 @@ class DDP(Strategy):
         if not self.zero1:
             return
         u = self.units[i]
-        n = u.numel // self.W
         self.comm.stream_barrier()  # every owner finished updating its slice
-        self.comm.all_gather(u.flat_param, u.flat_param[self.R * n:(self.R + 1) * n])
+        self.comm.all_gather_inplace(u.flat_param)
 
     # ---- phases ---------------------------------------------------------------------------------------
     def backward(self, loss):

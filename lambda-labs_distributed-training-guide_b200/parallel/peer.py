@@ -135,6 +135,20 @@ class PeerComm(TorchComm):
         _C.call("b2_peer_all_gather", full.data_ptr(), srcs, n, self.rank, self.world, skip_self, max_blocks,
                 self._stream())
 
+    def all_gather_inplace(self, full, max_blocks: int = 64):
+        """In-place variant: slice q is pulled from rank q's copy of the same buffer (the owned slices sit
+        at different offsets on different ranks, so the sources are ``peer_base[q] + q * slice``)."""
+        bases = self._peer_array(full) if self.world > 1 else None
+        if bases is None:
+            return super().all_gather_inplace(full)
+        n = full.numel() // self.world * full.element_size()
+        srcs = (ctypes.c_void_p * self.world)(*[bases[q] + q * n for q in range(self.world)])
+        if self.copy_engine:
+            _C.call("b2_peer_all_gather_ce", full.data_ptr(), srcs, n, self.rank, self.world, 1, self._stream())
+        else:
+            _C.call("b2_peer_all_gather", full.data_ptr(), srcs, n, self.rank, self.world, 1, max_blocks,
+                    self._stream())
+
     def reduce_scatter(self, shard, full, average=True, max_blocks: int = 64):
         fulls = self._peer_array(full) if self.world > 1 else None
         if fulls is None or shard.dtype != torch.bfloat16:
