@@ -37,6 +37,29 @@ struct EpiArgs {
   int ldc;
 };
 
+// ---- fused compute + collective variants (tensor parallel, see b2_gemm_ag / b2_gemm_rs) ----------
+// kFuse = 0: plain GEMM.
+// kFuse = 1 (all-gather -> GEMM): the rows of A arrive from the peers in `W` chunks of `rows_per_rank`
+//   rows while the kernel runs; chunk r is usable once flags[r] >= epoch. Tiles are visited starting
+//   with the local chunk and the TMA producer waits for a chunk's flag before its first load.
+// kFuse = 2 (GEMM -> reduce-scatter): row block r of C belongs to rank r. Each tile is stored with TMA
+//   straight into slot `rank` of the owner's (peer-mapped) staging buffer, so the scatter traffic
+//   overlaps the remaining main loop; the owner sums its W slots afterwards.
+constexpr int kMaxTP = 8;
+struct NoFuse {};
+struct FuseAWait {
+  const uint32_t* flags;
+  uint32_t epoch;
+  int rows_per_rank, rank, W;
+};
+struct FuseScatterC {
+  CUtensorMap cm[kMaxTP];  // cm[r]: rank r's slot `rank`, shape [rows_per_rank, N]
+  int rows_per_rank, rank, W;
+};
+template <class F> struct FuseKind { static constexpr int v = 0; };
+template <> struct FuseKind<FuseAWait> { static constexpr int v = 1; };
+template <> struct FuseKind<FuseScatterC> { static constexpr int v = 2; };
+
 template <int kCta, int BN>
 struct GemmCfg {
   static constexpr int kABytes = BM * BK * 2;
@@ -57,11 +80,13 @@ __device__ __forceinline__ float gelu_new(float x) {
   return 0.5f * x * (1.f + t);
 }
 
-template <int kCta, bool kAK, bool kBK, int kEpi, int BN>
+template <int kCta, bool kAK, bool kBK, int kEpi, int BN, class Fuse = NoFuse>
 __global__ void __launch_bounds__(256, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const __grid_constant__ CUtensorMap tmC, int M, int N, int K, EpiArgs epi) {
+                 const __grid_constant__ CUtensorMap tmC, int M, int N, int K, EpiArgs epi,
+                 const __grid_constant__ Fuse fuse) {
   using Cfg = GemmCfg<kCta, BN>;
+  constexpr int kFuse = FuseKind<Fuse>::v;
   constexpr int kStages = Cfg::kStages;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // swizzle-128B operands need 1024B alignment; align by hand (slack is included in kSmemBytes)
@@ -120,6 +145,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int r = t - g * per_group;
     mb = first_m + r % gsz;
     nb = r / gsz;
+    if constexpr (kFuse == 1) {
+      // start with the m-blocks of the local chunk (already present), then the peers in ring order
+      const int blocks_per_rank = fuse.rows_per_rank / (BM * kCta);
+      mb = (mb + fuse.rank * blocks_per_rank) % num_m;
+    }
   };
 
   if (warp == 0) {
@@ -132,6 +162,19 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         tile_coord(t, mb, nb);
         const int m0 = mb * tile_m + (int)cta_rank * BM;
         const int n0 = nb * BN + (int)cta_rank * (BN / kCta);
+        if constexpr (kFuse == 1) {
+          // rows of this m-block come from rank `owner`: wait until its chunk has landed
+          const int owner = min(m0 / fuse.rows_per_rank, fuse.W - 1);
+          if (owner != fuse.rank) {
+            uint32_t v;
+            do {
+              asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(fuse.flags + owner)
+                           : "memory");
+            } while ((int32_t)(v - fuse.epoch) < 0);
+            // the chunk was written by the copy engine: order it before the async-proxy (TMA) reads
+            asm volatile("fence.proxy.async.global;" ::: "memory");
+          }
+        }
         for (int kb = 0; kb < num_k; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           if (leader) mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes * kCta);
@@ -269,7 +312,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         fence_proxy_async_smem();
         named_bar_sync(1, 128);
         if (epi_leader) {
-          if (col0 < N && m0 < M) tma_store_2d(&tmC, sc, col0, m0);
+          if (col0 < N && m0 < M) {
+            if constexpr (kFuse == 2) {
+              const int owner = min(m0 / fuse.rows_per_rank, fuse.W - 1);
+              tma_store_2d(&fuse.cm[owner], sc, col0, m0 - owner * fuse.rows_per_rank);
+            } else {
+              tma_store_2d(&tmC, sc, col0, m0);
+            }
+          }
           tma_store_commit();
         }
         ++chunk_ctr;
@@ -380,9 +430,10 @@ int sm_count() {
   return n;
 }
 
-template <int kCta, bool kAK, bool kBK, int kEpi, int BN>
+template <int kCta, bool kAK, bool kBK, int kEpi, int BN, class Fuse = NoFuse>
 static int launch_gemm(void* C, const void* A, const void* B, int M, int N, int K, int lda, int ldb,
-                       int ldc, const EpiArgs& epi, int max_ctas, cudaStream_t stream) {
+                       int ldc, const EpiArgs& epi, int max_ctas, cudaStream_t stream,
+                       const Fuse& fuse = Fuse()) {
   using Cfg = GemmCfg<kCta, BN>;
   CUtensorMap tmA, tmB, tmC;
   int rc;
@@ -392,10 +443,14 @@ static int launch_gemm(void* C, const void* A, const void* B, int M, int N, int 
   if constexpr (kBK) rc = make_tmap_2d_bf16(&tmB, B, N, K, ldb, BN / kCta, BK);
   else rc = make_tmap_mn_bf16(&tmB, B, K, N, ldb, BK, BN / kCta / 64);
   if (rc) return rc;
-  rc = make_tmap_2d_bf16(&tmC, C, M, N, ldc, BM, kEpiChunk);
-  if (rc) return rc;
+  if constexpr (FuseKind<Fuse>::v == 2) {
+    tmC = fuse.cm[0];  // unused by the scatter variant; keep the parameter well formed
+  } else {
+    rc = make_tmap_2d_bf16(&tmC, C, M, N, ldc, BM, kEpiChunk);
+    if (rc) return rc;
+  }
 
-  auto kern = gemm_bf16_kernel<kCta, kAK, kBK, kEpi, BN>;
+  auto kern = gemm_bf16_kernel<kCta, kAK, kBK, kEpi, BN, Fuse>;
   static bool attr_set = false;
   if (!attr_set) {
     B2_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -422,7 +477,7 @@ static int launch_gemm(void* C, const void* A, const void* B, int M, int N, int 
   attrs[0].val.clusterDim.z = 1;
   cfg.attrs = attrs;
   cfg.numAttrs = 1;
-  B2_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, M, N, K, epi));
+  B2_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, M, N, K, epi, fuse));
   return 0;
 }
 
@@ -462,11 +517,136 @@ static int dispatch_layout(void* C, const void* A, const void* B, int M, int N, 
   return -2;
 }
 
+typedef CUresult (*WriteValue32Fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+static WriteValue32Fn get_write_value() {
+  static WriteValue32Fn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuStreamWriteValue32", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<WriteValue32Fn>(p);
+  });
+  return fn;
+}
+
+// out[i] = sum_w slots[w * n + i]   (bf16, fp32 accumulate): the local half of a scattered reduction
+__global__ void sum_slots_kernel(uint4* __restrict__ out, const uint4* __restrict__ slots, size_t n16,
+                                 int W) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16;
+       i += (size_t)gridDim.x * blockDim.x) {
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int w = 0; w < W; ++w) {
+      const uint4 v = slots[(size_t)w * n16 + i];
+      const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = unpack_bf16(u[j]);
+        acc[2 * j] += f.x;
+        acc[2 * j + 1] += f.y;
+      }
+    }
+    uint4 o;
+    o.x = pack_bf16(acc[0], acc[1]);
+    o.y = pack_bf16(acc[2], acc[3]);
+    o.z = pack_bf16(acc[4], acc[5]);
+    o.w = pack_bf16(acc[6], acc[7]);
+    out[i] = o;
+  }
+}
+
 }  // namespace b2
 
 extern "C" {
 
 const char* b2_last_error() { return b2::last_error(); }
+
+// ---- tensor-parallel fused GEMMs ---------------------------------------------------------------
+// All-gather -> GEMM. A [M, K] is a local buffer whose row chunks (rows_per_rank each) are filled by
+// b2_peer_all_gather_chunks on another stream while this kernel runs; flags[r] >= epoch marks chunk r
+// as present. C[M, N] = A * B^T (b_mn = 1: B stored [K, N]).
+int b2_gemm_ag(void* C, const void* A, const void* B, int M, int N, int K, int b_mn, int lda, int ldb,
+               int ldc, const unsigned int* flags, unsigned int epoch, int rows_per_rank, int rank,
+               int W, cudaStream_t stream) {
+  using namespace b2;
+  B2_REQUIRE(W >= 1 && W <= kMaxTP && rows_per_rank * W == M, "gemm_ag: M=%d != W=%d x rows=%d", M, W,
+             rows_per_rank);
+  B2_REQUIRE(rows_per_rank % (2 * BM) == 0, "gemm_ag: rows per rank (%d) must be a multiple of %d",
+             rows_per_rank, 2 * BM);
+  FuseAWait f;
+  f.flags = flags;
+  f.epoch = epoch;
+  f.rows_per_rank = rows_per_rank;
+  f.rank = rank;
+  f.W = W;
+  EpiArgs epi = {};
+  if (b_mn)
+    return launch_gemm<2, true, false, EPI_NONE, 256, FuseAWait>(C, A, B, M, N, K, lda, ldb, ldc, epi,
+                                                                 0, stream, f);
+  return launch_gemm<2, true, true, EPI_NONE, 256, FuseAWait>(C, A, B, M, N, K, lda, ldb, ldc, epi, 0,
+                                                              stream, f);
+}
+
+// GEMM -> reduce-scatter (scatter half). slot_bases[r]: address of slot `rank` in rank r's staging
+// buffer (peer-mapped), each slot [rows_per_rank, ld_slot >= N]. Row block r of A * B^T is TMA-stored
+// into slot_bases[r]. After a cross-rank barrier the owner sums its W slots (b2_sum_slots).
+int b2_gemm_rs(void* const* slot_bases, const void* A, const void* B, int M, int N, int K, int b_mn,
+               int lda, int ldb, int ld_slot, int rows_per_rank, int rank, int W,
+               cudaStream_t stream) {
+  using namespace b2;
+  B2_REQUIRE(W >= 1 && W <= kMaxTP && rows_per_rank * W == M, "gemm_rs: M=%d != W=%d x rows=%d", M, W,
+             rows_per_rank);
+  B2_REQUIRE(rows_per_rank % (2 * BM) == 0, "gemm_rs: rows per rank (%d) must be a multiple of %d",
+             rows_per_rank, 2 * BM);
+  FuseScatterC f;
+  for (int r = 0; r < kMaxTP; ++r) {
+    const int src = r < W ? r : 0;
+    if (int rc = make_tmap_2d_bf16(&f.cm[r], slot_bases[src], rows_per_rank, N, ld_slot, BM, kEpiChunk))
+      return rc;
+  }
+  f.rows_per_rank = rows_per_rank;
+  f.rank = rank;
+  f.W = W;
+  EpiArgs epi = {};
+  if (b_mn)
+    return launch_gemm<2, true, false, EPI_NONE, 256, FuseScatterC>(nullptr, A, B, M, N, K, lda, ldb,
+                                                                    ld_slot, epi, 0, stream, f);
+  return launch_gemm<2, true, true, EPI_NONE, 256, FuseScatterC>(nullptr, A, B, M, N, K, lda, ldb,
+                                                                 ld_slot, epi, 0, stream, f);
+}
+
+int b2_sum_slots(void* out, const void* slots, size_t n_elems, int W, cudaStream_t stream) {
+  using namespace b2;
+  B2_REQUIRE(n_elems % 8 == 0, "sum_slots: n not a multiple of 8");
+  const size_t n16 = n_elems / 8;
+  int blocks = (int)((n16 + 255) / 256);
+  if (blocks > sm_count() * 8) blocks = sm_count() * 8;
+  if (blocks < 1) blocks = 1;
+  sum_slots_kernel<<<blocks, 256, 0, stream>>>((uint4*)out, (const uint4*)slots, n16, W);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// Copy-engine all-gather in chunks with a completion flag per chunk: for every peer r != rank the rows
+// of chunk r are copied from peer_bases[r] + r * chunk_bytes into dst + r * chunk_bytes and then
+// flags[r] = epoch is written by the stream (cuStreamWriteValue32, no SM involved), which is what
+// b2_gemm_ag polls.
+int b2_peer_all_gather_chunks(void* dst, void* const* peer_bases, size_t chunk_bytes, int rank, int W,
+                              unsigned int* flags, unsigned int epoch, cudaStream_t stream) {
+  using namespace b2;
+  WriteValue32Fn wv = get_write_value();
+  B2_REQUIRE(wv != nullptr, "cuStreamWriteValue32 entry point unavailable");
+  for (int k = 1; k < W; ++k) {
+    const int peer = (rank + k) % W;
+    B2_CUDA_CHECK(cudaMemcpyAsync(static_cast<char*>(dst) + (size_t)peer * chunk_bytes,
+                                  static_cast<const char*>(peer_bases[peer]) + (size_t)peer * chunk_bytes,
+                                  chunk_bytes, cudaMemcpyDeviceToDevice, stream));
+    CUresult r = wv((CUstream)stream, (CUdeviceptr)(flags + peer), epoch, 0);
+    B2_REQUIRE(r == CUDA_SUCCESS, "cuStreamWriteValue32 failed: %d", (int)r);
+  }
+  return 0;
+}
 
 // C[M,N] (row-major, ldc) = epilogue(A * B^T) with A logically [M,K], B logically [N,K].
 //   a_mn = 0: A stored [M,K] (lda = row stride); a_mn = 1: A stored [K,M] (rows of length M).

@@ -51,6 +51,10 @@ def _declare(lib):
         "b2_ce_bwd": [P, P, P, P, I, I, I, I, I, F, P, P],
         "b2_adamw": [P, P, P, P, Z, F, F, F, F, F, I, F, I, P],
         "b2_add": [P, P, P, Z, P],
+        "b2_gemm_ag": [P, P, P, I, I, I, I, I, I, I, P, ctypes.c_uint, I, I, I, P],
+        "b2_gemm_rs": [P, P, P, I, I, I, I, I, I, I, I, I, I, P],
+        "b2_sum_slots": [P, P, Z, I, P],
+        "b2_peer_all_gather_chunks": [P, P, Z, I, I, P, ctypes.c_uint, P],
         "b2_cpu_adamw_bf16": [P, P, P, P, Z, F, F, F, F, F, I, F],
         "b2_peer_barrier": [P, I, I, I, ctypes.c_uint, P],
         "b2_peer_all_gather": [P, P, Z, I, I, I, I, P],

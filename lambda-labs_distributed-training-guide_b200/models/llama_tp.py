@@ -21,7 +21,8 @@ import torch
 from torch import nn
 
 from .. import ops
-from ..parallel.tp_ops import TPGroup, all_gather_seq, hidden_to_seq, reduce_scatter_seq
+from ..parallel.tp_fused import colwise, rowwise
+from ..parallel.tp_ops import TPGroup, hidden_to_seq
 from .config import ModelConfig
 from .llama import CausalLMOutput, LlamaForCausalLM
 
@@ -65,12 +66,15 @@ class TPLlamaForCausalLM(LlamaForCausalLM):
 
     def _tp_layer(self, layer, h, delta, ctx):
         tp = self.tp
+        att, mlp = layer.self_attn, layer.mlp
         x, h = layer.input_layernorm(delta if delta is not None else h, h if delta is not None else None)
-        a = layer.self_attn(all_gather_seq(x, tp), ctx)          # [T, H] partial sums over local heads
-        a = reduce_scatter_seq(a, tp)                             # [T/tp, H]
+        qkv = colwise(x, att.qkv_proj.weight, tp)                 # all-gather(seq) -> GEMM, local heads
+        qkv = ops.rope_qk(qkv, ctx.cos, ctx.sin, ctx.pos, att.n_q + att.n_kv, att.D, ctx.seq_len)
+        o = ops.attention(qkv, ctx.cu_seqlens, ctx.max_seqlen, att.n_q, att.n_kv, att.D)
+        a = rowwise(o, att.o_proj.weight, tp)                     # GEMM -> reduce-scatter(seq): [T/tp, H]
         x, h = layer.post_attention_layernorm(a, h)
-        m = layer.mlp(all_gather_seq(x, tp))
-        return h, reduce_scatter_seq(m, tp)
+        gu = colwise(x, mlp.gate_up_proj.weight, tp)
+        return h, rowwise(ops.swiglu(gu), mlp.down_proj.weight, tp)
 
     def forward(self, input_ids, labels=None, attention_mask=None, position_ids=None, **_):
         B, S = input_ids.shape
@@ -90,7 +94,7 @@ class TPLlamaForCausalLM(LlamaForCausalLM):
 
         def head(a, b=None):
             x, _ = self.model.norm(b, a) if b is not None else self.model.norm(a)
-            logits = ops.linear(all_gather_seq(x, tp), self.lm_head.weight)     # [T, V/tp]
+            logits = colwise(x, self.lm_head.weight, tp)                        # [T, V/tp]
             if shifted is None:
                 return logits
             return ops.vocab_parallel_cross_entropy(logits, shifted, self.vocab_start, tp.group)

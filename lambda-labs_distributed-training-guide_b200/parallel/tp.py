@@ -14,6 +14,8 @@ from __future__ import annotations
 
 from typing import Optional
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -51,8 +53,15 @@ class Mesh2D:
                 if t == self.tp_rank:
                     self.dp_group = g
 
-    def tp_handle(self) -> TPGroup:
-        return TPGroup(self.tp_group, self.tp_rank, self.tp)
+    def tp_handle(self, device=None, fused: bool = True) -> TPGroup:
+        h = TPGroup(self.tp_group, self.tp_rank, self.tp)
+        h.fused = None
+        if (fused and self.tp > 1 and device is not None and torch.device(device).type == "cuda"
+                and os.environ.get("B200TRAIN_TP_FUSED", "1") == "1" and self.tp <= 8):
+            from .tp_fused import FusedTP
+
+            h.fused = FusedTP(self.tp_group, self.tp_rank, self.tp, device)
+        return h
 
     def dp_comm(self) -> Comm:
         if self.world == 1 or self.dp == 1:
@@ -88,7 +97,7 @@ class TensorParallel(Strategy):
         super().__init__(cfg, device, lr, seed, dtype)
         world = dist.get_world_size() if dist.is_initialized() else 1
         self.mesh = Mesh2D(tp or world)
-        self.tpg = self.mesh.tp_handle()
+        self.tpg = self.mesh.tp_handle(self.device)
         self.dp_comm = self.mesh.dp_comm()
         self.act_ckpt = activation_checkpointing
         self.model = TPLlamaForCausalLM(cfg, self.tpg, dtype=dtype, device=self.device)
@@ -150,7 +159,7 @@ class TwoD(FSDP):
 
     def __init__(self, cfg, device, lr=3e-5, seed=0, dtype=torch.bfloat16, tp: int = 2, **kw):
         self.mesh = Mesh2D(tp)
-        self.tpg = self.mesh.tp_handle()
+        self.tpg = self.mesh.tp_handle(device)
         kw.pop("comm", None)
         super().__init__(cfg, device, lr=lr, seed=seed, dtype=dtype, comm=self.mesh.dp_comm(), **kw)
 
