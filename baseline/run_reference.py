@@ -50,7 +50,7 @@ def _load_module(path: Path, name: str):
 
 
 def run_reference(chapter: str, hf_config: dict, batch_size: int, seq_len: int, steps: int, warmup: int,
-                  extra_args=()) -> dict:
+                  extra_args=(), dp_size=None) -> dict:
     """Run ``warmup + steps`` optimizer steps of the reference chapter; returns timing of the last
     ``steps`` (CUDA events, max over ranks) plus the end-to-end host-clock figure."""
     import torch
@@ -81,7 +81,8 @@ def run_reference(chapter: str, hf_config: dict, batch_size: int, seq_len: int, 
                 p.unlink()
 
     vocab = hf_config["vocab_size"]
-    n_items = (warmup + steps) * batch_size * world
+    dp = dp_size or world            # chapters 06/07 sample over the dp coordinate only
+    n_items = (warmup + steps) * batch_size * dp
 
     class SyntheticTokens(torch.utils.data.Dataset):
         def __len__(self):
@@ -148,7 +149,7 @@ def run_reference(chapter: str, hf_config: dict, batch_size: int, seq_len: int, 
     if dist.is_initialized() and world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     total_dev_ms, e2e_ms = t.tolist()
-    tokens = world * batch_size * seq_len * steps
+    tokens = dp * batch_size * seq_len * steps
     return {
         "ms_per_step": total_dev_ms / steps,
         "tokens_per_s": tokens / (total_dev_ms / 1e3),
