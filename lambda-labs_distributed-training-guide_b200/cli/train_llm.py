@@ -79,6 +79,10 @@ def get_parser(chapter: str = "generic") -> argparse.ArgumentParser:
     p.add_argument("--deterministic", action="store_true")
     p.add_argument("--packed", action="store_true", help="packed rows: derive position ids per document")
     p.add_argument("--max-steps", default=None, type=int, help="stop after this many optimizer steps")
+    p.add_argument("--pretrained", default=None,
+                   help="local directory with *.safetensors to start from (reference: from_pretrained, ch05 / ch00)")
+    p.add_argument("--add-tokens", default=28_683 if chapter == "00-rime" else 0, type=int,
+                   help="grow the vocabulary by this many tokens (resize_token_embeddings, ch00)")
     return p
 
 
@@ -133,6 +137,8 @@ def main(chapter: str = "generic", argv=None):
     first = (local_rank == 0) if os.environ.get("B200TRAIN_NODE_LOCAL_CACHE") else (rank == 0)
     with rank_ordered(first):
         config = load_config(args.model_name)
+    if args.add_tokens and (args.pretrained or chapter != "00-rime"):
+        config.vocab_size += args.add_tokens
     LOGGER.info(f"{config.num_parameters()} model parameters")
     LOGGER.info(f"Before sharding: {get_mem_stats(device)}")
 
@@ -153,6 +159,11 @@ def main(chapter: str = "generic", argv=None):
             tp = min(world_size, max(per_node, 1))
         kw.update(tp=tp, activation_checkpointing=act == "on")
     engine = make_strategy(strategy_name, config, device, **kw)
+    if args.pretrained and not ckpt.has_checkpoint(Path(args.save_dir) / args.experiment_name):
+        from ..models.pretrained import load_pretrained
+
+        n_loaded = load_pretrained(engine, args.pretrained)
+        LOGGER.info(f"loaded {n_loaded} pretrained tensors from {args.pretrained}")
     LOGGER.info(f"After sharding: {get_mem_stats(device)}")
 
     with rank_ordered(first):

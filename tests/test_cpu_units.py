@@ -193,3 +193,27 @@ def test_elastic_toy_restarts_and_resumes(tmp_path):
     assert r.returncode == 0, r.stderr[-2000:]
     assert json.loads(state.read_text())["num_steps"] == 6
     assert "resuming at step 3" in (r.stdout + r.stderr)
+
+
+def test_pretrained_roundtrip_and_vocab_growth(tmp_path):
+    """save_pretrained -> load_pretrained into a differently-initialised FSDP engine reproduces the loss;
+    loading into a model with added tokens fills the new rows with the mean embedding."""
+    from b200train.models import load_config
+    from b200train.models.pretrained import load_pretrained, save_pretrained
+    from b200train.parallel import make_strategy
+
+    cfg = load_config("llama-tiny")
+    a = make_strategy("single", cfg, "cpu", dtype=torch.float32, seed=1)
+    save_pretrained(a, tmp_path / "ckpt")
+    ids = torch.randint(0, cfg.vocab_size, (2, 32))
+    ref = a.forward({"input_ids": ids, "labels": ids}).loss.item()
+    b = make_strategy("fsdp", cfg, "cpu", dtype=torch.float32, seed=2)
+    assert load_pretrained(b, tmp_path / "ckpt") > 0
+    assert abs(b.forward({"input_ids": ids, "labels": ids}).loss.item() - ref) < 1e-5
+    big = load_config("llama-tiny")
+    big.vocab_size += 16
+    c = make_strategy("single", big, "cpu", dtype=torch.float32, seed=3)
+    load_pretrained(c, tmp_path / "ckpt")
+    emb = c.model.model.embed_tokens.weight
+    assert torch.allclose(emb[-1], a.model.model.embed_tokens.weight.mean(0), atol=1e-6)
+    assert torch.equal(emb[:cfg.vocab_size], a.model.model.embed_tokens.weight)
