@@ -31,7 +31,9 @@ def main(argv=None):
     ap.add_argument("--fail-at-step", type=int, default=None)
     ap.add_argument("--fail-rank", type=int, default=0)
     args = ap.parse_args(argv)
-    dist.init_process_group("gloo")
+    import datetime
+
+    dist.init_process_group("gloo", timeout=datetime.timedelta(seconds=60))
     rank, world = dist.get_rank(), dist.get_world_size()
     path = Path(args.state_file)
     state = json.loads(path.read_text()) if path.exists() else {"num_steps": 0}

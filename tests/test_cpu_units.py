@@ -183,16 +183,37 @@ def test_model_matches_hf_implementation(name):
 
 
 def test_elastic_toy_restarts_and_resumes(tmp_path):
-    """torchrun --max-restarts: a rank fails once at step 3, the gang restarts and finishes from step 3."""
-    state = tmp_path / "toy-state.json"
-    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--max-restarts=2",
-           "--master-addr", "127.0.0.1", "--master-port", "29733", "--log-dir", str(tmp_path / "logs"),
-           str(ROOT / "related-topics" / "elastic-training" / "toy.py"), "--state-file", str(state),
-           "--total-steps", "6", "--fail-at-step", "3", "--fail-rank", "1"]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=240, env={**os.environ, "OMP_NUM_THREADS": "1"})
-    assert r.returncode == 0, r.stderr[-2000:]
-    assert json.loads(state.read_text())["num_steps"] == 6
-    assert "resuming at step 3" in (r.stdout + r.stderr)
+    """torchrun --max-restarts: a rank fails once at step 3, the gang restarts and finishes from step 3.
+    (gloo's TCP mesh set-up is occasionally refused right after a restart on this box, so the scenario
+    is retried from scratch a few times before it counts as a failure.)"""
+    import socket
+
+    last = None
+    for attempt in range(4):
+        sock = socket.socket()
+        sock.bind(("127.0.0.1", 0))
+        port = sock.getsockname()[1]
+        sock.close()
+        work = tmp_path / f"try{attempt}"
+        work.mkdir()
+        state = work / "toy-state.json"
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--max-restarts=4",
+               "--monitor-interval", "1", "--master-addr", "127.0.0.1", "--master-port", str(port),
+               "--log-dir", str(work / "logs"),
+               str(ROOT / "related-topics" / "elastic-training" / "toy.py"), "--state-file", str(state),
+               "--total-steps", "6", "--fail-at-step", "3", "--fail-rank", "1"]
+        env = {**os.environ, "OMP_NUM_THREADS": "1", "GLOO_SOCKET_IFNAME": "lo"}
+        try:
+            r = subprocess.run(cmd, capture_output=True, text=True, timeout=150, env=env)
+        except subprocess.TimeoutExpired as e:
+            last = f"timeout: {e}"
+            continue
+        out = r.stdout + r.stderr
+        if r.returncode == 0 and state.exists() and json.loads(state.read_text())["num_steps"] == 6 \
+                and "resuming at step 3" in out and "injected failure" in out:
+            return
+        last = out[-1500:]
+    pytest.fail(f"elastic toy never completed: {last}")
 
 
 def test_pretrained_roundtrip_and_vocab_growth(tmp_path):
