@@ -39,6 +39,10 @@ def main():
     ap.add_argument("--batch", type=int, default=None)
     args = ap.parse_args()
     c = CONFIGS[args.config]
+    if c["kw"].get("cpu_offload"):
+        # host AdamW threads per rank (the reference uses OMP_NUM_THREADS=26 on 8 ranks per node)
+        world_env = int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("WORLD_SIZE", "1")))
+        os.environ["OMP_NUM_THREADS"] = str(max(1, (os.cpu_count() or 8) // world_env - 2))
     import torch
     import torch.distributed as dist
 

@@ -138,6 +138,14 @@ class FSDP(Strategy):
         self._local_acc = {}      # unit -> unreduced gradient accumulator (no_sync)
         self._stepped = set()     # units already updated inside this backward (fuse_optimizer)
         self.comm_stream = torch.cuda.Stream(self.device) if self.is_cuda else None
+        # CPU offload: the host AdamW of a unit starts on a worker thread as soon as its gradient shard
+        # has landed in pinned memory, overlapping the rest of backward (the reference steps after it)
+        self._cpu_worker = None
+        self._cpu_jobs = []
+        if cpu_offload and self.is_cuda:
+            from concurrent.futures import ThreadPoolExecutor
+
+            self._cpu_worker = ThreadPoolExecutor(max_workers=1)
         self.model.unit_runner = self._runner
         self.model.train()
 
@@ -322,9 +330,22 @@ class FSDP(Strategy):
             else:
                 self.comm.reduce_scatter(self.shard_grad[i], full, average=True)
             done = self._record(self.comm_stream)
+        if self._cpu_worker is not None:
+            self._submit_cpu_step(i, done)
         self.grad_pool.release(slot, done)
         if self.fuse_optimizer:
             self._fused_step(i, done)
+
+    def _submit_cpu_step(self, i, landed):
+        if not self._stepped and not self._cpu_jobs:
+            self.optimizer.begin_step()
+        self._stepped.add(i)
+
+        def job():
+            landed.synchronize()          # the D2H copy of this unit's gradient shard has finished
+            self.optimizer.step_unit(i, grad=self.shard_grad[i], param=self.shard_param[i])
+
+        self._cpu_jobs.append(self._cpu_worker.submit(job))
 
     def _fused_step(self, i, after_event):
         """Sharded AdamW for unit ``i`` on the side stream as soon as its gradient shard is final."""
@@ -370,6 +391,9 @@ class FSDP(Strategy):
     def optimizer_step(self):
         if self.is_cuda:
             if self.cpu_offload:
+                for j in self._cpu_jobs:          # host updates started during backward
+                    j.result()
+                self._cpu_jobs.clear()
                 self.comm_stream.synchronize()   # gradient shards must have landed in host memory
             else:
                 torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
