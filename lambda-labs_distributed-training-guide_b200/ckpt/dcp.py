@@ -11,7 +11,7 @@ rows, so saving / loading re-chunks one unit at a time through the strategy's co
 from __future__ import annotations
 
 from pathlib import Path
-from typing import Dict
+
 
 import torch
 import torch.distributed as dist

@@ -8,7 +8,6 @@ import argparse
 import os
 import time
 
-import torch
 
 from .datasets import SyntheticTokens
 from .loader import make_dataloader

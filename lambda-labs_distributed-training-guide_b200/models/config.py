@@ -8,7 +8,7 @@ Reference: ``AutoConfig.from_pretrained(args.model_name, use_cache=False)``
 from __future__ import annotations
 
 import json
-from dataclasses import asdict, dataclass, field
+from dataclasses import asdict, dataclass
 from pathlib import Path
 from typing import Optional
 

@@ -31,12 +31,41 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn=False, b_mn=False, out=None, 
     M, K = (a.shape[1], a.shape[0]) if a_mn else (a.shape[0], a.shape[1])
     N, Kb = (b.shape[1], b.shape[0]) if b_mn else (b.shape[0], b.shape[1])
     assert K == Kb, f"gemm: inner dims differ ({K} vs {Kb})"
+    if (a_mn and M % 64) or (b_mn and N % 64):
+        return _gemm_padded(a, b, a_mn, b_mn, out, epilogue, bias, config, max_ctas, M, N)
     if out is None:
         out = torch.empty((M, N), dtype=torch.bfloat16, device=a.device)
     assert out.shape == (M, N) and out.stride(1) == 1
     _C.call("b2_gemm_bf16", out.data_ptr(), a.data_ptr(), b.data_ptr(), M, N, K, int(a_mn), int(b_mn),
             a.stride(0), b.stride(0), out.stride(0), epilogue, _C.ptr(bias),
             GEMM_CONFIG if config is None else config, max_ctas, stream(a))
+    return out
+
+
+def _gemm_padded(a, b, a_mn, b_mn, out, epilogue, bias, config, max_ctas, M, N):
+    """MN-major operands are fetched in 64-element atoms: pad their contiguous extent to a multiple of 64
+    with zeros (e.g. a vocabulary shard of 16032 columns under tp = 8), run, and keep the valid block."""
+    assert epilogue in (EPI_NONE, EPI_ACCUM) and bias is None
+    Mp, Np = (M + 63) // 64 * 64, (N + 63) // 64 * 64
+    if a_mn and Mp != M:
+        ap = torch.zeros((a.shape[0], Mp), dtype=a.dtype, device=a.device)
+        ap[:, :M] = a
+        a = ap
+    else:
+        Mp = M
+    if b_mn and Np != N:
+        bp = torch.zeros((b.shape[0], Np), dtype=b.dtype, device=b.device)
+        bp[:, :N] = b
+        b = bp
+    else:
+        Np = N
+    tmp = gemm(a, b, a_mn=a_mn, b_mn=b_mn, config=config, max_ctas=max_ctas)[:M, :N]
+    if out is None:
+        return tmp.contiguous()
+    if epilogue == EPI_ACCUM:
+        out.add_(tmp)
+    else:
+        out.copy_(tmp)
     return out
 
 

@@ -138,8 +138,6 @@ class Strategy:
     @torch.no_grad()
     def unit_named_full(self, i: int, kind: str, names_only: bool = False):
         if names_only:
-            u = self.units[i]
-            probe = torch.empty(u.numel, dtype=self.dtype, device="meta") if False else None
             return self._named_views(i, self._names_probe(i)).keys()
         return self._named_views(i, self._unit_full_flat(i, kind))
 

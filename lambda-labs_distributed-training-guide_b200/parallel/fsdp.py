@@ -35,6 +35,12 @@ from .hooks import run_unit
 from .optimizer import FlatAdamW
 
 
+import os
+
+# blocks given to an AdamW launched beside backward compute (co-resident with the persistent GEMM CTAs)
+_FUSED_ADAMW_BLOCKS = int(os.environ.get("B200TRAIN_FUSED_ADAMW_BLOCKS", "96"))
+
+
 class _BufferPool:
     """A few full-size buffers with a fixed unit -> slot mapping (unit ``i`` always lands at the same
     address, so tensors autograd saved in forward stay valid when the unit is re-gathered in backward).
@@ -355,7 +361,7 @@ class FSDP(Strategy):
         with self._on(self.comm_stream):
             self._wait(after_event, self.comm_stream)
             self.optimizer.step_unit(i, grad=self.shard_grad[i], param=self.shard_param[i],
-                                     max_blocks=(96 if self.is_cuda else 0))
+                                     max_blocks=(_FUSED_ADAMW_BLOCKS if self.is_cuda else 0))
             if self.resident:
                 self._opt_events[i] = self._record(self.comm_stream)
 

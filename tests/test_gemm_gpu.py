@@ -70,3 +70,17 @@ def test_gemm_strided_views():
     gemm(A, B, out=Cbig[:, :N])
     _check(Cbig[:, :N], A.float() @ B.float().t(), K)
     assert Cbig[:, N:].abs().max().item() == 0
+
+
+def test_gemm_mn_major_unaligned_extent():
+    """wgrad with an MN-major operand whose contiguous extent is not a multiple of 64 (tp-sharded vocab)."""
+    from b200train.ops import gemm
+
+    T, V, H = 512, 16032 // 8, 256   # 2004 columns: % 64 == 20
+    dy, x = _mk(T, V, 11), _mk(T, H, 12)
+    dw = gemm(dy, x, a_mn=True, b_mn=True)
+    _check(dw, dy.float().t() @ x.float(), T)
+    acc = _mk(V, H, 13)
+    acc0 = acc.float().clone()
+    gemm(dy, x, a_mn=True, b_mn=True, out=acc, epilogue=3)
+    _check(acc, acc0 + dy.float().t() @ x.float(), T)
