@@ -106,7 +106,7 @@ def parse():
     ap.add_argument("--batch-size", type=int, default=1, help="per-GPU batch (reference default -b 1)")
     ap.add_argument("--layers", type=int, default=None, help="debug only: truncating layers makes the run INVALID")
     ap.add_argument("--fuse-optimizer", default="auto", choices=["auto", "on", "off", "kernel", "stream"],
-                    help="run each unit's sharded AdamW inside backward on the comm stream (auto: only when sharded)")
+                    help="run each unit's sharded AdamW inside backward on the side stream (auto = stream)")
     return ap.parse_args()
 
 
@@ -125,7 +125,7 @@ def run_ours(args):
     if args.layers:
         cfg.num_hidden_layers = args.layers
     B, S = args.batch_size, args.seq_len
-    eng = make_strategy("fsdp", cfg, device, lr=3e-5, seed=0, fuse_optimizer={"auto": ("stream" if world > 1 else False), "on": True, "off": False,
+    eng = make_strategy("fsdp", cfg, device, lr=3e-5, seed=0, fuse_optimizer={"auto": "stream", "on": True, "off": False,
                                        "kernel": "kernel", "stream": "stream"}[args.fuse_optimizer])
 
     def host_batch(i):

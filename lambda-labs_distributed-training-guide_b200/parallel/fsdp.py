@@ -38,7 +38,7 @@ from .optimizer import FlatAdamW
 import os
 
 # blocks given to an AdamW launched beside backward compute (co-resident with the persistent GEMM CTAs)
-_FUSED_ADAMW_BLOCKS = int(os.environ.get("B200TRAIN_FUSED_ADAMW_BLOCKS", "96"))
+_FUSED_ADAMW_BLOCKS = int(os.environ.get("B200TRAIN_FUSED_ADAMW_BLOCKS", "296"))
 
 
 class _BufferPool:
