@@ -1,11 +1,12 @@
 // Causal flash-attention forward for sm_100a on tcgen05 tensor cores with TMEM accumulators.
 //
-// One CTA per (document, query head, 128-row query block); 192 threads:
+// One CTA per (document, query head, 128-row query block); 320 threads:
 //   warp 0     TMA producer  : Q once, then a 2-stage ring of K (K-major) and V (MN-major) tiles
 //   warp 1     MMA issuer    : S_j = Q K_j^T into one of two TMEM S buffers, O += P_j V_j into TMEM O
-//   warps 2-5  softmax       : one thread per query row; tcgen05.ld S, online softmax in the exp2
-//                              domain with lazy rescale of the TMEM O accumulator, P_j -> bf16 ->
-//                              128B-swizzled smem (A operand of the PV MMA); final O / l and LSE.
+//   warps 2-9  softmax       : two warpgroups, each thread owns one query row x 64 of the block's 128 kv
+//                              columns; tcgen05.ld S, online softmax in the exp2 domain (row max
+//                              exchanged through smem) with lazy rescale of the TMEM O accumulator,
+//                              P_j -> bf16 -> 128B-swizzled smem (A operand of the PV MMA); O / l, LSE.
 // S_{j+1} is issued before P_j is consumed so the tensor core overlaps the softmax of block j.
 // GQA (Hq = g * Hkv) and packed variable-length batches (cu_seqlens) are handled by indexing; the
 // operands are strided views (e.g. slices of one fused QKV activation), nothing is copied.
@@ -20,7 +21,7 @@ namespace b2 {
 
 constexpr int ABM = 128;  // query rows per CTA
 constexpr int ABN = 128;  // kv rows per block
-constexpr int kAttnThreads = 192;
+constexpr int kAttnThreads = 320;  // TMA warp, MMA warp, 2 softmax warpgroups (64 columns each)
 
 template <int D>
 struct AttnFwdSmem {
@@ -28,7 +29,8 @@ struct AttnFwdSmem {
   static constexpr int kK = ABN * D * 2;
   static constexpr int kV = ABN * D * 2;
   static constexpr int kP = ABM * ABN * 2;
-  static constexpr int kTotal = kQ + 2 * kK + 2 * kV + 2 * kP + 256 + 1024;
+  static constexpr int kStats = 2 * 2 * ABM * 2;  // bf16 row-max exchange between the two softmax halves
+  static constexpr int kTotal = kQ + 2 * kK + 2 * kV + 2 * kP + kStats + 256 + 1024;
 };
 
 struct AttnFwdParams {
@@ -56,7 +58,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   uint8_t* sK = sQ + SM::kQ;
   uint8_t* sV = sK + 2 * SM::kK;
   uint8_t* sP = sV + 2 * SM::kV;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * SM::kP);
+  __nv_bfloat16* sStat = reinterpret_cast<__nv_bfloat16*>(sP + 2 * SM::kP);  // [2 (parity)][2 (half)][ABM]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * SM::kP + SM::kStats);
   uint64_t* q_full = bars;          // 1
   uint64_t* k_full = bars + 1;      // 2
   uint64_t* k_empty = bars + 3;     // 2
@@ -93,8 +96,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       mbar_init(&v_full[i], 1);
       mbar_init(&v_empty[i], 1);
       mbar_init(&s_full[i], 1);
-      mbar_init(&s_free[i], 4);
-      mbar_init(&p_full[i], 4);
+      mbar_init(&s_free[i], 8);
+      mbar_init(&p_full[i], 8);
       mbar_init(&p_empty[i], 1);
     }
     mbar_init(o_done, 1);
@@ -179,40 +182,54 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     }
   } else {
     // ================= softmax / correction / epilogue =================
+    // Two warpgroups share every query row: half 0 owns kv columns [0, 64) of the block and the first
+    // D/2 columns of O, half 1 the rest. Only the row maximum is exchanged per block (through smem);
+    // the running sums are combined once at the end.
+    constexpr int HC = ABN / 2;            // score columns per thread
+    constexpr int OC = D / 2;              // O columns per thread
+    const int half = (warp - 2) >> 2;
     const int quarter = warp & 3;  // TMEM lane quarter this warp may access
     const int row = quarter * 32 + (int)lane_id();
     const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
     const int q_idx = q0 + row;  // query position inside the document
     float m_used = -INFINITY;    // running max (scaled, log2 domain) used as the exponent base
-    float l = 0.f;
+    float l = 0.f;               // this half's share of the running sum
     for (int j = 0; j < nkv; ++j) {
       const int s = j & 1;
       mbar_wait(&s_full[s], (j >> 1) & 1);
       tc_fence_after();
-      float sv[ABN];
+      float sv[HC];
 #pragma unroll
-      for (int c = 0; c < ABN / 32; ++c) {
+      for (int c = 0; c < HC / 32; ++c) {
         uint32_t r[32];
-        tmem_ld_32x32b_x32(tmem_S[s] + lane_off + c * 32, r);
+        tmem_ld_32x32b_x32(tmem_S[s] + lane_off + half * HC + c * 32, r);
         tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 32; ++i) sv[c * 32 + i] = __uint_as_float(r[i]) * p.scale_log2;
+        for (int i = 0; i < 32; ++i) sv[c * 32 + i] = __uint_as_float(r[i]);
       }
       tc_fence_before();
       __syncwarp();
       if (lane_id() == 0) mbar_arrive(&s_free[s]);
       // masking: causal diagonal and document tail
-      const int kv0 = j * ABN;
-      const bool need_mask = (kv0 + ABN > kv_len) || (p.causal && kv0 + ABN > q0);
+      const int kv0 = j * ABN + half * HC;
+      const bool need_mask = (j * ABN + ABN > kv_len) || (p.causal && j * ABN + ABN > q0);
       if (need_mask) {
         const int lim = p.causal ? min(q_idx, doc_len - 1) : doc_len - 1;  // last visible kv index
 #pragma unroll
-        for (int i = 0; i < ABN; ++i)
+        for (int i = 0; i < HC; ++i)
           if (kv0 + i > lim) sv[i] = -INFINITY;
       }
       float mx = sv[0];
 #pragma unroll
-      for (int i = 1; i < ABN; ++i) mx = fmaxf(mx, sv[i]);
+      for (int i = 1; i < HC; ++i) mx = fmaxf(mx, sv[i]);
+      // exchange the row maximum with the other half (double-buffered by block parity: one barrier)
+      // (both halves use the bf16-rounded maxima, so they agree bit for bit on the exponent base; a base
+      // that is a rounding below the true maximum only makes the largest p slightly exceed 1)
+      __nv_bfloat16* stat = sStat + (j & 1) * (2 * ABM);
+      const __nv_bfloat16 mine = __float2bfloat16_rn(mx);
+      stat[half * ABM + row] = mine;
+      named_bar_sync(3, 256);
+      mx = fmaxf(__bfloat162float(mine), __bfloat162float(stat[(half ^ 1) * ABM + row])) * p.scale_log2;
       // lazy rescale: keep a stale exponent base until the row max grows by more than 2^8
       float alpha = 1.f;
       const bool need = mx > m_used + 8.f;
@@ -225,55 +242,60 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         mbar_wait(o_done, (j - 1) & 1);  // PV_{j-1} retired: O is stable
         tc_fence_after();
 #pragma unroll
-        for (int c = 0; c < D / 16; ++c) {
+        for (int c = 0; c < OC / 16; ++c) {
           uint32_t r[16];
-          tmem_ld_32x32b_x16(tmem_O + lane_off + c * 16, r);
+          tmem_ld_32x32b_x16(tmem_O + lane_off + half * OC + c * 16, r);
           tmem_ld_wait();
 #pragma unroll
           for (int i = 0; i < 16; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
-          tmem_st_32x32b_x16(tmem_O + lane_off + c * 16, r);
+          tmem_st_32x32b_x16(tmem_O + lane_off + half * OC + c * 16, r);
         }
         tmem_st_wait();
         tc_fence_before();
       }
       const float base = (m_used == -INFINITY) ? 0.f : m_used;
       float psum = 0.f;
-      uint32_t pk[ABN / 2];
+      uint32_t pk[HC / 2];
 #pragma unroll
-      for (int i = 0; i < ABN / 2; ++i) {
-        const float p0 = exp2f(sv[2 * i] - base);
-        const float p1 = exp2f(sv[2 * i + 1] - base);
+      for (int i = 0; i < HC / 2; ++i) {
+        const float p0 = exp2f(fmaf(sv[2 * i], p.scale_log2, -base));
+        const float p1 = exp2f(fmaf(sv[2 * i + 1], p.scale_log2, -base));
         psum += p0 + p1;
         pk[i] = pack_bf16(p0, p1);
       }
       l += psum;
       mbar_wait(&p_empty[s], ((j >> 1) & 1) ^ 1);  // PV_{j-2} finished reading this P buffer
-      const uint32_t pbase = smem_u32(sP + s * SM::kP) + row * 128;
+      // this half's 64 columns are one 128-byte swizzle atom of the K-major P tile
+      const uint32_t pbase = smem_u32(sP + s * SM::kP) + half * (ABM * 128) + row * 128;
 #pragma unroll
-      for (int a = 0; a < 2; ++a) {
-#pragma unroll
-        for (int c = 0; c < 8; ++c) {
-          const uint32_t addr = pbase + a * (ABM * 128) + ((c ^ (row & 7)) << 4);
-          const int b = a * 32 + c * 4;
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(pk[b]),
-                       "r"(pk[b + 1]), "r"(pk[b + 2]), "r"(pk[b + 3])
-                       : "memory");
-        }
+      for (int c = 0; c < 8; ++c) {
+        const uint32_t addr = pbase + ((c ^ (row & 7)) << 4);
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(pk[4 * c]),
+                     "r"(pk[4 * c + 1]), "r"(pk[4 * c + 2]), "r"(pk[4 * c + 3])
+                     : "memory");
       }
       fence_proxy_async_smem();
       __syncwarp();
       if (lane_id() == 0) mbar_arrive(&p_full[s]);
     }
-    // ---- epilogue: O / l -> bf16, LSE ----
+    // ---- epilogue: combine the two partial sums, O / l -> bf16, LSE ----
+    // (the two parity buffers together hold one fp32 per (half, row); every thread is past its last
+    // row-max exchange once it arrives at the barrier below, and reads only after it)
+    named_bar_sync(3, 256);
+    float* lsum = reinterpret_cast<float*>(sStat);
+    lsum[half * ABM + row] = l;
+    named_bar_sync(3, 256);
+    l += lsum[(half ^ 1) * ABM + row];
     mbar_wait(o_done, (nkv - 1) & 1);
     tc_fence_after();
     const float inv_l = l > 0.f ? 1.f / l : 0.f;
     const bool valid = q_idx < doc_len;
-    __nv_bfloat16* orow = p.o + (size_t)(doc_start + q_idx) * p.o_stride + (size_t)head * D;
+    __nv_bfloat16* orow =
+        p.o + (size_t)(doc_start + q_idx) * p.o_stride + (size_t)head * D + half * OC;
 #pragma unroll
-    for (int c = 0; c < D / 32; ++c) {
+    for (int c = 0; c < OC / 32; ++c) {
       uint32_t r[32];
-      tmem_ld_32x32b_x32(tmem_O + lane_off + c * 32, r);
+      tmem_ld_32x32b_x32(tmem_O + lane_off + half * OC + c * 32, r);
       tmem_ld_wait();
       if (valid) {
 #pragma unroll
@@ -290,7 +312,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         }
       }
     }
-    if (valid)
+    if (valid && half == 0)
       p.lse[(size_t)head * p.T + doc_start + q_idx] =
           (l > 0.f) ? (m_used + log2f(l)) * 0.6931471805599453f : -INFINITY;
     tc_fence_before();

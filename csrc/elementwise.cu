@@ -29,6 +29,16 @@ __device__ __forceinline__ BF8 f_to_bf8(const float (&f)[8]) {
   for (int i = 0; i < 4; ++i) v.u[i] = pack_bf16(f[2 * i], f[2 * i + 1]);
   return v;
 }
+// streaming (evict-first) 16-byte accesses for data touched exactly once per kernel
+__device__ __forceinline__ BF8 ld_stream(const BF8* p) {
+  const uint4 v = __ldcs(reinterpret_cast<const uint4*>(p));
+  BF8 r;
+  r.u[0] = v.x; r.u[1] = v.y; r.u[2] = v.z; r.u[3] = v.w;
+  return r;
+}
+__device__ __forceinline__ void st_stream(BF8* p, const BF8& v) {
+  __stcs(reinterpret_cast<uint4*>(p), make_uint4(v.u[0], v.u[1], v.u[2], v.u[3]));
+}
 __device__ __forceinline__ float bf16_round(float x) {
   return __bfloat162float(__float2bfloat16_rn(x));
 }
@@ -379,24 +389,37 @@ __global__ void fold_partials2_kernel(__nv_bfloat16* __restrict__ dw, __nv_bfloa
 // ------------------------------------------------------------------------------------------------
 // SwiGLU on a fused [T, 2I] gate|up buffer, and gelu_new
 // ------------------------------------------------------------------------------------------------
-__global__ void swiglu_fwd_kernel(__nv_bfloat16* __restrict__ out,
-                                  const __nv_bfloat16* __restrict__ gu, int T, int I) {
+__device__ __forceinline__ BF8 swiglu_vec(const BF8& gv, const BF8& uv) {
+  float g[8], u[8], o[8];
+  bf8_to_f(gv, g);
+  bf8_to_f(uv, u);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) o[j] = bf16_round(g[j] / (1.f + __expf(-g[j]))) * u[j];
+  return f_to_bf8(o);
+}
+
+__global__ void __launch_bounds__(256)
+swiglu_fwd_kernel(__nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ gu, int T, int I) {
   const int nvec = I >> 3;
   const size_t total = (size_t)T * nvec;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (size_t)gridDim.x * blockDim.x) {
-    const size_t row = i / nvec;
-    const int c = (int)(i - row * nvec);
-    const BF8* base = reinterpret_cast<const BF8*>(gu + row * 2 * (size_t)I);
-    float g[8], u[8], o[8];
-    bf8_to_f(base[c], g);
-    bf8_to_f(base[nvec + c], u);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float s = bf16_round(g[j] / (1.f + __expf(-g[j])));
-      o[j] = s * u[j];
-    }
-    reinterpret_cast<BF8*>(out + row * (size_t)I)[c] = f_to_bf8(o);
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + stride < total; i += 2 * stride) {  // two independent vectors (4 loads) in flight
+    const size_t i1 = i + stride;
+    const size_t r0 = i / nvec, r1 = i1 / nvec;
+    const int c0 = (int)(i - r0 * nvec), c1 = (int)(i1 - r1 * nvec);
+    const BF8* b0 = reinterpret_cast<const BF8*>(gu + r0 * 2 * (size_t)I);
+    const BF8* b1 = reinterpret_cast<const BF8*>(gu + r1 * 2 * (size_t)I);
+    const BF8 g0 = ld_stream(b0 + c0), u0 = ld_stream(b0 + nvec + c0);
+    const BF8 g1 = ld_stream(b1 + c1), u1 = ld_stream(b1 + nvec + c1);
+    reinterpret_cast<BF8*>(out + r0 * (size_t)I)[c0] = swiglu_vec(g0, u0);
+    reinterpret_cast<BF8*>(out + r1 * (size_t)I)[c1] = swiglu_vec(g1, u1);
+  }
+  if (i < total) {
+    const size_t r0 = i / nvec;
+    const int c0 = (int)(i - r0 * nvec);
+    const BF8* b0 = reinterpret_cast<const BF8*>(gu + r0 * 2 * (size_t)I);
+    reinterpret_cast<BF8*>(out + r0 * (size_t)I)[c0] = swiglu_vec(ld_stream(b0 + c0), ld_stream(b0 + nvec + c0));
   }
 }
 
@@ -411,9 +434,11 @@ __global__ void swiglu_bwd_kernel(__nv_bfloat16* __restrict__ dgu,
     const int c = (int)(i - row * nvec);
     const BF8* base = reinterpret_cast<const BF8*>(gu + row * 2 * (size_t)I);
     float g[8], u[8], d[8], dg[8], du[8];
-    bf8_to_f(base[c], g);
-    bf8_to_f(base[nvec + c], u);
-    bf8_to_f(reinterpret_cast<const BF8*>(dout + row * (size_t)I)[c], d);
+    const BF8 gv = ld_stream(base + c), uv = ld_stream(base + nvec + c);
+    const BF8 dv = ld_stream(reinterpret_cast<const BF8*>(dout + row * (size_t)I) + c);
+    bf8_to_f(gv, g);
+    bf8_to_f(uv, u);
+    bf8_to_f(dv, d);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const float sig = 1.f / (1.f + __expf(-g[j]));
@@ -658,21 +683,21 @@ adamw_kernel(__nv_bfloat16* __restrict__ p, __nv_bfloat16* __restrict__ m,
   // two independent 16-byte vectors per thread per trip: 8 loads in flight before any math
   for (; i + stride < nvec; i += 2 * stride) {
     const size_t i1 = i + stride;
-    const BF8 p0 = reinterpret_cast<const BF8*>(p)[i], p1 = reinterpret_cast<const BF8*>(p)[i1];
-    const BF8 m0 = reinterpret_cast<const BF8*>(m)[i], m1 = reinterpret_cast<const BF8*>(m)[i1];
-    const BF8 v0 = reinterpret_cast<const BF8*>(v)[i], v1 = reinterpret_cast<const BF8*>(v)[i1];
-    const BF8 g0 = reinterpret_cast<const BF8*>(g)[i], g1 = reinterpret_cast<const BF8*>(g)[i1];
+    const BF8 p0 = ld_stream(reinterpret_cast<const BF8*>(p) + i), p1 = ld_stream(reinterpret_cast<const BF8*>(p) + i1);
+    const BF8 m0 = ld_stream(reinterpret_cast<const BF8*>(m) + i), m1 = ld_stream(reinterpret_cast<const BF8*>(m) + i1);
+    const BF8 v0 = ld_stream(reinterpret_cast<const BF8*>(v) + i), v1 = ld_stream(reinterpret_cast<const BF8*>(v) + i1);
+    const BF8 g0 = ld_stream(reinterpret_cast<const BF8*>(g) + i), g1 = ld_stream(reinterpret_cast<const BF8*>(g) + i1);
     float pf[8], mf[8], vf[8], gf[8];
     bf8_to_f(p0, pf); bf8_to_f(m0, mf); bf8_to_f(v0, vf); bf8_to_f(g0, gf);
     adamw_vec(pf, mf, vf, gf, decay, beta1, beta2, eps, step_size, inv_bc2_sqrt, grad_scale);
-    reinterpret_cast<BF8*>(p)[i] = f_to_bf8(pf);
-    reinterpret_cast<BF8*>(m)[i] = f_to_bf8(mf);
-    reinterpret_cast<BF8*>(v)[i] = f_to_bf8(vf);
+    st_stream(reinterpret_cast<BF8*>(p) + i, f_to_bf8(pf));
+    st_stream(reinterpret_cast<BF8*>(m) + i, f_to_bf8(mf));
+    st_stream(reinterpret_cast<BF8*>(v) + i, f_to_bf8(vf));
     bf8_to_f(p1, pf); bf8_to_f(m1, mf); bf8_to_f(v1, vf); bf8_to_f(g1, gf);
     adamw_vec(pf, mf, vf, gf, decay, beta1, beta2, eps, step_size, inv_bc2_sqrt, grad_scale);
-    reinterpret_cast<BF8*>(p)[i1] = f_to_bf8(pf);
-    reinterpret_cast<BF8*>(m)[i1] = f_to_bf8(mf);
-    reinterpret_cast<BF8*>(v)[i1] = f_to_bf8(vf);
+    st_stream(reinterpret_cast<BF8*>(p) + i1, f_to_bf8(pf));
+    st_stream(reinterpret_cast<BF8*>(m) + i1, f_to_bf8(mf));
+    st_stream(reinterpret_cast<BF8*>(v) + i1, f_to_bf8(vf));
   }
   if (i < nvec) {
     float pf[8], mf[8], vf[8], gf[8];
