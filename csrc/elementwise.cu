@@ -545,18 +545,34 @@ __global__ void embedding_fwd_kernel(__nv_bfloat16* __restrict__ out,
         reinterpret_cast<const BF8*>(table + (size_t)ids[t] * H)[c];
   }
 }
-// dtable[ids[t], :] += dout[t, :]   (bf16x2 atomics; dtable must be zeroed or hold prior grads)
-__global__ void embedding_bwd_kernel(__nv_bfloat16* __restrict__ dtable,
-                                     const __nv_bfloat16* __restrict__ dout,
-                                     const long long* __restrict__ ids, int T, int H) {
-  const int npair = H >> 1;
-  const size_t total = (size_t)T * npair;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (size_t)gridDim.x * blockDim.x) {
-    const size_t t = i / npair;
-    const int c = (int)(i - t * npair);
-    const __nv_bfloat162 v = reinterpret_cast<const __nv_bfloat162*>(dout + t * (size_t)H)[c];
-    atomicAdd(reinterpret_cast<__nv_bfloat162*>(dtable + (size_t)ids[t] * H) + c, v);
+// dtable[id, :] (+)= sum over the positions holding `id` of dout[pos, :], accumulated in fp32 and
+// without atomics: the token ids are sorted on the host side (sorted_ids / perm), block i does work only
+// when position i starts a run of equal ids and then sums the whole run (deterministic, and exact like
+// the reference's sort-based embedding_dense_backward, however often a token repeats).
+__global__ void __launch_bounds__(128)
+embedding_bwd_kernel(__nv_bfloat16* __restrict__ dtable, const __nv_bfloat16* __restrict__ dout,
+                     const long long* __restrict__ sorted_ids, const long long* __restrict__ perm,
+                     int T, int H, int accumulate) {
+  const int i = blockIdx.x;
+  const long long id = sorted_ids[i];
+  if (i > 0 && sorted_ids[i - 1] == id) return;  // not the first position of its run
+  const int nvec = H >> 3;
+  for (int c = threadIdx.x; c < nvec; c += blockDim.x) {
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int k = i; k < T && sorted_ids[k] == id; ++k) {
+      float v[8];
+      bf8_to_f(reinterpret_cast<const BF8*>(dout + (size_t)perm[k] * H)[c], v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += v[j];
+    }
+    BF8* dst = reinterpret_cast<BF8*>(dtable + (size_t)id * H) + c;
+    if (accumulate) {
+      float o[8];
+      bf8_to_f(*dst, o);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += o[j];
+    }
+    *dst = f_to_bf8(acc);
   }
 }
 
@@ -874,12 +890,14 @@ int b2_embedding_fwd(void* out, const void* table, const long long* ids, int T, 
   B2_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
-int b2_embedding_bwd(void* dtable, const void* dout, const long long* ids, int T, int H,
-                     cudaStream_t stream) {
-  B2_REQUIRE(H % 2 == 0, "embedding: H=%d odd", H);
+// sorted_ids: the T token ids in ascending order; perm[k]: original position of sorted_ids[k].
+// Rows of tokens that do not occur are left untouched (zero dtable first unless accumulating).
+int b2_embedding_bwd(void* dtable, const void* dout, const long long* sorted_ids,
+                     const long long* perm, int T, int H, int accumulate, cudaStream_t stream) {
+  B2_REQUIRE(H % 8 == 0, "embedding: H=%d not a multiple of 8", H);
   if (T == 0) return 0;
-  embedding_bwd_kernel<<<ew_grid((size_t)T * (H / 2), 256), 256, 0, stream>>>(
-      (bf16*)dtable, (const bf16*)dout, ids, T, H);
+  embedding_bwd_kernel<<<T, 128, 0, stream>>>((bf16*)dtable, (const bf16*)dout, sorted_ids, perm, T, H,
+                                              accumulate);
   B2_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

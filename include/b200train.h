@@ -90,8 +90,8 @@ int b2_rope(void* x, const void* cosT, const void* sinT, const int* pos, int T, 
             int row_stride, int seq_len, int backward, b2_stream_t stream);
 int b2_embedding_fwd(void* out, const void* table, const long long* ids, int T, int H,
                      b2_stream_t stream);
-int b2_embedding_bwd(void* dtable, const void* dout, const long long* ids, int T, int H,
-                     b2_stream_t stream);
+int b2_embedding_bwd(void* dtable, const void* dout, const long long* sorted_ids,
+                     const long long* perm, int T, int H, int accumulate, b2_stream_t stream);
 
 /* ---- cross entropy ---------------------------------------------------------------------------
  * Reference: HF ForCausalLMLoss (fp32 log-softmax + nll), loss parallel 06-tensor-parallel/train_llm.py:239. */

@@ -45,7 +45,7 @@ def _declare(lib):
         "b2_gelu_bwd": [P, P, P, Z, P],
         "b2_rope": [P, P, P, P, I, I, I, I, I, I, P],
         "b2_embedding_fwd": [P, P, P, I, I, P],
-        "b2_embedding_bwd": [P, P, P, I, I, P],
+        "b2_embedding_bwd": [P, P, P, P, I, I, I, P],
         "b2_ce_fwd": [P, P, P, P, I, I, I, I, P],
         "b2_ce_shard_stats": [P, P, P, P, P, I, I, I, I, I, P],
         "b2_ce_bwd": [P, P, P, P, I, I, I, I, I, F, P, P],

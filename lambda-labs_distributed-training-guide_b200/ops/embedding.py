@@ -30,15 +30,20 @@ class _Embedding(torch.autograd.Function):
         if not d2.is_contiguous():
             d2 = d2.contiguous()
         direct = getattr(table, "_b2_direct_grad", False) and table.grad is not None
+        accumulate = 0
         if direct:
-            if not getattr(table, "_b2_grad_ready", False):
+            if getattr(table, "_b2_grad_ready", False):
+                accumulate = 1          # e.g. a tied lm_head already wrote its wgrad into this buffer
+            else:
                 table.grad.zero_()
             table._b2_grad_ready = True
             dt = table.grad
         else:
             dt = torch.zeros_like(table)
-        _C.call("b2_embedding_bwd", dt.data_ptr(), d2.data_ptr(), flat.data_ptr(), flat.numel(), H,
-                stream(table))
+        # sort the ids once: runs of equal ids are reduced in fp32 by one block each (no atomics)
+        sorted_ids, perm = torch.sort(flat)
+        _C.call("b2_embedding_bwd", dt.data_ptr(), d2.data_ptr(), sorted_ids.data_ptr(), perm.data_ptr(),
+                flat.numel(), H, accumulate, stream(table))
         return None, (None if direct else dt)
 
 

@@ -120,7 +120,7 @@ def test_embedding():
     V, H, T = 1000, 512, 777
     table = _r(V, H, seed=1).requires_grad_()
     ids = torch.randint(0, V, (T,), device="cuda")
-    ids[:50] = 7  # heavy duplicates exercise the atomics
+    ids[:300] = 7  # a token repeated 300 times (fp32 run reduction, no atomics)
     out = embedding(ids, table)
     g = _r(T, H, seed=2)
     out.backward(g)
@@ -128,7 +128,7 @@ def test_embedding():
     outr = torch.nn.functional.embedding(ids, tr)
     outr.backward(g.float())
     assert torch.equal(out.float(), outr)
-    _close(table.grad, tr.grad, 0.15, 3e-2)
+    _close(table.grad, tr.grad, 2e-2, 1e-2)
 
 
 @pytest.mark.parametrize("V", [1000, 50257, 128256])
