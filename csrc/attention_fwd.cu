@@ -3,10 +3,14 @@
 // One CTA per (document, query head, 128-row query block); 320 threads:
 //   warp 0     TMA producer  : Q once, then a 2-stage ring of K (K-major) and V (MN-major) tiles
 //   warp 1     MMA issuer    : S_j = Q K_j^T into one of two TMEM S buffers, O += P_j V_j into TMEM O
-//   warps 2-9  softmax       : two warpgroups, each thread owns one query row x 64 of the block's 128 kv
-//                              columns; tcgen05.ld S, online softmax in the exp2 domain (row max
-//                              exchanged through smem) with lazy rescale of the TMEM O accumulator,
-//                              P_j -> bf16 -> 128B-swizzled smem (A operand of the PV MMA); O / l, LSE.
+//   warps 2-9  softmax       : two warpgroups in ping-pong: warpgroup w handles the kv blocks j with
+//                              j % 2 == w, one thread per query row, with its own S buffer, its own O
+//                              accumulator in TMEM and its own running (max, sum). While one warpgroup
+//                              drains S from TMEM the other is in its exp2 phase, so the TMEM read
+//                              port, the MUFU pipe and the tensor pipe work concurrently. tcgen05.ld S,
+//                              online softmax in the exp2 domain with lazy rescale of O, P_j -> bf16 ->
+//                              128B-swizzled smem (A operand of the PV MMA). The two partial results
+//                              are merged at the end (through the P buffers) into O / l and the LSE.
 // S_{j+1} is issued before P_j is consumed so the tensor core overlaps the softmax of block j.
 // GQA (Hq = g * Hkv) and packed variable-length batches (cu_seqlens) are handled by indexing; the
 // operands are strided views (e.g. slices of one fused QKV activation), nothing is copied.
@@ -29,7 +33,7 @@ struct AttnFwdSmem {
   static constexpr int kK = ABN * D * 2;
   static constexpr int kV = ABN * D * 2;
   static constexpr int kP = ABM * ABN * 2;
-  static constexpr int kStats = 2 * 2 * ABM * 2;  // bf16 row-max exchange between the two softmax halves
+  static constexpr int kStats = 2 * ABM * 4;      // (max, sum) of warpgroup 1 for the final merge
   static constexpr int kTotal = kQ + 2 * kK + 2 * kV + 2 * kP + kStats + 256 + 1024;
 };
 
@@ -58,7 +62,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   uint8_t* sK = sQ + SM::kQ;
   uint8_t* sV = sK + 2 * SM::kK;
   uint8_t* sP = sV + 2 * SM::kV;
-  __nv_bfloat16* sStat = reinterpret_cast<__nv_bfloat16*>(sP + 2 * SM::kP);  // [2 (parity)][2 (half)][ABM]
+  float* sStat = reinterpret_cast<float*>(sP + 2 * SM::kP);  // [2 (max, sum)][ABM]
   uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * SM::kP + SM::kStats);
   uint64_t* q_full = bars;          // 1
   uint64_t* k_full = bars + 1;      // 2
@@ -69,8 +73,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   uint64_t* s_free = bars + 11;     // 2
   uint64_t* p_full = bars + 13;     // 2
   uint64_t* p_empty = bars + 15;    // 2
-  uint64_t* o_done = bars + 17;     // 1
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
+  uint64_t* o_done = bars + 17;     // 2
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 19);
 
   const int warp = threadIdx.x >> 5;
   const int doc = blockIdx.z;
@@ -96,11 +100,11 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       mbar_init(&v_full[i], 1);
       mbar_init(&v_empty[i], 1);
       mbar_init(&s_full[i], 1);
-      mbar_init(&s_free[i], 8);
-      mbar_init(&p_full[i], 8);
+      mbar_init(&s_free[i], 4);
+      mbar_init(&p_full[i], 4);
+      mbar_init(&o_done[i], 1);
       mbar_init(&p_empty[i], 1);
     }
-    mbar_init(o_done, 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<1>(tmem_slot, 512);
@@ -109,7 +113,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t tmem_S[2] = {tmem_base, tmem_base + 128};
-  const uint32_t tmem_O = tmem_base + 256;
+  const uint32_t tmem_O[2] = {tmem_base + 256, tmem_base + 256 + D};  // one accumulator per warpgroup
 
   if (warp == 0) {
     // ================= TMA producer =================
@@ -172,64 +176,52 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           const uint64_t da =
               make_smem_desc_sw128(pa + (kk >> 2) * (ABM * 128) + (kk & 3) * 32, 16, 1024);
           const uint64_t db = make_smem_desc_sw128(va + kk * 2048, ABN * 128, 1024);
-          umma_f16<1>(tmem_O, da, db, idesc_o, (j | kk) != 0);
+          umma_f16<1>(tmem_O[s], da, db, idesc_o, (j >= 2 || kk != 0) ? 1u : 0u);
         }
         umma_commit<1>(&v_empty[s]);
         umma_commit<1>(&p_empty[s]);
-        umma_commit<1>(o_done);
+        umma_commit<1>(&o_done[s]);
       }
       __syncwarp();
     }
   } else {
     // ================= softmax / correction / epilogue =================
-    // Two warpgroups share every query row: half 0 owns kv columns [0, 64) of the block and the first
-    // D/2 columns of O, half 1 the rest. Only the row maximum is exchanged per block (through smem);
-    // the running sums are combined once at the end.
-    constexpr int HC = ABN / 2;            // score columns per thread
-    constexpr int OC = D / 2;              // O columns per thread
-    const int half = (warp - 2) >> 2;
-    const int quarter = warp & 3;  // TMEM lane quarter this warp may access
+    const int wg = (warp - 2) >> 2;  // ping-pong warpgroup: handles kv blocks j with (j & 1) == wg
+    const int quarter = warp & 3;    // TMEM lane quarter this warp may access
     const int row = quarter * 32 + (int)lane_id();
     const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
     const int q_idx = q0 + row;  // query position inside the document
     float m_used = -INFINITY;    // running max (scaled, log2 domain) used as the exponent base
-    float l = 0.f;               // this half's share of the running sum
-    for (int j = 0; j < nkv; ++j) {
-      const int s = j & 1;
-      mbar_wait(&s_full[s], (j >> 1) & 1);
+    float l = 0.f;
+    int k = 0;                   // number of blocks this warpgroup has finished
+    for (int j = wg; j < nkv; j += 2, ++k) {
+      mbar_wait(&s_full[wg], k & 1);
       tc_fence_after();
-      float sv[HC];
+      float sv[ABN];
 #pragma unroll
-      for (int c = 0; c < HC / 32; ++c) {
+      for (int c = 0; c < ABN / 32; ++c) {
         uint32_t r[32];
-        tmem_ld_32x32b_x32(tmem_S[s] + lane_off + half * HC + c * 32, r);
+        tmem_ld_32x32b_x32(tmem_S[wg] + lane_off + c * 32, r);
         tmem_ld_wait();
 #pragma unroll
         for (int i = 0; i < 32; ++i) sv[c * 32 + i] = __uint_as_float(r[i]);
       }
       tc_fence_before();
       __syncwarp();
-      if (lane_id() == 0) mbar_arrive(&s_free[s]);
+      if (lane_id() == 0) mbar_arrive(&s_free[wg]);
       // masking: causal diagonal and document tail
-      const int kv0 = j * ABN + half * HC;
-      const bool need_mask = (j * ABN + ABN > kv_len) || (p.causal && j * ABN + ABN > q0);
+      const int kv0 = j * ABN;
+      const bool need_mask = (kv0 + ABN > kv_len) || (p.causal && kv0 + ABN > q0);
       if (need_mask) {
         const int lim = p.causal ? min(q_idx, doc_len - 1) : doc_len - 1;  // last visible kv index
 #pragma unroll
-        for (int i = 0; i < HC; ++i)
+        for (int i = 0; i < ABN; ++i)
           if (kv0 + i > lim) sv[i] = -INFINITY;
       }
       float mx = sv[0];
 #pragma unroll
-      for (int i = 1; i < HC; ++i) mx = fmaxf(mx, sv[i]);
-      // exchange the row maximum with the other half (double-buffered by block parity: one barrier)
-      // (both halves use the bf16-rounded maxima, so they agree bit for bit on the exponent base; a base
-      // that is a rounding below the true maximum only makes the largest p slightly exceed 1)
-      __nv_bfloat16* stat = sStat + (j & 1) * (2 * ABM);
-      const __nv_bfloat16 mine = __float2bfloat16_rn(mx);
-      stat[half * ABM + row] = mine;
-      named_bar_sync(3, 256);
-      mx = fmaxf(__bfloat162float(mine), __bfloat162float(stat[(half ^ 1) * ABM + row])) * p.scale_log2;
+      for (int i = 1; i < ABN; ++i) mx = fmaxf(mx, sv[i]);
+      mx *= p.scale_log2;
       // lazy rescale: keep a stale exponent base until the row max grows by more than 2^8
       float alpha = 1.f;
       const bool need = mx > m_used + 8.f;
@@ -238,83 +230,121 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         l *= alpha;
         m_used = mx;
       }
-      if (j > 0 && __any_sync(0xffffffffu, need)) {
-        mbar_wait(o_done, (j - 1) & 1);  // PV_{j-1} retired: O is stable
+      if (k > 0 && __any_sync(0xffffffffu, need)) {
+        mbar_wait(&o_done[wg], (k - 1) & 1);  // this warpgroup's previous PV retired: its O is stable
         tc_fence_after();
 #pragma unroll
-        for (int c = 0; c < OC / 16; ++c) {
+        for (int c = 0; c < D / 16; ++c) {
           uint32_t r[16];
-          tmem_ld_32x32b_x16(tmem_O + lane_off + half * OC + c * 16, r);
+          tmem_ld_32x32b_x16(tmem_O[wg] + lane_off + c * 16, r);
           tmem_ld_wait();
 #pragma unroll
           for (int i = 0; i < 16; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
-          tmem_st_32x32b_x16(tmem_O + lane_off + half * OC + c * 16, r);
+          tmem_st_32x32b_x16(tmem_O[wg] + lane_off + c * 16, r);
         }
         tmem_st_wait();
         tc_fence_before();
       }
       const float base = (m_used == -INFINITY) ? 0.f : m_used;
       float psum = 0.f;
-      uint32_t pk[HC / 2];
+      mbar_wait(&p_empty[wg], (k & 1) ^ 1);  // the previous PV of this warpgroup finished reading P
+      const uint32_t pbase = smem_u32(sP + wg * SM::kP) + row * 128;
 #pragma unroll
-      for (int i = 0; i < HC / 2; ++i) {
-        const float p0 = exp2f(fmaf(sv[2 * i], p.scale_log2, -base));
-        const float p1 = exp2f(fmaf(sv[2 * i + 1], p.scale_log2, -base));
-        psum += p0 + p1;
-        pk[i] = pack_bf16(p0, p1);
-      }
-      l += psum;
-      mbar_wait(&p_empty[s], ((j >> 1) & 1) ^ 1);  // PV_{j-2} finished reading this P buffer
-      // this half's 64 columns are one 128-byte swizzle atom of the K-major P tile
-      const uint32_t pbase = smem_u32(sP + s * SM::kP) + half * (ABM * 128) + row * 128;
+      for (int a = 0; a < 2; ++a) {
 #pragma unroll
-      for (int c = 0; c < 8; ++c) {
-        const uint32_t addr = pbase + ((c ^ (row & 7)) << 4);
-        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(pk[4 * c]),
-                     "r"(pk[4 * c + 1]), "r"(pk[4 * c + 2]), "r"(pk[4 * c + 3])
-                     : "memory");
-      }
-      fence_proxy_async_smem();
-      __syncwarp();
-      if (lane_id() == 0) mbar_arrive(&p_full[s]);
-    }
-    // ---- epilogue: combine the two partial sums, O / l -> bf16, LSE ----
-    // (the two parity buffers together hold one fp32 per (half, row); every thread is past its last
-    // row-max exchange once it arrives at the barrier below, and reads only after it)
-    named_bar_sync(3, 256);
-    float* lsum = reinterpret_cast<float*>(sStat);
-    lsum[half * ABM + row] = l;
-    named_bar_sync(3, 256);
-    l += lsum[(half ^ 1) * ABM + row];
-    mbar_wait(o_done, (nkv - 1) & 1);
-    tc_fence_after();
-    const float inv_l = l > 0.f ? 1.f / l : 0.f;
-    const bool valid = q_idx < doc_len;
-    __nv_bfloat16* orow =
-        p.o + (size_t)(doc_start + q_idx) * p.o_stride + (size_t)head * D + half * OC;
+        for (int c = 0; c < 8; ++c) {
+          uint32_t pk[4];
 #pragma unroll
-    for (int c = 0; c < OC / 32; ++c) {
-      uint32_t r[32];
-      tmem_ld_32x32b_x32(tmem_O + lane_off + half * OC + c * 32, r);
-      tmem_ld_wait();
-      if (valid) {
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          uint4 v;
-          v.x = pack_bf16(__uint_as_float(r[8 * i]) * inv_l, __uint_as_float(r[8 * i + 1]) * inv_l);
-          v.y = pack_bf16(__uint_as_float(r[8 * i + 2]) * inv_l,
-                          __uint_as_float(r[8 * i + 3]) * inv_l);
-          v.z = pack_bf16(__uint_as_float(r[8 * i + 4]) * inv_l,
-                          __uint_as_float(r[8 * i + 5]) * inv_l);
-          v.w = pack_bf16(__uint_as_float(r[8 * i + 6]) * inv_l,
-                          __uint_as_float(r[8 * i + 7]) * inv_l);
-          *reinterpret_cast<uint4*>(orow + c * 32 + i * 8) = v;
+          for (int e = 0; e < 4; ++e) {
+            const int i = a * 64 + c * 8 + e * 2;
+            const float p0 = exp2f(fmaf(sv[i], p.scale_log2, -base));
+            const float p1 = exp2f(fmaf(sv[i + 1], p.scale_log2, -base));
+            psum += p0 + p1;
+            pk[e] = pack_bf16(p0, p1);
+          }
+          const uint32_t addr = pbase + a * (ABM * 128) + ((c ^ (row & 7)) << 4);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(pk[0]), "r"(pk[1]),
+                       "r"(pk[2]), "r"(pk[3])
+                       : "memory");
         }
       }
+      l += psum;
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane_id() == 0) mbar_arrive(&p_full[wg]);
     }
-    if (valid && half == 0)
-      p.lse[(size_t)head * p.T + doc_start + q_idx] =
-          (l > 0.f) ? (m_used + log2f(l)) * 0.6931471805599453f : -INFINITY;
+    // ---- merge the two warpgroups' partial results: O = (f0 O0 + f1 O1) / (f0 l0 + f1 l1) ----
+    if (k > 0) {
+      mbar_wait(&o_done[wg], (k - 1) & 1);  // last PV of this warpgroup (which also read P last)
+      tc_fence_after();
+    }
+    if (wg == 1) {
+      sStat[row] = m_used;
+      sStat[ABM + row] = l;
+    }
+    // all PV MMAs that read the P buffers have retired for both warpgroups once both pass this barrier
+    named_bar_sync(3, 256);
+    const float m1 = sStat[row], l1 = sStat[ABM + row];
+    float m_all, f_mine, l_all;
+    if (wg == 0) {
+      m_all = fmaxf(m_used, m1);
+      const float f0 = (m_used == -INFINITY) ? 0.f : exp2f(m_used - m_all);
+      const float f1 = (m1 == -INFINITY) ? 0.f : exp2f(m1 - m_all);
+      l_all = f0 * l + f1 * l1;
+      f_mine = f0;
+    } else {
+      m_all = 0.f;
+      l_all = 0.f;
+      f_mine = 1.f;  // warpgroup 1 hands over its raw accumulator; warpgroup 0 applies both factors
+    }
+    float* xbuf = reinterpret_cast<float*>(sP);  // [D][ABM] fp32, column-major: conflict-free per warp
+    const bool valid = q_idx < doc_len;
+    if (wg == 1) {
+#pragma unroll
+      for (int c = 0; c < D / 32; ++c) {
+        uint32_t r[32];
+        if (k > 0) {
+          tmem_ld_32x32b_x32(tmem_O[1] + lane_off + c * 32, r);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) r[i] = 0u;
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) xbuf[(c * 32 + i) * ABM + row] = __uint_as_float(r[i]);
+      }
+    }
+    named_bar_sync(3, 256);
+    if (wg == 0) {
+      const float f1 = (m1 == -INFINITY) ? 0.f : exp2f(m1 - m_all);
+      const float inv_l = l_all > 0.f ? 1.f / l_all : 0.f;
+      const float a0 = f_mine * inv_l, a1 = f1 * inv_l;
+      __nv_bfloat16* orow = p.o + (size_t)(doc_start + q_idx) * p.o_stride + (size_t)head * D;
+#pragma unroll
+      for (int c = 0; c < D / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(tmem_O[0] + lane_off + c * 32, r);
+        tmem_ld_wait();
+        float o[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+          o[i] = __uint_as_float(r[i]) * a0 + xbuf[(c * 32 + i) * ABM + row] * a1;
+        if (valid) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            uint4 v;
+            v.x = pack_bf16(o[8 * i], o[8 * i + 1]);
+            v.y = pack_bf16(o[8 * i + 2], o[8 * i + 3]);
+            v.z = pack_bf16(o[8 * i + 4], o[8 * i + 5]);
+            v.w = pack_bf16(o[8 * i + 6], o[8 * i + 7]);
+            *reinterpret_cast<uint4*>(orow + c * 32 + i * 8) = v;
+          }
+        }
+      }
+      if (valid)
+        p.lse[(size_t)head * p.T + doc_start + q_idx] =
+            (l_all > 0.f) ? (m_all + log2f(l_all)) * 0.6931471805599453f : -INFINITY;
+    }
     tc_fence_before();
   }
 
