@@ -9,8 +9,9 @@
 //                              drains S from TMEM the other is in its exp2 phase, so the TMEM read
 //                              port, the MUFU pipe and the tensor pipe work concurrently. tcgen05.ld S,
 //                              online softmax in the exp2 domain with lazy rescale of O, P_j -> bf16 ->
-//                              128B-swizzled smem (A operand of the PV MMA). The two partial results
-//                              are merged at the end (through the P buffers) into O / l and the LSE.
+//                              tcgen05.st back into tensor memory over S (the PV MMA reads its A operand
+//                              from TMEM, so P never touches shared memory). The two partial results
+//                              are merged at the end (through a staging buffer) into O / l and the LSE.
 // S_{j+1} is issued before P_j is consumed so the tensor core overlaps the softmax of block j.
 // GQA (Hq = g * Hkv) and packed variable-length batches (cu_seqlens) are handled by indexing; the
 // operands are strided views (e.g. slices of one fused QKV activation), nothing is copied.
@@ -170,16 +171,15 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       mbar_wait(&p_full[s], (j >> 1) & 1);
       tc_fence_after();
       if (elect_one()) {
-        const uint32_t pa = smem_u32(sP + s * SM::kP), va = smem_u32(sV + s * SM::kV);
+        // P_j (bf16) sits in the first 64 columns of this warpgroup's S buffer: the A operand is read
+        // from tensor memory, 8 columns (16 K-elements) per MMA
+        const uint32_t va = smem_u32(sV + s * SM::kV);
 #pragma unroll
         for (int kk = 0; kk < ABN / 16; ++kk) {
-          const uint64_t da =
-              make_smem_desc_sw128(pa + (kk >> 2) * (ABM * 128) + (kk & 3) * 32, 16, 1024);
           const uint64_t db = make_smem_desc_sw128(va + kk * 2048, ABN * 128, 1024);
-          umma_f16<1>(tmem_O[s], da, db, idesc_o, (j >= 2 || kk != 0) ? 1u : 0u);
+          umma_f16_ts(tmem_O[s], tmem_S[s] + kk * 8, db, idesc_o, (j >= 2 || kk != 0) ? 1u : 0u);
         }
         umma_commit<1>(&v_empty[s]);
-        umma_commit<1>(&p_empty[s]);
         umma_commit<1>(&o_done[s]);
       }
       __syncwarp();
@@ -247,29 +247,24 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
       const float base = (m_used == -INFINITY) ? 0.f : m_used;
       float psum = 0.f;
-      mbar_wait(&p_empty[wg], (k & 1) ^ 1);  // the previous PV of this warpgroup finished reading P
-      const uint32_t pbase = smem_u32(sP + wg * SM::kP) + row * 128;
+      // P (bf16, two K-elements per 32-bit column) overwrites the first 64 columns of this warpgroup's S
+      // buffer; the next S MMA into this buffer is issued after PV_j, so tensor-pipe order protects it
 #pragma unroll
-      for (int a = 0; a < 2; ++a) {
+      for (int c = 0; c < 4; ++c) {
+        uint32_t pk[16];
 #pragma unroll
-        for (int c = 0; c < 8; ++c) {
-          uint32_t pk[4];
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const int i = a * 64 + c * 8 + e * 2;
-            const float p0 = exp2f(fmaf(sv[i], p.scale_log2, -base));
-            const float p1 = exp2f(fmaf(sv[i + 1], p.scale_log2, -base));
-            psum += p0 + p1;
-            pk[e] = pack_bf16(p0, p1);
-          }
-          const uint32_t addr = pbase + a * (ABM * 128) + ((c ^ (row & 7)) << 4);
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(pk[0]), "r"(pk[1]),
-                       "r"(pk[2]), "r"(pk[3])
-                       : "memory");
+        for (int e = 0; e < 16; ++e) {
+          const int i = c * 32 + e * 2;
+          const float p0 = exp2f(fmaf(sv[i], p.scale_log2, -base));
+          const float p1 = exp2f(fmaf(sv[i + 1], p.scale_log2, -base));
+          psum += p0 + p1;
+          pk[e] = pack_bf16(p0, p1);
         }
+        tmem_st_32x32b_x16(tmem_S[wg] + lane_off + c * 16, pk);
       }
       l += psum;
-      fence_proxy_async_smem();
+      tmem_st_wait();
+      tc_fence_before();
       __syncwarp();
       if (lane_id() == 0) mbar_arrive(&p_full[wg]);
     }
