@@ -26,6 +26,12 @@ struct PeerPtrs {
 
 struct alignas(16) V4 { uint32_t u[4]; };
 
+__device__ __forceinline__ float sqrt_approx(float x) {
+  float r;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
 __device__ __forceinline__ V4 ld_peer(const V4* ptr) {
   V4 r;
   asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
@@ -155,9 +161,9 @@ __device__ __forceinline__ void rs_finish(float (&acc)[8], size_t i, float scale
       vf.x = adam.beta2 * vf.x + (1.f - adam.beta2) * g0 * g0;
       vf.y = adam.beta2 * vf.y + (1.f - adam.beta2) * g1 * g1;
       pf.x = pf.x * adam.decay -
-             adam.step_size * __fdividef(mf.x, sqrtf(vf.x) * adam.inv_bc2_sqrt + adam.eps);
+             adam.step_size * __fdividef(mf.x, sqrt_approx(vf.x) * adam.inv_bc2_sqrt + adam.eps);
       pf.y = pf.y * adam.decay -
-             adam.step_size * __fdividef(mf.y, sqrtf(vf.y) * adam.inv_bc2_sqrt + adam.eps);
+             adam.step_size * __fdividef(mf.y, sqrt_approx(vf.y) * adam.inv_bc2_sqrt + adam.eps);
       pv.u[j] = pack_bf16(pf.x, pf.y);
       mv.u[j] = pack_bf16(mf.x, mf.y);
       vv.u[j] = pack_bf16(vf.x, vf.y);

@@ -394,61 +394,53 @@ __device__ __forceinline__ BF8 swiglu_vec(const BF8& gv, const BF8& uv) {
   bf8_to_f(gv, g);
   bf8_to_f(uv, u);
 #pragma unroll
-  for (int j = 0; j < 8; ++j) o[j] = bf16_round(g[j] / (1.f + __expf(-g[j]))) * u[j];
+  for (int j = 0; j < 8; ++j) o[j] = bf16_round(__fdividef(g[j], 1.f + __expf(-g[j]))) * u[j];
   return f_to_bf8(o);
 }
 
+// one block walks rows (grid-stride), its threads walk the 16-byte columns: no index division
 __global__ void __launch_bounds__(256)
 swiglu_fwd_kernel(__nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ gu, int T, int I) {
   const int nvec = I >> 3;
-  const size_t total = (size_t)T * nvec;
-  const size_t stride = (size_t)gridDim.x * blockDim.x;
-  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  for (; i + stride < total; i += 2 * stride) {  // two independent vectors (4 loads) in flight
-    const size_t i1 = i + stride;
-    const size_t r0 = i / nvec, r1 = i1 / nvec;
-    const int c0 = (int)(i - r0 * nvec), c1 = (int)(i1 - r1 * nvec);
-    const BF8* b0 = reinterpret_cast<const BF8*>(gu + r0 * 2 * (size_t)I);
-    const BF8* b1 = reinterpret_cast<const BF8*>(gu + r1 * 2 * (size_t)I);
-    const BF8 g0 = ld_stream(b0 + c0), u0 = ld_stream(b0 + nvec + c0);
-    const BF8 g1 = ld_stream(b1 + c1), u1 = ld_stream(b1 + nvec + c1);
-    reinterpret_cast<BF8*>(out + r0 * (size_t)I)[c0] = swiglu_vec(g0, u0);
-    reinterpret_cast<BF8*>(out + r1 * (size_t)I)[c1] = swiglu_vec(g1, u1);
-  }
-  if (i < total) {
-    const size_t r0 = i / nvec;
-    const int c0 = (int)(i - r0 * nvec);
-    const BF8* b0 = reinterpret_cast<const BF8*>(gu + r0 * 2 * (size_t)I);
-    reinterpret_cast<BF8*>(out + r0 * (size_t)I)[c0] = swiglu_vec(ld_stream(b0 + c0), ld_stream(b0 + nvec + c0));
+  for (int row = blockIdx.x; row < T; row += gridDim.x) {
+    const BF8* g = reinterpret_cast<const BF8*>(gu + (size_t)row * 2 * I);
+    const BF8* u = g + nvec;
+    BF8* o = reinterpret_cast<BF8*>(out + (size_t)row * I);
+    int c = threadIdx.x;
+    for (; c + 256 < nvec; c += 512) {  // two independent vectors (4 loads) in flight
+      const BF8 g0 = ld_stream(g + c), u0 = ld_stream(u + c);
+      const BF8 g1 = ld_stream(g + c + 256), u1 = ld_stream(u + c + 256);
+      o[c] = swiglu_vec(g0, u0);
+      o[c + 256] = swiglu_vec(g1, u1);
+    }
+    if (c < nvec) o[c] = swiglu_vec(ld_stream(g + c), ld_stream(u + c));
   }
 }
 
-__global__ void swiglu_bwd_kernel(__nv_bfloat16* __restrict__ dgu,
-                                  const __nv_bfloat16* __restrict__ dout,
-                                  const __nv_bfloat16* __restrict__ gu, int T, int I) {
+__global__ void __launch_bounds__(256)
+swiglu_bwd_kernel(__nv_bfloat16* __restrict__ dgu, const __nv_bfloat16* __restrict__ dout,
+                  const __nv_bfloat16* __restrict__ gu, int T, int I) {
   const int nvec = I >> 3;
-  const size_t total = (size_t)T * nvec;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (size_t)gridDim.x * blockDim.x) {
-    const size_t row = i / nvec;
-    const int c = (int)(i - row * nvec);
-    const BF8* base = reinterpret_cast<const BF8*>(gu + row * 2 * (size_t)I);
-    float g[8], u[8], d[8], dg[8], du[8];
-    const BF8 gv = ld_stream(base + c), uv = ld_stream(base + nvec + c);
-    const BF8 dv = ld_stream(reinterpret_cast<const BF8*>(dout + row * (size_t)I) + c);
-    bf8_to_f(gv, g);
-    bf8_to_f(uv, u);
-    bf8_to_f(dv, d);
+  for (int row = blockIdx.x; row < T; row += gridDim.x) {
+    const BF8* gp = reinterpret_cast<const BF8*>(gu + (size_t)row * 2 * I);
+    const BF8* dp = reinterpret_cast<const BF8*>(dout + (size_t)row * I);
+    BF8* ob = reinterpret_cast<BF8*>(dgu + (size_t)row * 2 * I);
+    for (int c = threadIdx.x; c < nvec; c += 256) {
+      const BF8 gv = ld_stream(gp + c), uv = ld_stream(gp + nvec + c), dv = ld_stream(dp + c);
+      float g[8], u[8], d[8], dg[8], du[8];
+      bf8_to_f(gv, g);
+      bf8_to_f(uv, u);
+      bf8_to_f(dv, d);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float sig = 1.f / (1.f + __expf(-g[j]));
-      const float silu = g[j] * sig;
-      du[j] = d[j] * silu;
-      dg[j] = d[j] * u[j] * (sig * (1.f + g[j] * (1.f - sig)));
+      for (int j = 0; j < 8; ++j) {
+        const float sig = __fdividef(1.f, 1.f + __expf(-g[j]));
+        const float silu = g[j] * sig;
+        du[j] = d[j] * silu;
+        dg[j] = d[j] * u[j] * (sig * (1.f + g[j] * (1.f - sig)));
+      }
+      ob[c] = f_to_bf8(dg);
+      ob[nvec + c] = f_to_bf8(du);
     }
-    BF8* ob = reinterpret_cast<BF8*>(dgu + row * 2 * (size_t)I);
-    ob[c] = f_to_bf8(dg);
-    ob[nvec + c] = f_to_bf8(du);
   }
 }
 
@@ -673,6 +665,12 @@ ce_bwd_kernel(__nv_bfloat16* __restrict__ dlogits, const __nv_bfloat16* __restri
 // params: fp32 math per element, decoupled weight decay, bias correction). `grad_scale` folds the
 // 1/world factor of a data-parallel mean into the update.
 // ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float sqrt_approx(float x) {
+  float r;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
 __device__ __forceinline__ void adamw_vec(float (&pf)[8], float (&mf)[8], float (&vf)[8],
                                           const float (&gf)[8], float decay, float beta1,
                                           float beta2, float eps, float step_size,
@@ -682,7 +680,7 @@ __device__ __forceinline__ void adamw_vec(float (&pf)[8], float (&mf)[8], float 
     const float gr = gf[j] * grad_scale;
     mf[j] = beta1 * mf[j] + (1.f - beta1) * gr;
     vf[j] = beta2 * vf[j] + (1.f - beta2) * gr * gr;
-    const float denom = sqrtf(vf[j]) * inv_bc2_sqrt + eps;
+    const float denom = sqrt_approx(vf[j]) * inv_bc2_sqrt + eps;
     pf[j] = pf[j] * decay - step_size * __fdividef(mf[j], denom);
   }
 }
@@ -839,15 +837,15 @@ int b2_layernorm_bwd(void* dx, void* dw, void* db, float* partial, const void* d
 int b2_swiglu_fwd(void* out, const void* gu, int T, int I, cudaStream_t stream) {
   B2_REQUIRE(I % 8 == 0, "swiglu: I=%d not a multiple of 8", I);
   if (T == 0) return 0;
-  swiglu_fwd_kernel<<<ew_grid((size_t)T * (I / 8), 256), 256, 0, stream>>>((bf16*)out,
-                                                                           (const bf16*)gu, T, I);
+  swiglu_fwd_kernel<<<T < sm_count() * 8 ? T : sm_count() * 8, 256, 0, stream>>>((bf16*)out,
+                                                                                 (const bf16*)gu, T, I);
   B2_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
 int b2_swiglu_bwd(void* dgu, const void* dout, const void* gu, int T, int I, cudaStream_t stream) {
   B2_REQUIRE(I % 8 == 0, "swiglu: I=%d not a multiple of 8", I);
   if (T == 0) return 0;
-  swiglu_bwd_kernel<<<ew_grid((size_t)T * (I / 8), 256), 256, 0, stream>>>(
+  swiglu_bwd_kernel<<<T < sm_count() * 8 ? T : sm_count() * 8, 256, 0, stream>>>(
       (bf16*)dgu, (const bf16*)dout, (const bf16*)gu, T, I);
   B2_CUDA_CHECK(cudaGetLastError());
   return 0;
