@@ -478,46 +478,43 @@ __global__ void gelu_kernel(__nv_bfloat16* __restrict__ out, const __nv_bfloat16
 // x: [T, row_stride] ; cos/sin: [P, D] bf16 tables ; pos: [T] int32 (nullptr -> t % seq_len)
 // out = x*cos + rotate_half(x)*sin ; sign = -1 applies the transpose (backward).
 // ------------------------------------------------------------------------------------------------
-__global__ void rope_kernel(__nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ cosT,
-                            const __nv_bfloat16* __restrict__ sinT, const int* __restrict__ pos,
-                            int T, int nheads, int D, int row_stride, int seq_len, float sign) {
+__global__ void __launch_bounds__(256)
+rope_kernel(__nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ cosT,
+            const __nv_bfloat16* __restrict__ sinT, const int* __restrict__ pos, int T, int nheads,
+            int D, int row_stride, int seq_len, float sign) {
   const int half_vec = D >> 4;  // 16B vectors per half head
-  const size_t total = (size_t)T * nheads * half_vec;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (size_t)gridDim.x * blockDim.x) {
-    const int c = (int)(i % half_vec);
-    const size_t th = i / half_vec;
-    const int head = (int)(th % nheads);
-    const size_t t = th / nheads;
-    const int p = pos ? pos[t] : (int)(t % seq_len);
-    __nv_bfloat16* base = x + t * (size_t)row_stride + (size_t)head * D;
-    BF8* lo = reinterpret_cast<BF8*>(base) + c;
-    BF8* hi = reinterpret_cast<BF8*>(base + (D >> 1)) + c;
-    const BF8* cl = reinterpret_cast<const BF8*>(cosT + (size_t)p * D) + c;
-    const BF8* ch = reinterpret_cast<const BF8*>(cosT + (size_t)p * D + (D >> 1)) + c;
-    const BF8* sl = reinterpret_cast<const BF8*>(sinT + (size_t)p * D) + c;
-    const BF8* sh = reinterpret_cast<const BF8*>(sinT + (size_t)p * D + (D >> 1)) + c;
-    float a[8], b[8], c0[8], c1[8], s0[8], s1[8], oa[8], ob[8];
-    bf8_to_f(*lo, a);
-    bf8_to_f(*hi, b);
-    bf8_to_f(*cl, c0);
-    bf8_to_f(*ch, c1);
-    bf8_to_f(*sl, s0);
-    bf8_to_f(*sh, s1);
+  const int per_row = nheads * half_vec;
+  for (int t = blockIdx.x; t < T; t += gridDim.x) {  // one token row per block trip: no index division
+    const int p = pos ? pos[t] : t % seq_len;
+    const __nv_bfloat16* crow = cosT + (size_t)p * D;
+    const __nv_bfloat16* srow = sinT + (size_t)p * D;
+    for (int i = threadIdx.x; i < per_row; i += blockDim.x) {
+      const int head = i / half_vec, c = i - head * half_vec;
+      __nv_bfloat16* base = x + (size_t)t * row_stride + (size_t)head * D;
+      BF8* lo = reinterpret_cast<BF8*>(base) + c;
+      BF8* hi = reinterpret_cast<BF8*>(base + (D >> 1)) + c;
+      float a[8], b[8], c0[8], c1[8], s0[8], s1[8], oa[8], ob[8];
+      bf8_to_f(*lo, a);
+      bf8_to_f(*hi, b);
+      bf8_to_f(reinterpret_cast<const BF8*>(crow)[c], c0);
+      bf8_to_f(reinterpret_cast<const BF8*>(crow + (D >> 1))[c], c1);
+      bf8_to_f(reinterpret_cast<const BF8*>(srow)[c], s0);
+      bf8_to_f(reinterpret_cast<const BF8*>(srow + (D >> 1))[c], s1);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      if (sign > 0.f) {
-        // rotate_half(x) = [-x_hi, x_lo]
-        oa[j] = a[j] * c0[j] - b[j] * s0[j];
-        ob[j] = b[j] * c1[j] + a[j] * s1[j];
-      } else {
-        // transpose: d_lo = g_lo*cos_lo + g_hi*sin_hi ; d_hi = g_hi*cos_hi - g_lo*sin_lo
-        oa[j] = a[j] * c0[j] + b[j] * s1[j];
-        ob[j] = b[j] * c1[j] - a[j] * s0[j];
+      for (int j = 0; j < 8; ++j) {
+        if (sign > 0.f) {
+          // rotate_half(x) = [-x_hi, x_lo]
+          oa[j] = a[j] * c0[j] - b[j] * s0[j];
+          ob[j] = b[j] * c1[j] + a[j] * s1[j];
+        } else {
+          // transpose: d_lo = g_lo*cos_lo + g_hi*sin_hi ; d_hi = g_hi*cos_hi - g_lo*sin_lo
+          oa[j] = a[j] * c0[j] + b[j] * s1[j];
+          ob[j] = b[j] * c1[j] - a[j] * s0[j];
+        }
       }
+      *lo = f_to_bf8(oa);
+      *hi = f_to_bf8(ob);
     }
-    *lo = f_to_bf8(oa);
-    *hi = f_to_bf8(ob);
   }
 }
 
@@ -872,7 +869,7 @@ int b2_rope(void* x, const void* cosT, const void* sinT, const int* pos, int T, 
   B2_REQUIRE(D % 16 == 0 && row_stride % 8 == 0, "rope: D=%d row_stride=%d unsupported", D,
              row_stride);
   if (T == 0 || nheads == 0) return 0;
-  rope_kernel<<<ew_grid((size_t)T * nheads * (D / 16), 256), 256, 0, stream>>>(
+  rope_kernel<<<T < sm_count() * 8 ? T : sm_count() * 8, 256, 0, stream>>>(
       (bf16*)x, (const bf16*)cosT, (const bf16*)sinT, pos, T, nheads, D, row_stride, seq_len,
       backward ? -1.f : 1.f);
   B2_CUDA_CHECK(cudaGetLastError());
