@@ -186,3 +186,26 @@ def to_hf_dict(cfg: ModelConfig) -> dict:
     if cfg.rope_scaling:
         d["rope_scaling"] = dict(cfg.rope_scaling)
     return d
+
+
+def group_by_numel(sizes, min_numel: int):
+    """Greedy grouping of consecutive layers into wrap units of at least ``min_numel`` parameters.
+
+    Stands in for ``size_based_auto_wrap_policy(min_num_params=--numel-to-wrap)``
+    (``04-fully-sharded-data-parallel/train_llm.py:84-86``): a layer that is large enough is its own unit,
+    smaller layers are merged with their successors (GPT-2's twelve 7 M-parameter blocks become one unit at
+    the default 100 M, as they end up in the root wrap of the reference). A short tail joins the last group.
+    """
+    groups, cur, acc = [], [], 0
+    for i, n in enumerate(sizes):
+        cur.append(i)
+        acc += n
+        if acc >= min_numel:
+            groups.append(cur)
+            cur, acc = [], 0
+    if cur:
+        if groups and min_numel > 0:
+            groups[-1].extend(cur)
+        else:
+            groups.append(cur)
+    return groups

@@ -96,6 +96,7 @@ class GPT2LMHeadModel(nn.Module):
         self.lm_head = nn.Linear(cfg.hidden_size, cfg.vocab_size, bias=False, dtype=dtype, device=device)
         self.lm_head.weight = self.transformer.wte.weight  # tied
         self.unit_runner = None  # see LlamaForCausalLM
+        self.layer_groups = None
 
     @torch.no_grad()
     def init_weights(self, seed: Optional[int] = None):
@@ -117,10 +118,21 @@ class GPT2LMHeadModel(nn.Module):
     def units(self):
         t = self.transformer
         out = [("transformer.wte+wpe", [t.wte.weight, t.wpe.weight])]
-        for i, blk in enumerate(t.h):
-            out.append((f"transformer.h.{i}", list(blk.parameters())))
+        for g in self._groups():
+            name = f"transformer.h.{g[0]}" if len(g) == 1 else f"transformer.h.{g[0]}-{g[-1]}"
+            out.append((name, [p for j in g for p in t.h[j].parameters()]))
         out.append(("transformer.ln_f", list(t.ln_f.parameters())))
         return out
+
+    def _groups(self):
+        return self.layer_groups or [[i] for i in range(len(self.transformer.h))]
+
+    def group_layers(self, min_numel: int):
+        """Merge consecutive blocks into wrap units of >= ``min_numel`` parameters (``--numel-to-wrap``)."""
+        from .config import group_by_numel
+
+        sizes = [sum(p.numel() for p in blk.parameters()) for blk in self.transformer.h]
+        self.layer_groups = group_by_numel(sizes, min_numel) if min_numel > 0 else None
 
     @property
     def layers(self):
@@ -144,12 +156,15 @@ class GPT2LMHeadModel(nn.Module):
         flat_ids, flat_pos = input_ids.reshape(-1), position_ids.reshape(-1)
         h = self._run(0, lambda: ops.embedding(flat_ids, t.wte.weight) + ops.embedding(flat_pos, t.wpe.weight))
         delta = None
-        for i, blk in enumerate(t.h):
-            if delta is None:
-                h, delta = self._run(i + 1, lambda a, blk=blk: blk(a, None, ctx), h)
-            else:
-                h, delta = self._run(i + 1, lambda a, b, blk=blk: blk(a, b, ctx), h, delta)
-        L = len(t.h)
+        groups = self._groups()
+        for gi, g in enumerate(groups):
+            def run_group(a, b=None, g=g):
+                for j in g:
+                    a, b = t.h[j](a, b, ctx)
+                return a, b
+
+            h, delta = self._run(gi + 1, run_group, h) if delta is None else self._run(gi + 1, run_group, h, delta)
+        L = len(groups)
         shifted = ops.shift_labels(labels).reshape(-1) if labels is not None else None
 
         def head(a, b=None):

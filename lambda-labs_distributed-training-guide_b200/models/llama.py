@@ -128,6 +128,8 @@ class LlamaForCausalLM(nn.Module):
         # unit_runner(unit_index, fn, *tensors) -> fn(*tensors); unit 0 = embedding, 1..L = layers,
         # L+1 = final norm + head (same order as units())
         self.unit_runner = None
+        self.layer_groups = None  # None: every layer is its own unit (see group_layers)
+        self.layer_groups = None  # None: every layer is its own unit (see group_layers)
 
     # ---- init (HF _init_weights: normal(0, initializer_range) for linears / embeddings, ones for norms)
     @torch.no_grad()
@@ -149,13 +151,26 @@ class LlamaForCausalLM(nn.Module):
     #      05-training-llama-405b/train_llm.py:101-107)
     def units(self):
         out = [("model.embed_tokens", [self.model.embed_tokens.weight])]
-        for i, layer in enumerate(self.model.layers):
-            out.append((f"model.layers.{i}", list(layer.parameters())))
+        for g in self._groups():
+            name = f"model.layers.{g[0]}" if len(g) == 1 else f"model.layers.{g[0]}-{g[-1]}"
+            out.append((name, [p for j in g for p in self.model.layers[j].parameters()]))
         tail = [self.model.norm.weight]
         if not self.config.tie_word_embeddings:
             tail.append(self.lm_head.weight)
         out.append(("model.norm+lm_head", tail))
         return out
+
+    def _groups(self):
+        return self.layer_groups or [[i] for i in range(len(self.model.layers))]
+
+    def group_layers(self, min_numel: int):
+        """Merge consecutive layers into wrap units of >= ``min_numel`` parameters (``--numel-to-wrap``,
+        ``04-fully-sharded-data-parallel/train_llm.py:84-86``). Must be called before a strategy lays
+        out its flat storage."""
+        from .config import group_by_numel
+
+        sizes = [sum(p.numel() for p in layer.parameters()) for layer in self.model.layers]
+        self.layer_groups = group_by_numel(sizes, min_numel) if min_numel > 0 else None
 
     def _rope_tables(self, device, n):
         if self._rope is None or self._rope[0].device != device or self._rope[0].shape[0] < n:
@@ -187,12 +202,15 @@ class LlamaForCausalLM(nn.Module):
         flat_ids = input_ids.reshape(-1)
         h = self._run(0, lambda: ops.embedding(flat_ids, self.model.embed_tokens.weight))
         delta = None
-        for i, layer in enumerate(self.model.layers):
-            if delta is None:
-                h, delta = self._run(i + 1, lambda a, layer=layer: layer(a, None, ctx), h)
-            else:
-                h, delta = self._run(i + 1, lambda a, b, layer=layer: layer(a, b, ctx), h, delta)
-        L = len(self.model.layers)
+        layers, groups = self.model.layers, self._groups()
+        for gi, g in enumerate(groups):
+            def run_group(a, b=None, g=g):
+                for j in g:
+                    a, b = layers[j](a, b, ctx)
+                return a, b
+
+            h, delta = self._run(gi + 1, run_group, h) if delta is None else self._run(gi + 1, run_group, h, delta)
+        L = len(groups)
         shifted = ops.shift_labels(labels).reshape(-1) if labels is not None else None
 
         def head(a, b=None):

@@ -98,6 +98,8 @@ class FSDP(Strategy):
 
         # ---- model skeleton on the meta device; units define the flat layout -------------------
         self.model = self._build_meta_model(cfg, dtype)
+        if numel_to_wrap and hasattr(self.model, "group_layers"):
+            self.model.group_layers(numel_to_wrap)
         self.units: List[_Layout] = [_Layout(name, params, self.W) for name, params in self.model.units()]
         n_units = len(self.units)
         max_numel = max(u.numel for u in self.units)

@@ -234,3 +234,24 @@ def test_dcp_roundtrip_tensor_parallel(strategy, world):
     tmp = tempfile.mkdtemp()
     nxt, got = run_dist("w_dcp_2d", tmp, strategy, world=world)[0]
     assert abs(nxt - got) < 1e-5, (nxt, got)
+
+
+def test_fsdp_size_based_wrap_groups_layers():
+    """--numel-to-wrap merges consecutive layers into one sharding unit without changing the maths."""
+    from b200train.models import build_model, load_config
+    from b200train.models.config import group_by_numel
+
+    assert group_by_numel([5, 5, 5, 5, 5], 10) == [[0, 1], [2, 3, 4]]
+    assert group_by_numel([20, 3, 20], 10) == [[0], [1, 2]]
+    assert group_by_numel([1, 1], 100) == [[0, 1]]
+    cfg = load_config("llama-tiny")
+    model = build_model(cfg, dtype=torch.float32, device="meta", init=False)
+    per_layer = sum(p.numel() for p in model.model.layers[0].parameters())
+    n_before = len(model.units())
+    model.group_layers(2 * per_layer)
+    assert len(model.units()) == n_before - cfg.num_hidden_layers + cfg.num_hidden_layers // 2
+    kw = dict(numel_to_wrap=2 * per_layer)  # weights are initialised per unit: same layout on both sides
+    ref = _single_losses("fsdp", kw)
+    got = _dist_losses("fsdp", kw)
+    for a, b in zip(ref, got):
+        assert abs(a - b) < 2e-3, (ref, got)
