@@ -60,9 +60,21 @@ def main():
     res["peer_ag_ce_ms"] = timed(lambda: comm.all_gather(full, shard, copy_engine=True))
     for mb in (16, 32, 64, 128):
         res[f"peer_ag_ms_b{mb}"] = timed(lambda: comm.all_gather(full, shard, max_blocks=mb, copy_engine=False))
-        res[f"peer_rs_ms_b{mb}"] = timed(lambda: comm.reduce_scatter(out_shard, full_sym, max_blocks=mb))
+        res[f"peer_rs_ms_b{mb}"] = timed(lambda: comm.reduce_scatter(out_shard, full_sym, max_blocks=mb, nvls=False))
         res[f"peer_rs_adamw_ms_b{mb}"] = timed(
-            lambda: comm.reduce_scatter_adamw(p, m, v, full_sym, 1e-4, 0.9, 0.999, 1e-8, 0.01, 3, max_blocks=mb))
+            lambda: comm.reduce_scatter_adamw(p, m, v, full_sym, 1e-4, 0.9, 0.999, 1e-8, 0.01, 3, max_blocks=mb, nvls=False))
+
+    res["nvls"] = bool(comm.has_nvls)
+    if comm.has_nvls:
+        ar_buf = comm.empty(numel)
+        ar_buf.normal_()
+        res["nccl_ar_ms"] = timed(lambda: dist.all_reduce(ar_buf, op=dist.ReduceOp.AVG))
+        res["peer_ar_ms_b64"] = timed(lambda: comm.all_reduce(ar_buf, max_blocks=64, nvls=False))
+        for mb in (16, 32, 64, 128):
+            res[f"nvls_rs_ms_b{mb}"] = timed(lambda: comm.reduce_scatter(out_shard, full_sym, max_blocks=mb, nvls=True))
+            res[f"nvls_rs_adamw_ms_b{mb}"] = timed(lambda: comm.reduce_scatter_adamw(
+                p, m, v, full_sym, 1e-4, 0.9, 0.999, 1e-8, 0.01, 3, max_blocks=mb, nvls=True))
+            res[f"nvls_ar_ms_b{mb}"] = timed(lambda: comm.all_reduce(ar_buf, max_blocks=mb, nvls=True))
 
     # overlap: a chain of GEMMs on the main stream with collectives on a side stream
     A = torch.randn(4096, 4096, device=device).to(torch.bfloat16)
@@ -90,14 +102,19 @@ def main():
                                                                                     op=dist.ReduceOp.AVG))))
     res["gemm+peer_agce_rs_ms_b64"] = timed(overlapped(lambda: (comm.all_gather(full, shard, copy_engine=True),
                                                                 comm.reduce_scatter(out_shard, full_sym,
-                                                                                    max_blocks=64))))
+                                                                                    max_blocks=64, nvls=False))))
+    if comm.has_nvls:
+        for mb in (16, 32, 64):
+            res[f"gemm+peer_agce_nvls_rs_ms_b{mb}"] = timed(overlapped(
+                lambda: (comm.all_gather(full, shard, copy_engine=True),
+                         comm.reduce_scatter(out_shard, full_sym, max_blocks=mb, nvls=True))))
     for mb in (32, 64, 128):
         res[f"gemm+peer_ag_rs_ms_b{mb}"] = timed(overlapped(lambda: (comm.all_gather(full, shard, max_blocks=mb, copy_engine=False),
                                                                      comm.reduce_scatter(out_shard, full_sym,
-                                                                                         max_blocks=mb))))
+                                                                                         max_blocks=mb, nvls=False))))
         res[f"gemm+peer_ag_rsadamw_ms_b{mb}"] = timed(overlapped(
             lambda: (comm.all_gather(full, shard, max_blocks=mb, copy_engine=False),
-                     comm.reduce_scatter_adamw(p, m, v, full_sym, 1e-4, 0.9, 0.999, 1e-8, 0.01, 3, max_blocks=mb))))
+                     comm.reduce_scatter_adamw(p, m, v, full_sym, 1e-4, 0.9, 0.999, 1e-8, 0.01, 3, max_blocks=mb, nvls=False))))
     if rank == 0:
         for k, val in res.items():
             print(f"{k:36s} {val:10.3f}" if isinstance(val, float) else f"{k:36s} {val}")

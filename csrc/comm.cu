@@ -11,6 +11,9 @@
 //   b2_peer_reduce_scatter_adamw    the same reduction feeding AdamW on the owned parameter shard in
 //                                   registers: the reduced gradient shard never touches memory
 //   b2_peer_all_reduce              two-phase all-reduce on a symmetric buffer (DDP buckets, TP norm grads)
+//   b2_nvls_reduce_scatter(_adamw)  the reduction done by the NVSwitch: one multimem.ld_reduce on the
+//   b2_nvls_all_reduce              multicast mapping returns the sum over all ranks (NVLS), and
+//                                   multimem.st writes a result into every rank's copy at once
 //
 // Reference: the NCCL collectives issued implicitly by DistributedDataParallel / FullyShardedDataParallel
 // / ZeroRedundancyOptimizer (02-distributed-data-parallel/train_llm.py:65,81-83,
@@ -295,6 +298,107 @@ peer_all_reduce_kernel(PeerPtrs buf, size_t n16_slice, int rank, int W, float sc
   }
 }
 
+// ---- NVLS (in-switch reduction / multicast) variants -----------------------------------------------
+// `mc` is the multicast mapping of a symmetric buffer: a load-reduce on it makes the NVSwitch fetch the
+// same offset from every rank and return the fp32-accumulated sum (rounded to bf16 once), a store on
+// it lands in every rank's copy. Per reduced 16 bytes a rank issues ONE load instead of W, and only
+// 1/W of the unit crosses its NVLink receive side.
+__device__ __forceinline__ V4 multimem_ld_reduce_bf16x8(const V4* mc) {
+  V4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.u[0]), "=r"(r.u[1]), "=r"(r.u[2]), "=r"(r.u[3])
+               : "l"(mc)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ void multimem_st(V4* mc, const V4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "r"(v.u[0]),
+               "r"(v.u[1]), "r"(v.u[2]), "r"(v.u[3])
+               : "memory");
+}
+
+template <bool kAdam>
+__global__ void __launch_bounds__(kCommThreads, 3)
+nvls_reduce_scatter_kernel(V4* __restrict__ out_shard, const V4* __restrict__ mc_full, size_t n16,
+                           int rank, int W, float scale, PeerPtrs pads, int chan_base, uint32_t epoch,
+                           unsigned int* counter, AdamArgs adam) {
+  if (blockIdx.x == 0) {
+    __threadfence_system();
+    signal_peers(pads, rank, W, chan_base + kChanIn, epoch);
+  }
+  wait_peers(pads, rank, W, chan_base + kChanIn, epoch);
+  constexpr int U = kAdam ? 2 : 4;
+  const V4* src = mc_full + (size_t)rank * n16;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n16; i0 += U * stride) {
+    V4 g[U], pv[U], mv[U], vv[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = i0 + u * stride;
+      if (i < n16) {
+        g[u] = multimem_ld_reduce_bf16x8(src + i);
+        if constexpr (kAdam) {
+          pv[u] = reinterpret_cast<V4*>(adam.p)[i];
+          mv[u] = reinterpret_cast<V4*>(adam.m)[i];
+          vv[u] = reinterpret_cast<V4*>(adam.v)[i];
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = i0 + u * stride;
+      if (i < n16) {
+        float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        acc_bf16x8(acc, g[u]);
+        rs_finish<kAdam>(acc, i, scale, out_shard, adam, pv[u], mv[u], vv[u]);
+      }
+    }
+  }
+  if (last_block_done(counter)) {  // every rank has finished reading: the full buffers may be reused
+    __threadfence_system();
+    signal_peers(pads, rank, W, chan_base + kChanOut, epoch);
+    wait_peers(pads, rank, W, chan_base + kChanOut, epoch);
+  }
+}
+
+// In-place all-reduce: rank r load-reduces slice r through the switch and multicasts the result into
+// every rank's buffer; one pass over 1/W of the data per rank.
+__global__ void __launch_bounds__(kCommThreads, 3)
+nvls_all_reduce_kernel(V4* __restrict__ mc, size_t n16_slice, int rank, int W, float scale,
+                       PeerPtrs pads, int chan_base, uint32_t epoch, unsigned int* counter) {
+  if (blockIdx.x == 0) {
+    __threadfence_system();
+    signal_peers(pads, rank, W, chan_base + kChanIn, epoch);
+  }
+  wait_peers(pads, rank, W, chan_base + kChanIn, epoch);
+  V4* slice = mc + (size_t)rank * n16_slice;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n16_slice; i0 += 4 * stride) {
+    V4 g[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (i0 + u * stride < n16_slice) g[u] = multimem_ld_reduce_bf16x8(slice + i0 + u * stride);
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (i0 + u * stride < n16_slice) {
+        if (scale != 1.f) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float2 f = unpack_bf16(g[u].u[j]);
+            g[u].u[j] = pack_bf16(f.x * scale, f.y * scale);
+          }
+        }
+        multimem_st(slice + i0 + u * stride, g[u]);
+      }
+  }
+  // my slice has reached every rank, and every rank's slice has reached me
+  if (last_block_done(counter)) {
+    __threadfence_system();
+    signal_peers(pads, rank, W, chan_base + kChanOut, epoch);
+    wait_peers(pads, rank, W, chan_base + kChanOut, epoch);
+  }
+}
+
 static int clamp_blocks(size_t work16, int max_blocks) {
   size_t b = (work16 + kCommThreads - 1) / kCommThreads;
   int cap = max_blocks > 0 ? max_blocks : 64;
@@ -396,6 +500,62 @@ int b2_peer_all_reduce(void* const* bufs, size_t elems, int rank, int W, float s
   const size_t n16_slice = elems / 8 / W;
   peer_all_reduce_kernel<<<clamp_blocks(n16_slice, max_blocks), 256, 0, stream>>>(
       to_ptrs(bufs, W), n16_slice, rank, W, scale, to_ptrs(pads, W), chan_base, epoch, counter);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// NVLS variants: `mc_full` / `mc_buf` is the multicast address of the symmetric buffer (0 when the
+// platform has no multicast support: callers then use the peer-load kernels above).
+int b2_nvls_reduce_scatter(void* out_shard, const void* mc_full, size_t shard_elems, int rank, int W,
+                           float scale, void* const* pads, int chan_base, unsigned int epoch,
+                           unsigned int* counter, int max_blocks, cudaStream_t stream) {
+  B2_REQUIRE(W >= 1 && W <= kMaxPeers, "peer collectives support up to %d ranks (got %d)", kMaxPeers, W);
+  B2_REQUIRE(mc_full != nullptr, "nvls reduce_scatter: no multicast mapping%s", "");
+  B2_REQUIRE(shard_elems % 8 == 0, "reduce_scatter: shard of %zu elements is not a multiple of 8", shard_elems);
+  const size_t n16 = shard_elems / 8;
+  AdamArgs none = {};
+  nvls_reduce_scatter_kernel<false><<<clamp_blocks(n16, max_blocks), kCommThreads, 0, stream>>>(
+      static_cast<V4*>(out_shard), static_cast<const V4*>(mc_full), n16, rank, W, scale,
+      to_ptrs(pads, W), chan_base, epoch, counter, none);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int b2_nvls_reduce_scatter_adamw(void* p, void* m, void* v, const void* mc_full, size_t shard_elems,
+                                 int rank, int W, float grad_scale, float lr, float beta1,
+                                 float beta2, float eps, float wd, int step, void* const* pads,
+                                 int chan_base, unsigned int epoch, unsigned int* counter,
+                                 int max_blocks, cudaStream_t stream) {
+  B2_REQUIRE(W >= 1 && W <= kMaxPeers, "peer collectives support up to %d ranks (got %d)", kMaxPeers, W);
+  B2_REQUIRE(mc_full != nullptr, "nvls reduce_scatter: no multicast mapping%s", "");
+  B2_REQUIRE(shard_elems % 8 == 0, "reduce_scatter: shard of %zu elements is not a multiple of 8", shard_elems);
+  const size_t n16 = shard_elems / 8;
+  AdamArgs a;
+  a.p = static_cast<__nv_bfloat16*>(p);
+  a.m = static_cast<__nv_bfloat16*>(m);
+  a.v = static_cast<__nv_bfloat16*>(v);
+  a.decay = 1.f - lr * wd;
+  a.beta1 = beta1;
+  a.beta2 = beta2;
+  a.eps = eps;
+  a.step_size = lr / (1.f - powf(beta1, (float)step));
+  a.inv_bc2_sqrt = 1.f / sqrtf(1.f - powf(beta2, (float)step));
+  nvls_reduce_scatter_kernel<true><<<clamp_blocks(n16, max_blocks), kCommThreads, 0, stream>>>(
+      nullptr, static_cast<const V4*>(mc_full), n16, rank, W, grad_scale, to_ptrs(pads, W), chan_base,
+      epoch, counter, a);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int b2_nvls_all_reduce(void* mc_buf, size_t elems, int rank, int W, float scale, void* const* pads,
+                       int chan_base, unsigned int epoch, unsigned int* counter, int max_blocks,
+                       cudaStream_t stream) {
+  B2_REQUIRE(W >= 1 && W <= kMaxPeers, "peer collectives support up to %d ranks (got %d)", kMaxPeers, W);
+  B2_REQUIRE(mc_buf != nullptr, "nvls all_reduce: no multicast mapping%s", "");
+  B2_REQUIRE(elems % (8 * (size_t)W) == 0, "all_reduce: %zu elements not a multiple of 8*W", elems);
+  const size_t n16_slice = elems / 8 / W;
+  nvls_all_reduce_kernel<<<clamp_blocks(n16_slice, max_blocks), kCommThreads, 0, stream>>>(
+      static_cast<V4*>(mc_buf), n16_slice, rank, W, scale, to_ptrs(pads, W), chan_base, epoch, counter);
   B2_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

@@ -111,6 +111,62 @@ int b2_adamw(void* p, void* m, void* v, const void* g, size_t n, float lr, float
              b2_stream_t stream);
 int b2_add(void* out, const void* a, const void* b, size_t n, b2_stream_t stream);
 
+/* ---- host AdamW for CPU-offloaded shards (OpenMP) -----------------------------------------------
+ * Reference: AdamW(fused=True) running on CPU under CPUOffload, 05-training-llama-405b/README.md:147-153. */
+int b2_cpu_adamw_bf16(void* p, void* m, void* v, const void* g, size_t n, float lr, float beta1,
+                      float beta2, float eps, float wd, int step, float grad_scale);
+
+/* ---- NVLink / NVSwitch peer-memory collectives (one process per GPU, one node) -------------------
+ * Pointer arrays hold W peer-mapped addresses of the same symmetric buffer, index = rank. `pads` is the
+ * symmetric signal pad (uint32 [channel][16]); `epoch` increases by one per call and channel pair;
+ * `counter` is one zeroed uint32 in local memory per stream.
+ * Reference: the NCCL collectives issued by DistributedDataParallel / ZeroRedundancyOptimizer /
+ * FullyShardedDataParallel (02-distributed-data-parallel/train_llm.py:65,81-83,
+ * 04-fully-sharded-data-parallel/train_llm.py:87-95) and the separate optimizer.step() (04-...:213). */
+int b2_peer_barrier(void* const* pads, int rank, int W, int channel, unsigned int epoch,
+                    b2_stream_t stream);
+int b2_peer_all_gather(void* dst, void* const* srcs, size_t shard_bytes, int rank, int W,
+                       int skip_self, int max_blocks, b2_stream_t stream);
+int b2_peer_all_gather_ce(void* dst, void* const* srcs, size_t shard_bytes, int rank, int W,
+                          int skip_self, b2_stream_t stream);
+int b2_peer_reduce_scatter(void* out_shard, void* const* fulls, size_t shard_elems, int rank, int W,
+                           float scale, void* const* pads, int chan_base, unsigned int epoch,
+                           unsigned int* counter, int max_blocks, b2_stream_t stream);
+int b2_peer_reduce_scatter_adamw(void* p, void* m, void* v, void* const* fulls, size_t shard_elems,
+                                 int rank, int W, float grad_scale, float lr, float beta1,
+                                 float beta2, float eps, float wd, int step, void* const* pads,
+                                 int chan_base, unsigned int epoch, unsigned int* counter,
+                                 int max_blocks, b2_stream_t stream);
+int b2_peer_all_reduce(void* const* bufs, size_t elems, int rank, int W, float scale,
+                       void* const* pads, int chan_base, unsigned int epoch, unsigned int* counter,
+                       int max_blocks, b2_stream_t stream);
+/* The same reductions done inside the NVSwitch (NVLS): `mc_*` is the multicast address of the
+ * symmetric buffer; multimem.ld_reduce returns the sum over ranks, multimem.st writes to every rank. */
+int b2_nvls_reduce_scatter(void* out_shard, const void* mc_full, size_t shard_elems, int rank, int W,
+                           float scale, void* const* pads, int chan_base, unsigned int epoch,
+                           unsigned int* counter, int max_blocks, b2_stream_t stream);
+int b2_nvls_reduce_scatter_adamw(void* p, void* m, void* v, const void* mc_full, size_t shard_elems,
+                                 int rank, int W, float grad_scale, float lr, float beta1,
+                                 float beta2, float eps, float wd, int step, void* const* pads,
+                                 int chan_base, unsigned int epoch, unsigned int* counter,
+                                 int max_blocks, b2_stream_t stream);
+int b2_nvls_all_reduce(void* mc_buf, size_t elems, int rank, int W, float scale, void* const* pads,
+                       int chan_base, unsigned int epoch, unsigned int* counter, int max_blocks,
+                       b2_stream_t stream);
+
+/* ---- tensor-parallel linears fused with their collective ------------------------------------------
+ * Reference: PrepareModuleInput(Shard(1) -> Replicate()) + ColwiseParallel, and
+ * RowwiseParallel(output_layouts=Shard(1)) (06-tensor-parallel/train_llm.py:89-115), i.e. NCCL
+ * all-gather -> cuBLAS and cuBLAS -> NCCL reduce-scatter as separate steps. */
+int b2_peer_all_gather_chunks(void* dst, void* const* peer_bases, size_t chunk_bytes, int rank, int W,
+                              unsigned int* flags, unsigned int epoch, b2_stream_t stream);
+int b2_gemm_ag(void* C, const void* A, const void* B, int M, int N, int K, int b_mn, int lda, int ldb,
+               int ldc, const unsigned int* flags, unsigned int epoch, int rows_per_rank, int rank,
+               int W, b2_stream_t stream);
+int b2_gemm_rs(void* const* slot_bases, const void* A, const void* B, int M, int N, int K, int b_mn,
+               int lda, int ldb, int ld_slot, int rows_per_rank, int rank, int W, b2_stream_t stream);
+int b2_sum_slots(void* out, const void* slots, size_t n_elems, int W, b2_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -62,6 +62,9 @@ def _declare(lib):
         "b2_peer_reduce_scatter": [P, P, Z, I, I, F, P, I, ctypes.c_uint, P, I, P],
         "b2_peer_reduce_scatter_adamw": [P, P, P, P, Z, I, I, F, F, F, F, F, F, I, P, I, ctypes.c_uint, P, I, P],
         "b2_peer_all_reduce": [P, Z, I, I, F, P, I, ctypes.c_uint, P, I, P],
+        "b2_nvls_reduce_scatter": [P, P, Z, I, I, F, P, I, ctypes.c_uint, P, I, P],
+        "b2_nvls_reduce_scatter_adamw": [P, P, P, P, Z, I, I, F, F, F, F, F, F, I, P, I, ctypes.c_uint, P, I, P],
+        "b2_nvls_all_reduce": [P, Z, I, I, F, P, I, ctypes.c_uint, P, I, P],
     }
     for name, argtypes in sig.items():
         fn = getattr(lib, name, None)

@@ -37,6 +37,8 @@ class _Arena:
         self.hdl = symm.rendezvous(self.buf, group=group if group is not None else dist.group.WORLD)
         self.base = self.buf.data_ptr()
         self.peer_bases = [int(p) for p in self.hdl.buffer_ptrs]
+        # multicast (NVLS) mapping of the same allocation; 0 when the fabric has no multicast support
+        self.mc_base = int(getattr(self.hdl, "multicast_ptr", 0) or 0)
         self.nbytes = nbytes
         self.used = 0
 
@@ -59,6 +61,13 @@ class PeerComm(TorchComm):
         self.arenas: List[_Arena] = []
         # pure copies (parameter all-gather) can ride the DMA engines instead of SM load/store loops
         self.copy_engine = os.environ.get("B200TRAIN_AG", "ce") == "ce"
+        # reductions through the NVSwitch (multimem.ld_reduce on the multicast mapping) when the arena has
+        # one. "auto": from 4 ranks up, where one switch-side load replaces W-1 peer loads per element
+        # (measured: profiles/comm_bench_w2.json, comm_bench_w4.json); at 2 ranks the peer loads are faster
+        mode = os.environ.get("B200TRAIN_NVLS", "auto")
+        self.nvls = mode == "1" or (mode == "auto" and self.world >= 4)
+        # the switch saturates with few blocks in flight; fewer blocks leave more of the SMs to the GEMMs
+        self.nvls_blocks = int(os.environ.get("B200TRAIN_NVLS_BLOCKS", "16"))
         pad = self.empty(64 * 16, torch.int32)   # signal pad: [channel][16 ranks]
         pad.zero_()
         self._pad = pad
@@ -96,6 +105,15 @@ class PeerComm(TorchComm):
             return None
         arr = (ctypes.c_void_p * self.world)(*[b + off for b in a.peer_bases])
         return arr
+
+    def _mc_ptr(self, t: torch.Tensor) -> int:
+        """Multicast address of a symmetric tensor (0: not symmetric, or no NVLS on this machine)."""
+        a, off = self._locate(t)
+        return a.mc_base + off if a is not None and a.mc_base else 0
+
+    @property
+    def has_nvls(self) -> bool:
+        return bool(self.arenas) and all(a.mc_base for a in self.arenas)
 
     def _epoch(self, chan: int) -> int:
         e = self._epochs.get(chan, 0) + 1
@@ -149,31 +167,51 @@ class PeerComm(TorchComm):
             _C.call("b2_peer_all_gather", full.data_ptr(), srcs, n, self.rank, self.world, 1, max_blocks,
                     self._stream())
 
-    def reduce_scatter(self, shard, full, average=True, max_blocks: int = 64):
+    def reduce_scatter(self, shard, full, average=True, max_blocks: int = 0, nvls: Optional[bool] = None):
         fulls = self._peer_array(full) if self.world > 1 else None
         if fulls is None or shard.dtype != torch.bfloat16:
             return super().reduce_scatter(shard, full, average)
+        mc = self._mc_ptr(full) if (self.nvls if nvls is None else nvls) else 0
+        if mc:
+            _C.call("b2_nvls_reduce_scatter", shard.data_ptr(), mc, shard.numel(), self.rank, self.world,
+                    (1.0 / self.world) if average else 1.0, self._pad_ptrs, CHAN_RS, self._epoch(CHAN_RS),
+                    self._counter().data_ptr(), max_blocks or self.nvls_blocks, self._stream())
+            return
         _C.call("b2_peer_reduce_scatter", shard.data_ptr(), fulls, shard.numel(), self.rank, self.world,
                 (1.0 / self.world) if average else 1.0, self._pad_ptrs, CHAN_RS, self._epoch(CHAN_RS),
-                self._counter().data_ptr(), max_blocks, self._stream())
+                self._counter().data_ptr(), max_blocks or 64, self._stream())
 
     def reduce_scatter_adamw(self, p, m, v, full_grad, lr, beta1, beta2, eps, wd, step, average=True,
-                             max_blocks: int = 128) -> bool:
+                             max_blocks: int = 128, nvls: Optional[bool] = None) -> bool:
         """Fused gradient reduce-scatter + AdamW on the owned shard. Returns False when the buffers are not
         eligible (caller then runs the two steps separately)."""
         fulls = self._peer_array(full_grad) if self.world > 1 else None
         if fulls is None or p.dtype != torch.bfloat16:
             return False
+        mc = self._mc_ptr(full_grad) if (self.nvls if nvls is None else nvls) else 0
+        if mc:
+            _C.call("b2_nvls_reduce_scatter_adamw", p.data_ptr(), m.data_ptr(), v.data_ptr(), mc, p.numel(),
+                    self.rank, self.world, (1.0 / self.world) if average else 1.0, lr, beta1, beta2, eps, wd,
+                    step, self._pad_ptrs, CHAN_RS, self._epoch(CHAN_RS), self._counter().data_ptr(), max_blocks,
+                    self._stream())
+            return True
         _C.call("b2_peer_reduce_scatter_adamw", p.data_ptr(), m.data_ptr(), v.data_ptr(), fulls, p.numel(),
                 self.rank, self.world, (1.0 / self.world) if average else 1.0, lr, beta1, beta2, eps, wd, step,
                 self._pad_ptrs, CHAN_RS, self._epoch(CHAN_RS), self._counter().data_ptr(), max_blocks,
                 self._stream())
         return True
 
-    def all_reduce(self, t, average=True, max_blocks: int = 64):
+    def all_reduce(self, t, average=True, max_blocks: int = 64, nvls: Optional[bool] = None):
         bufs = self._peer_array(t) if self.world > 1 else None
         if bufs is None or t.dtype != torch.bfloat16 or t.numel() % (8 * self.world):
             return super().all_reduce(t, average)
+        # the one-pass multimem all-reduce beats the two-phase peer kernel at every W measured
+        mc = self._mc_ptr(t) if ((os.environ.get("B200TRAIN_NVLS", "auto") != "0") if nvls is None else nvls) else 0
+        if mc:
+            _C.call("b2_nvls_all_reduce", mc, t.numel(), self.rank, self.world,
+                    (1.0 / self.world) if average else 1.0, self._pad_ptrs, CHAN_AR, self._epoch(CHAN_AR),
+                    self._counter().data_ptr(), max_blocks, self._stream())
+            return t
         _C.call("b2_peer_all_reduce", bufs, t.numel(), self.rank, self.world,
                 (1.0 / self.world) if average else 1.0, self._pad_ptrs, CHAN_AR, self._epoch(CHAN_AR),
                 self._counter().data_ptr(), max_blocks, self._stream())
