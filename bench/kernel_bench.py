@@ -49,15 +49,17 @@ def bench_gemm(results, quick=False):
         ("qkv_fwd", T, 6144, 4096, "kk"), ("o_fwd", T, 4096, 4096, "kk"),
         ("gateup_fwd", T, 28672, 4096, "kk"), ("down_fwd", T, 4096, 14336, "kk"),
         ("head_fwd", T, 128256, 4096, "kk"),
-        ("qkv_dgrad", T, 4096, 6144, "kmn"), ("gateup_dgrad", T, 4096, 28672, "kmn"),
+        ("qkv_dgrad", T, 4096, 6144, "kmn"), ("o_dgrad", T, 4096, 4096, "kmn"),
+        ("gateup_dgrad", T, 4096, 28672, "kmn"),
         ("down_dgrad", T, 14336, 4096, "kmn"),
-        ("qkv_wgrad", 6144, 4096, T, "mnmn"), ("gateup_wgrad", 28672, 4096, T, "mnmn"),
+        ("qkv_wgrad", 6144, 4096, T, "mnmn"), ("o_wgrad", 4096, 4096, T, "mnmn"),
+        ("gateup_wgrad", 28672, 4096, T, "mnmn"),
         ("down_wgrad", 4096, 14336, T, "mnmn"), ("head_wgrad", 128256, 4096, T, "mnmn"),
     ]
     if quick:
         shapes = shapes[:4]
     configs = [("c1n256", 1 | (256 << 8)), ("c2n256", 2 | (256 << 8)), ("c1n128", 1 | (128 << 8)),
-               ("c2n128", 2 | (128 << 8))]
+               ("c2n128", 2 | (128 << 8)), ("c2n256_whole_tail", 2 | (256 << 8) | (1 << 24))]
     for name, M, N, K, layout in shapes:
         a_mn = layout in ("mnmn",)
         b_mn = layout in ("kmn", "mnmn")
@@ -175,6 +177,8 @@ if __name__ == "__main__":
     fns = (bench_gemm, bench_attention, bench_elementwise)
     if "--no-gemm" in sys.argv:
         fns = fns[1:]
+    if "--only-gemm" in sys.argv:
+        fns = fns[:1]
     for fn in fns:
         try:
             fn(results, quick) if fn is bench_gemm else fn(results)
@@ -182,4 +186,5 @@ if __name__ == "__main__":
             print(f"{fn.__name__} failed: {type(e).__name__}: {e}", flush=True)
             results[fn.__name__ + "_error"] = str(e)
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
-    json.dump(results, open(os.path.join(ROOT, "gpurun_out", "kernel_bench.json"), "w"), indent=1)
+    out = "kernel_bench_gemm.json" if "--only-gemm" in sys.argv else "kernel_bench.json"
+    json.dump(results, open(os.path.join(ROOT, "gpurun_out", out), "w"), indent=1)

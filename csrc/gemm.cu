@@ -84,7 +84,8 @@ template <int kCta, bool kAK, bool kBK, int kEpi, int BN, class Fuse = NoFuse>
 __global__ void __launch_bounds__(256, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmC, int M, int N, int K, EpiArgs epi,
-                 const __grid_constant__ Fuse fuse) {
+                 const __grid_constant__ Fuse fuse, const __grid_constant__ CUtensorMap tmBh,
+                 int split_from) {
   using Cfg = GemmCfg<kCta, BN>;
   constexpr int kFuse = FuseKind<Fuse>::v;
   constexpr int kStages = Cfg::kStages;
@@ -110,6 +111,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     tma_prefetch_desc(&tmC);
+    tma_prefetch_desc(&tmBh);
   }
   if (warp == 1 && elect_one()) {
     for (int s = 0; s < kStages; ++s) {
@@ -136,6 +138,18 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int num_k = (K + BK - 1) / BK;
   const int num_workers = gridDim.x / kCta;
   const int worker = blockIdx.x / kCta;
+  // Tail split: tiles [split_from, num_tiles) -- the partial last wave -- are each cut into two
+  // half-width (BN/2) units so the remainder spreads over twice as many workers (wave quantisation:
+  // 256 tiles on 74 workers cost 4 waves whole, 3.5 split). split_from == num_tiles: no split.
+  const int num_units = split_from + 2 * (num_tiles - split_from);
+  auto unit_tile = [&](int u, int& t, int& n_off, int& bn_cur) {
+    if (u < split_from) {
+      t = u; n_off = 0; bn_cur = BN;
+    } else {
+      const int h = u - split_from;
+      t = split_from + (h >> 1); n_off = (h & 1) * (BN / 2); bn_cur = BN / 2;
+    }
+  };
   constexpr int kGroupM = 8;
   auto tile_coord = [&](int t, int& mb, int& nb) {
     const int per_group = kGroupM * num_n;
@@ -157,11 +171,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = worker; t < num_tiles; t += num_workers) {
-        int mb, nb;
+      for (int u = worker; u < num_units; u += num_workers) {
+        int t, n_off, bn_cur, mb, nb;
+        unit_tile(u, t, n_off, bn_cur);
         tile_coord(t, mb, nb);
         const int m0 = mb * tile_m + (int)cta_rank * BM;
-        const int n0 = nb * BN + (int)cta_rank * (BN / kCta);
+        const int n0 = nb * BN + n_off + (int)cta_rank * (bn_cur / kCta);
+        const CUtensorMap* tb = bn_cur == BN ? &tmB : &tmBh;
+        const uint32_t stage_tx = (uint32_t)(Cfg::kABytes + (bn_cur / kCta) * BK * 2) * kCta;
         if constexpr (kFuse == 1) {
           // rows of this m-block come from rank `owner`: wait until its chunk has landed
           const int owner = min(m0 / fuse.rows_per_rank, fuse.W - 1);
@@ -177,14 +194,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
         for (int kb = 0; kb < num_k; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          if (leader) mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes * kCta);
+          if (leader) mbar_expect_tx(&full_bar[stage], stage_tx);
           const int k0 = kb * BK;
           uint8_t* sa = smem_a + stage * Cfg::kABytes;
           uint8_t* sb = smem_b + stage * Cfg::kBBytes;
           if constexpr (kAK) tma_load_2d<kCta>(&tmA, &full_bar[stage], sa, k0, m0, kEvictNormal);
           else tma_load_3d<kCta>(&tmA, &full_bar[stage], sa, 0, k0, m0 / 64, kEvictNormal);
-          if constexpr (kBK) tma_load_2d<kCta>(&tmB, &full_bar[stage], sb, k0, n0, kEvictNormal);
-          else tma_load_3d<kCta>(&tmB, &full_bar[stage], sb, 0, k0, n0 / 64, kEvictNormal);
+          if constexpr (kBK) tma_load_2d<kCta>(tb, &full_bar[stage], sb, k0, n0, kEvictNormal);
+          else tma_load_3d<kCta>(tb, &full_bar[stage], sb, 0, k0, n0 / 64, kEvictNormal);
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
       }
@@ -192,7 +209,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   } else if (warp == 1) {
     // ================= MMA issuer (pair leader only) =================
     if (leader) {
-      constexpr uint32_t idesc = make_idesc_bf16(BM * kCta, BN, !kAK, !kBK);
+      constexpr uint32_t idesc_full = make_idesc_bf16(BM * kCta, BN, !kAK, !kBK);
+      constexpr uint32_t idesc_half = make_idesc_bf16(BM * kCta, BN / 2, !kAK, !kBK);
       // K-major: rows are 128B apart, 8-row groups 1024B apart (SBO); LBO unused.
       // MN-major: 64-element MN atoms are BK*128 B apart (LBO), 8-row K groups 1024B apart (SBO).
       constexpr uint32_t lbo_a = kAK ? 16 : BK * 128, lbo_b = kBK ? 16 : BK * 128;
@@ -201,7 +219,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int t = worker; t < num_tiles; t += num_workers) {
+      for (int u = worker; u < num_units; u += num_workers) {
+        const uint32_t idesc = u < split_from ? idesc_full : idesc_half;
         if constexpr (kCta == 2) mbar_wait_cluster(&tempty_bar[acc], acc_phase ^ 1);
         else mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
@@ -236,21 +255,23 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     int acc = 0;
     uint32_t acc_phase = 0;
     uint32_t chunk_ctr = 0;
-    for (int t = worker; t < num_tiles; t += num_workers) {
-      int mb, nb;
+    for (int u = worker; u < num_units; u += num_workers) {
+      int t, n_off, bn_cur, mb, nb;
+      unit_tile(u, t, n_off, bn_cur);
       tile_coord(t, mb, nb);
       const int m0 = mb * tile_m + (int)cta_rank * BM;
-      const int n0 = nb * BN;
+      const int n0 = nb * BN + n_off;
+      const int n_chunks = bn_cur / kEpiChunk;
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + acc * BN;
 #pragma unroll 1
-      for (int c = 0; c < BN / kEpiChunk; ++c) {
+      for (int c = 0; c < n_chunks; ++c) {
         uint32_t r0[32], r1[32];
         tmem_ld_32x32b_x32(taddr + c * kEpiChunk, r0);
         tmem_ld_32x32b_x32(taddr + c * kEpiChunk + 32, r1);
         tmem_ld_wait();
-        if (c == BN / kEpiChunk - 1) {
+        if (c == n_chunks - 1) {
           // accumulator fully drained to registers: hand the TMEM stage back to the MMA warp
           tc_fence_before();
           __syncwarp();
@@ -430,10 +451,18 @@ int sm_count() {
   return n;
 }
 
+static bool tail_split_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("B200TRAIN_GEMM_TAIL_SPLIT");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
+
 template <int kCta, bool kAK, bool kBK, int kEpi, int BN, class Fuse = NoFuse>
 static int launch_gemm(void* C, const void* A, const void* B, int M, int N, int K, int lda, int ldb,
                        int ldc, const EpiArgs& epi, int max_ctas, cudaStream_t stream,
-                       const Fuse& fuse = Fuse()) {
+                       const Fuse& fuse = Fuse(), bool allow_split = true) {
   using Cfg = GemmCfg<kCta, BN>;
   CUtensorMap tmA, tmB, tmC;
   int rc;
@@ -465,6 +494,20 @@ static int launch_gemm(void* C, const void* A, const void* B, int M, int N, int 
   if (workers > num_tiles) workers = num_tiles;
   if (workers < 1) workers = 1;
 
+  // tail split (see the kernel): only when the last wave is at most half full, so the halves fit in one
+  // more round; the fused variants order their tiles by chunk arrival and keep whole tiles
+  int split_from = num_tiles;
+  CUtensorMap tmBh = tmB;
+  if (allow_split && tail_split_enabled() && BN == 256 && FuseKind<Fuse>::v == 0 && num_tiles > workers) {
+    const int rem = num_tiles % workers;
+    if (rem > 0 && 2 * rem <= workers) {
+      if constexpr (kBK) rc = make_tmap_2d_bf16(&tmBh, B, N, K, ldb, BN / 2 / kCta, BK);
+      else rc = make_tmap_mn_bf16(&tmBh, B, K, N, ldb, BK, BN / 2 / kCta / 64);
+      if (rc) return rc;
+      split_from = num_tiles - rem;
+    }
+  }
+
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(workers * kCta);
   cfg.blockDim = dim3(256);
@@ -477,16 +520,17 @@ static int launch_gemm(void* C, const void* A, const void* B, int M, int N, int 
   attrs[0].val.clusterDim.z = 1;
   cfg.attrs = attrs;
   cfg.numAttrs = 1;
-  B2_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, M, N, K, epi, fuse));
+  B2_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, M, N, K, epi, fuse, tmBh, split_from));
   return 0;
 }
 
 template <int kCta, int BN>
 static int dispatch_layout(void* C, const void* A, const void* B, int M, int N, int K, int a_mn,
                            int b_mn, int lda, int ldb, int ldc, int epilogue, const EpiArgs& epi,
-                           int max_ctas, cudaStream_t stream) {
+                           int max_ctas, cudaStream_t stream, bool allow_split = true) {
 #define B2_GEMM_CASE(AK, BKM, EPI)                                                                 \
-  return launch_gemm<kCta, AK, BKM, EPI, BN>(C, A, B, M, N, K, lda, ldb, ldc, epi, max_ctas, stream)
+  return launch_gemm<kCta, AK, BKM, EPI, BN>(C, A, B, M, N, K, lda, ldb, ldc, epi, max_ctas, stream, \
+                                             NoFuse(), allow_split)
   if (!a_mn && !b_mn) {
     switch (epilogue) {
       case EPI_NONE: B2_GEMM_CASE(true, true, EPI_NONE);
@@ -652,7 +696,8 @@ int b2_peer_all_gather_chunks(void* dst, void* const* peer_bases, size_t chunk_b
 //   a_mn = 0: A stored [M,K] (lda = row stride); a_mn = 1: A stored [K,M] (rows of length M).
 //   b_mn = 0: B stored [N,K];                    b_mn = 1: B stored [K,N].
 //   epilogue: 0 none, 1 +bias[N], 2 gelu_new(+bias), 3 C += (reads c_old == C, same ldc).
-//   config: 0 auto; otherwise (cta_group) | (BN << 8), e.g. 2 | (256 << 8).
+//   config: 0 auto; otherwise (cta_group) | (BN << 8), e.g. 2 | (256 << 8); bit 24 keeps the last
+//   partial wave in whole tiles (no tail split).
 //   max_ctas: cap on the persistent grid (0 = all SMs) so a concurrent kernel keeps some SMs.
 int b2_gemm_bf16(void* C, const void* A, const void* B, int M, int N, int K, int a_mn, int b_mn,
                  int lda, int ldb, int ldc, int epilogue, const void* bias, int config,
@@ -664,22 +709,23 @@ int b2_gemm_bf16(void* C, const void* A, const void* B, int M, int N, int K, int
   epi.c_old = static_cast<const __nv_bfloat16*>(C);
   epi.ldc = ldc;
   int cta = config & 0xff, bn = (config >> 8) & 0xffff;
+  const bool allow_split = !(config & (1 << 24));
   if (cta == 0) cta = 2;
   if (bn == 0) bn = 256;
   // MN-major operands are fetched in 64-element atoms: each CTA's slice must be atom aligned
   if (cta == 2 && (M <= BM)) cta = 1;
   if (cta == 1 && bn == 256)
     return dispatch_layout<1, 256>(C, A, B, M, N, K, a_mn, b_mn, lda, ldb, ldc, epilogue, epi,
-                                   max_ctas, stream);
+                                   max_ctas, stream, allow_split);
   if (cta == 1 && bn == 128)
     return dispatch_layout<1, 128>(C, A, B, M, N, K, a_mn, b_mn, lda, ldb, ldc, epilogue, epi,
-                                   max_ctas, stream);
+                                   max_ctas, stream, allow_split);
   if (cta == 2 && bn == 256)
     return dispatch_layout<2, 256>(C, A, B, M, N, K, a_mn, b_mn, lda, ldb, ldc, epilogue, epi,
-                                   max_ctas, stream);
+                                   max_ctas, stream, allow_split);
   if (cta == 2 && bn == 128)
     return dispatch_layout<2, 128>(C, A, B, M, N, K, a_mn, b_mn, lda, ldb, ldc, epilogue, epi,
-                                   max_ctas, stream);
+                                   max_ctas, stream, allow_split);
   set_last_error("b2_gemm_bf16: bad config %d", config);
   return -2;
 }

@@ -84,3 +84,29 @@ def test_gemm_mn_major_unaligned_extent():
     acc0 = acc.float().clone()
     gemm(dy, x, a_mn=True, b_mn=True, out=acc, epilogue=3)
     _check(acc, acc0 + dy.float().t() @ x.float(), T)
+
+
+@pytest.mark.parametrize("config", [1 | (256 << 8), 2 | (256 << 8)])
+@pytest.mark.parametrize("shape", [(4096, 4096, 256), (3840, 4160, 320)])
+@pytest.mark.parametrize("layout", ["kk", "kmn", "mnmn"])
+def test_gemm_tail_split(config, shape, layout):
+    """Shapes whose last wave is less than half full (256 or 255 tile pairs on 74 workers, 512 / 510
+    tiles on 148): the remainder runs as half-width units. Same values as the whole-tile schedule."""
+    from b200train.ops import gemm
+
+    M, N, K = shape
+    a_mn = layout == "mnmn"
+    b_mn = layout in ("kmn", "mnmn")
+    A, B = _mk(M, K, 11), _mk(N, K, 12)
+    a = A.t().contiguous() if a_mn else A
+    b = B.t().contiguous() if b_mn else B
+    split = gemm(a, b, a_mn=a_mn, b_mn=b_mn, config=config)
+    whole = gemm(a, b, a_mn=a_mn, b_mn=b_mn, config=config | (1 << 24))
+    torch.cuda.synchronize()
+    _check(split, A.float() @ B.float().t(), K)
+    assert torch.equal(split, whole)
+    # accumulate epilogue through the split tail
+    C = _mk(M, N, 13)
+    C0 = C.float().clone()
+    gemm(a, b, a_mn=a_mn, b_mn=b_mn, out=C, epilogue=3, config=config)
+    _check(C, A.float() @ B.float().t() + C0, K)
