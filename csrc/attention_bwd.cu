@@ -13,8 +13,10 @@
 // the transposed product, so Q, dO, K, P and dS are each stored once.
 //   warp 0     TMA producer (K_j, V_j once; 2-stage ring of Q_i / dO_i)
 //   warp 1     MMA issuer
-//   warps 2-5  softmax warpgroup (one thread per query row)
+//   warps 2-5  softmax warpgroup A (one thread per query row, kv columns 0..31)
 //   warps 6-9  dQ warpgroup (TMEM -> swizzled smem -> TMA reduce-add into dq_accum), drains dK^T at the end
+//   warps 10-13 softmax warpgroup B (kv columns 32..63): the exp2 / dS arithmetic is the longest stage
+//              of the per-step chain, two warps per scheduler halve it
 //
 // Replaces flash_attn_2_cuda's backward (reference: 05-training-llama-405b/train_llm.py:87 +
 // loss.backward() at :237).
@@ -25,7 +27,7 @@ namespace b2 {
 
 constexpr int QB = 128;  // query rows per step
 constexpr int KB = 64;   // kv rows per CTA
-constexpr int kBwdThreads = 320;
+constexpr int kBwdThreads = 448;
 
 template <int D>
 struct AttnBwdSmem {
@@ -160,8 +162,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       mbar_init(&qdo_full[i], 1);
       mbar_init(&qdo_empty[i], 1);
       mbar_init(&sdp_full[i], 1);
-      mbar_init(&sdp_free[i], 4);
-      mbar_init(&pds_full[i], 4);
+      mbar_init(&sdp_free[i], 8);   // 4 warps of each softmax warpgroup
+      mbar_init(&pds_full[i], 8);
       mbar_init(&pds_empty[i], 1);
     }
     mbar_init(dq_full, 1);
@@ -274,8 +276,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
       __syncwarp();
     }
-  } else if (warp < 6) {
-    // ================= softmax warpgroup =================
+  } else if (warp < 6 || warp >= 10) {
+    // ================= softmax warpgroups (A: columns 0..31, B: columns 32..63) =================
+    const int hf = warp >= 10 ? 1 : 0;
     const int quarter = warp & 3;
     const int row = quarter * 32 + (int)lane_id();
     const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
@@ -295,13 +298,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       const int lim = valid_row ? (p.causal ? min(q_idx, doc_len - 1) : doc_len - 1) : -1;
       const uint32_t prow = smem_u32(sP) + row * 128;
       const uint32_t drow = smem_u32(sDS) + row * 128;
-#pragma unroll
-      for (int hf = 0; hf < KB / 32; ++hf) {
+      {
         uint32_t sr[32], dr[32];
         tmem_ld_32x32b_x32(tm_S[s] + lane_off + hf * 32, sr);
         tmem_ld_32x32b_x32(tm_dP[s] + lane_off + hf * 32, dr);
         tmem_ld_wait();
-        if (hf == KB / 32 - 1) {  // both halves are in registers: the S / dP buffers may be refilled
+        {  // this warp's share is in registers: the S / dP buffers may be refilled once all 8 arrive
           tc_fence_before();
           __syncwarp();
           if (lane_id() == 0) mbar_arrive(&sdp_free[s]);
@@ -321,7 +323,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           pp[i] = pack_bf16(pv[0], pv[1]);
           dd[i] = pack_bf16(dv[0], dv[1]);
         }
-        if (hf == 0) mbar_wait(&pds_empty[0], (it & 1) ^ 1);  // previous step's MMAs finished reading P / dS
+        mbar_wait(&pds_empty[0], (it & 1) ^ 1);  // previous step's MMAs finished reading P / dS
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           const uint32_t off = ((hf * 4 + c) ^ (row & 7)) << 4;
@@ -342,8 +344,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       mbar_wait(done_bar, 0);
       tc_fence_after();
       const int d = row;
-#pragma unroll
-      for (int c = 0; c < KB / 32; ++c) {
+      {
+        const int c = hf;  // each warpgroup drains its own 32 kv columns
         uint32_t r[32];
         tmem_ld_32x32b_x32(tm_dVt + lane_off + c * 32, r);
         tmem_ld_wait();
