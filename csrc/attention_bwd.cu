@@ -78,7 +78,7 @@ __global__ void attn_bwd_delta_kernel(float* __restrict__ delta, const __nv_bflo
 // dq[t, :] = bf16(dq_accum[t, :])
 __global__ void attn_bwd_convert_dq_kernel(__nv_bfloat16* __restrict__ dq,
                                            const float* __restrict__ acc, int T, int cols,
-                                           int dq_stride) {
+                                           int dq_stride, float scale) {
   const int nvec = cols >> 2;
   const size_t total = (size_t)T * nvec;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
@@ -87,8 +87,8 @@ __global__ void attn_bwd_convert_dq_kernel(__nv_bfloat16* __restrict__ dq,
     const int c = (int)(i - t * nvec);
     const float4 v = reinterpret_cast<const float4*>(acc + t * cols)[c];
     uint2 o;
-    o.x = pack_bf16(v.x, v.y);
-    o.y = pack_bf16(v.z, v.w);
+    o.x = pack_bf16(v.x * scale, v.y * scale);
+    o.y = pack_bf16(v.z * scale, v.w * scale);
     *reinterpret_cast<uint2*>(dq + t * (size_t)dq_stride + c * 4) = o;
   }
 }
@@ -316,7 +316,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           for (int e = 0; e < 2; ++e) {
             const int c = 2 * i + e;
             const bool on = (kv0 + hf * 32 + c) <= lim;
-            const float pe = on ? exp2f(__uint_as_float(sr[c]) * p.scale_log2 - lse2) : 0.f;
+            const float pe = on ? fast_exp2(__uint_as_float(sr[c]) * p.scale_log2 - lse2) : 0.f;
             pv[e] = pe;
             dv[e] = pe * (__uint_as_float(dr[c]) - delta) * p.scale;
           }
@@ -438,6 +438,427 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   }
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// Second-generation backward (head_dim 128): transposed scores with P^T / dS^T kept in tensor memory.
+//
+// One CTA per (document, kv head, 128-row kv block j); a step is one (query head, 64-row query block i).
+//     S^T  = K_j  Q_i^T            [128 kv x 64 q]   TMEM, double buffered
+//     dP^T = V_j  dO_i^T           [128 kv x 64 q]   TMEM, double buffered
+//     P^T  = exp2(S^T c - lse_q),  dS^T = P^T (dP^T - delta_q) scale     (lane = kv row)
+//     dV  += P^T  dO_i             A operand read from TMEM (P^T written back over S^T as bf16)
+//     dK  += dS^T Q_i              A operand read from TMEM (dS^T next to P^T)
+//     dQ^T = K_j^T dS              [128 d x 64 q] into the columns dP^T occupied; dS^T also goes to smem
+// Against the first kernel (S = Q K^T, 64-row kv block, P and dS through shared memory) a unit of work
+// moves ~1.5x fewer shared-memory bytes: no P tile, half the dQ staging (one reduce per 128 kv rows
+// instead of per 64), half the Q / dO re-loads, and two of the five MMAs read A from TMEM. That
+// kernel was bound by shared-memory bandwidth (ncu: tensor pipe 30 % active).
+//   warp 0       TMA producer        warp 1        MMA issuer
+//   warps 2-5    softmax warpgroup A (q columns 0..31)     warps 10-13  softmax warpgroup B (32..63)
+//   warps 6-9    dQ^T drain: warp w owns head-dim lanes 32w..32w+31 = one [64 q x 32 d] fp32 box per
+//                step, staged in its private buffer and added into dq_accum by its own TMA reduce
+constexpr int QB2 = 64;    // query rows per step
+constexpr int KB2 = 128;   // kv rows per CTA
+struct AttnBwd2Smem {
+  static constexpr int D = 128;
+  static constexpr int kK = KB2 * D * 2;        // 32 KB
+  static constexpr int kV = KB2 * D * 2;        // 32 KB
+  static constexpr int kQ = QB2 * D * 2;        // 16 KB per stage
+  static constexpr int kDO = QB2 * D * 2;       // 16 KB per stage
+  static constexpr int kDS = KB2 * QB2 * 2;     // 16 KB per stage
+  static constexpr int kDQBox = QB2 * 32 * 4;   // 8 KB: one warp's [64 q x 32 d] fp32 box
+  static constexpr int kStats = 2 * 2 * 64 * 4; // [warpgroup][stage][lse2 x32 | delta x32] fp32 = 1 KB
+  static constexpr int kTotal = kK + kV + 2 * (kQ + kDO + kDS) + 4 * 2 * kDQBox + kStats + 256 + 1024;
+};
+
+__global__ void __launch_bounds__(kBwdThreads, 1)
+attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
+                 const __grid_constant__ CUtensorMap tmDQ, AttnBwdParams p) {
+  using SM = AttnBwd2Smem;
+  constexpr int D = 128;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint8_t* sK = smem;
+  uint8_t* sV = sK + SM::kK;
+  uint8_t* sQ = sV + SM::kV;             // 2 stages
+  uint8_t* sDO = sQ + 2 * SM::kQ;        // 2 stages
+  uint8_t* sDS = sDO + 2 * SM::kDO;      // 2 stages
+  uint8_t* sDQ = sDS + 2 * SM::kDS;      // [4 warps][2] boxes
+  float* sStats = reinterpret_cast<float*>(sDQ + 8 * SM::kDQBox);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sDQ + 8 * SM::kDQBox + SM::kStats);
+  uint64_t* kv_full = bars;            // 1
+  uint64_t* qdo_full = bars + 1;       // 2
+  uint64_t* qdo_empty = bars + 3;      // 2
+  uint64_t* s_full = bars + 5;         // 2  S^T of a step is in TMEM
+  uint64_t* p_full = bars + 7;         // 2  P^T written back (8 warps)
+  uint64_t* ds_full = bars + 9;        // 2  dS^T in TMEM and smem (8 warps)
+  uint64_t* dq_full = bars + 11;       // 2  dQ^T of a step is in TMEM
+  uint64_t* dq_free = bars + 13;       // 2  ... and has been read out (4 warps)
+  uint64_t* done_bar = bars + 15;      // 1
+  uint64_t* dp_full = bars + 16;       // 2  dP^T of a step is in TMEM
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
+
+  const int warp = threadIdx.x >> 5;
+  const int per_kb = p.Hkv * p.ndocs;
+  const int jb = (int)blockIdx.x / per_kb;
+  const int kvh = ((int)blockIdx.x % per_kb) % p.Hkv;
+  const int doc = ((int)blockIdx.x % per_kb) / p.Hkv;
+  const int doc_start = p.cu_seqlens[doc];
+  const int doc_len = p.cu_seqlens[doc + 1] - doc_start;
+  const int num_kb = (doc_len + KB2 - 1) / KB2;
+  if (jb >= num_kb) return;
+  const int kv0 = jb * KB2;
+  const int num_qb = (doc_len + QB2 - 1) / QB2;
+  const int i0 = p.causal ? kv0 / QB2 : 0;  // first query block with a row >= kv0
+  const int nqi = num_qb - i0;
+  const int group = p.Hq / p.Hkv;
+  const int n_iter = group * nqi;
+
+  if (warp == 0 && elect_one()) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmK);
+    tma_prefetch_desc(&tmV);
+    tma_prefetch_desc(&tmDO);
+    tma_prefetch_desc(&tmDQ);
+    mbar_init(kv_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&qdo_full[i], 1);
+      mbar_init(&qdo_empty[i], 1);
+      mbar_init(&s_full[i], 1);
+      mbar_init(&dp_full[i], 1);
+      mbar_init(&p_full[i], 8);
+      mbar_init(&ds_full[i], 8);
+      mbar_init(&dq_full[i], 1);
+      mbar_init(&dq_free[i], 4);
+    }
+    mbar_init(done_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<1>(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  // columns: [0,128) S^T x2 (64 each; later P^T at +0/+32 and dS^T at +16/+48, bf16 pairs),
+  //          [128,256) dP^T x2 (64 each; later dQ^T), [256,384) dV, [384,512) dK
+  const uint32_t tm_S[2] = {tmem_base, tmem_base + 64};
+  const uint32_t tm_dP[2] = {tmem_base + 128, tmem_base + 192};
+  const uint32_t tm_dV = tmem_base + 256;
+  const uint32_t tm_dK = tmem_base + 384;
+
+  if (warp == 0) {
+    // ================= TMA producer =================
+    if (elect_one()) {
+      mbar_expect_tx(kv_full, SM::kK + SM::kV);
+#pragma unroll
+      for (int a = 0; a < 2; ++a) {
+        tma_load_2d<1>(&tmK, kv_full, sK + a * (KB2 * 128), kvh * D + a * 64, doc_start + kv0, kEvictFirst);
+        tma_load_2d<1>(&tmV, kv_full, sV + a * (KB2 * 128), kvh * D + a * 64, doc_start + kv0, kEvictFirst);
+      }
+      for (int it = 0; it < n_iter; ++it) {
+        const int s = it & 1;
+        const int head = kvh * group + it / nqi;
+        const int row = doc_start + (i0 + it % nqi) * QB2;
+        mbar_wait(&qdo_empty[s], ((it >> 1) & 1) ^ 1);
+        mbar_expect_tx(&qdo_full[s], SM::kQ + SM::kDO);
+#pragma unroll
+        for (int a = 0; a < 2; ++a) {
+          tma_load_2d<1>(&tmQ, &qdo_full[s], sQ + s * SM::kQ + a * (QB2 * 128), head * D + a * 64, row, kEvictLast);
+          tma_load_2d<1>(&tmDO, &qdo_full[s], sDO + s * SM::kDO + a * (QB2 * 128), head * D + a * 64, row, kEvictLast);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    constexpr uint32_t idesc_st = make_idesc_bf16(KB2, QB2, false, false);  // S^T, dP^T: K-major x K-major
+    constexpr uint32_t idesc_dv = make_idesc_bf16(KB2, D, false, true);     // dV, dK: TMEM A x MN-major B
+    constexpr uint32_t idesc_dq = make_idesc_bf16(D, QB2, true, true);      // dQ^T: MN-major x MN-major
+    // S^T of the next step goes out as early as possible (its columns are free once the previous
+    // user's dV / dK were issued); dP^T waits for the dQ^T that lived in its columns to be drained
+    auto issue_s = [&](int it) {
+      const int s = it & 1;
+      mbar_wait(&qdo_full[s], (it >> 1) & 1);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t qa = smem_u32(sQ + s * SM::kQ), ka = smem_u32(sK);
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk) {
+          const uint32_t offa = (kk >> 2) * (KB2 * 128) + (kk & 3) * 32;
+          const uint32_t offb = (kk >> 2) * (QB2 * 128) + (kk & 3) * 32;
+          umma_f16<1>(tm_S[s], make_smem_desc_sw128(ka + offa, 16, 1024),
+                      make_smem_desc_sw128(qa + offb, 16, 1024), idesc_st, kk != 0);
+        }
+        umma_commit<1>(&s_full[s]);
+      }
+      __syncwarp();
+    };
+    auto issue_dp = [&](int it) {
+      const int s = it & 1;
+      mbar_wait(&dq_free[s], ((it >> 1) & 1) ^ 1);  // dQ^T of step it-2 has left the dP^T columns
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t da = smem_u32(sDO + s * SM::kDO), va = smem_u32(sV);
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk) {
+          const uint32_t offa = (kk >> 2) * (KB2 * 128) + (kk & 3) * 32;
+          const uint32_t offb = (kk >> 2) * (QB2 * 128) + (kk & 3) * 32;
+          umma_f16<1>(tm_dP[s], make_smem_desc_sw128(va + offa, 16, 1024),
+                      make_smem_desc_sw128(da + offb, 16, 1024), idesc_st, kk != 0);
+        }
+        umma_commit<1>(&dp_full[s]);
+      }
+      __syncwarp();
+    };
+    mbar_wait(kv_full, 0);
+    if (n_iter > 0) {
+      issue_s(0);
+      issue_dp(0);
+    }
+    for (int it = 0; it < n_iter; ++it) {
+      if (it + 1 < n_iter) issue_s(it + 1);
+      const int s = it & 1;
+      const uint32_t par = (it >> 1) & 1;
+      const uint32_t qa = smem_u32(sQ + s * SM::kQ), da = smem_u32(sDO + s * SM::kDO);
+      mbar_wait(&p_full[s], par);
+      tc_fence_after();
+      if (elect_one()) {
+        // dV[kv, d] += P^T[kv, q] dO[q, d]: K = 64 query rows, 16 per instruction = 8 TMEM columns
+#pragma unroll
+        for (int kk = 0; kk < QB2 / 16; ++kk)
+          umma_f16_ts(tm_dV, tm_S[s] + (kk >> 1) * 32 + (kk & 1) * 8,
+                      make_smem_desc_sw128(da + kk * 2048, QB2 * 128, 1024), idesc_dv, (it | kk) != 0);
+      }
+      __syncwarp();
+      if (it + 1 < n_iter) issue_dp(it + 1);
+      mbar_wait(&ds_full[s], par);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t ka = smem_u32(sK), dsa = smem_u32(sDS + s * SM::kDS);
+#pragma unroll
+        for (int kk = 0; kk < QB2 / 16; ++kk)
+          umma_f16_ts(tm_dK, tm_S[s] + 16 + (kk >> 1) * 32 + (kk & 1) * 8,
+                      make_smem_desc_sw128(qa + kk * 2048, QB2 * 128, 1024), idesc_dv, (it | kk) != 0);
+        // dQ^T[d, q] = K^T[d, kv] dS[kv, q]: reduction over the 128 kv rows
+#pragma unroll
+        for (int kk = 0; kk < KB2 / 16; ++kk)
+          umma_f16<1>(tm_dP[s], make_smem_desc_sw128(ka + kk * 2048, KB2 * 128, 1024),
+                      make_smem_desc_sw128(dsa + kk * 2048, KB2 * 128, 1024), idesc_dq, kk != 0);
+        umma_commit<1>(&qdo_empty[s]);
+        umma_commit<1>(&dq_full[s]);
+        if (it == n_iter - 1) umma_commit<1>(done_bar);
+      }
+      __syncwarp();
+    }
+  } else if (warp < 6 || warp >= 10) {
+    // ================= softmax warpgroups: lane = kv row, h selects 32 of the 64 q columns =========
+    const int h = warp >= 10 ? 1 : 0;
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + (int)lane_id();   // kv row inside the block
+    const int kv_idx = kv0 + row;
+    const bool kv_ok = kv_idx < doc_len;
+    const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
+    for (int it = 0; it < n_iter; ++it) {
+      const int s = it & 1;
+      const uint32_t par = (it >> 1) & 1;
+      const int head = kvh * group + it / nqi;
+      const int q0 = (i0 + it % nqi) * QB2 + 32 * h;   // first query row of this warpgroup's columns
+      // lane j fetches the row statistics of query q0 + j; after the wait below they go to a small
+      // shared table (one per warpgroup and stage; the four warps store identical values, and a warp
+      // only reads after its own stores) that every lane reads back with broadcast 16-byte loads
+      float lse2_l = 0.f, delta_l = 0.f;
+      if (q0 + (int)lane_id() < doc_len) {
+        const size_t idx = (size_t)head * p.T + doc_start + q0 + lane_id();
+        lse2_l = p.lse[idx] * 1.4426950408889634f;
+        delta_l = p.delta[idx];
+      }
+      const int n_q = min(32, doc_len - q0);           // valid columns
+      // column c is visible iff q0 + c >= kv_idx (causal) and c < n_q
+      const int c_lo = p.causal ? max(kv_idx - q0, 0) : 0;
+      const bool all_on = __all_sync(0xffffffffu, kv_ok && c_lo == 0 && n_q >= 32);
+      mbar_wait(&s_full[s], par);
+      tc_fence_after();
+      // past this wait every warp has finished step it-2, the previous user of this table
+      float* st = sStats + (h * 2 + s) * 64;
+      st[lane_id()] = lse2_l;
+      st[32 + lane_id()] = delta_l;
+      __syncwarp();
+      uint32_t sr[32];
+      float pf[32];
+      tmem_ld_32x32b_x32(tm_S[s] + lane_off + 32 * h, sr);
+      tmem_ld_wait();
+      uint32_t pk[16];
+      if (all_on) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float4 l4 = reinterpret_cast<const float4*>(st)[i];
+          pf[4 * i] = fast_exp2(fmaf(__uint_as_float(sr[4 * i]), p.scale_log2, -l4.x));
+          pf[4 * i + 1] = fast_exp2(fmaf(__uint_as_float(sr[4 * i + 1]), p.scale_log2, -l4.y));
+          pf[4 * i + 2] = fast_exp2(fmaf(__uint_as_float(sr[4 * i + 2]), p.scale_log2, -l4.z));
+          pf[4 * i + 3] = fast_exp2(fmaf(__uint_as_float(sr[4 * i + 3]), p.scale_log2, -l4.w));
+        }
+      } else {
+#pragma unroll
+        for (int c = 0; c < 32; ++c) {
+          const bool on = kv_ok && c >= c_lo && c < n_q;
+          pf[c] = on ? fast_exp2(fmaf(__uint_as_float(sr[c]), p.scale_log2, -st[c])) : 0.f;
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 16; ++i) pk[i] = pack_bf16(pf[2 * i], pf[2 * i + 1]);
+      tmem_st_32x32b_x16(tm_S[s] + lane_off + 32 * h, pk);       // P^T over this warpgroup's S^T columns
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane_id() == 0) mbar_arrive(&p_full[s]);
+      // ---- dS^T = P^T (dP^T - delta); the softmax scale is applied by the dK drain and the dQ convert ----
+      mbar_wait(&dp_full[s], par);
+      tc_fence_after();
+      tmem_ld_32x32b_x32(tm_dP[s] + lane_off + 32 * h, sr);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float4 d4 = reinterpret_cast<const float4*>(st + 32)[i];
+        const float a0 = pf[4 * i] * (__uint_as_float(sr[4 * i]) - d4.x);
+        const float a1 = pf[4 * i + 1] * (__uint_as_float(sr[4 * i + 1]) - d4.y);
+        const float a2 = pf[4 * i + 2] * (__uint_as_float(sr[4 * i + 2]) - d4.z);
+        const float a3 = pf[4 * i + 3] * (__uint_as_float(sr[4 * i + 3]) - d4.w);
+        pk[2 * i] = pack_bf16(a0, a1);
+        pk[2 * i + 1] = pack_bf16(a2, a3);
+      }
+      tmem_st_32x32b_x16(tm_S[s] + lane_off + 32 * h + 16, pk);  // dS^T next to P^T
+      // the same values as a [kv rows][64 q] swizzled tile: B operand of dQ^T
+      const uint32_t drow = smem_u32(sDS + s * SM::kDS) + row * 128;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const uint32_t off = ((h * 4 + c) ^ (row & 7)) << 4;
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(drow + off), "r"(pk[4 * c]),
+                     "r"(pk[4 * c + 1]), "r"(pk[4 * c + 2]), "r"(pk[4 * c + 3])
+                     : "memory");
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane_id() == 0) mbar_arrive(&ds_full[s]);
+    }
+    // ---- drain dV: lane = kv row, this warpgroup takes head-dim columns [64h, 64h + 64) ----
+    if (n_iter > 0) {
+      mbar_wait(done_bar, 0);
+      tc_fence_after();
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(tm_dV + lane_off + h * 64 + c * 32, r);
+        tmem_ld_wait();
+        if (kv_ok) {
+          uint4* dst = reinterpret_cast<uint4*>(p.dv + (size_t)(doc_start + kv_idx) * p.dv_stride +
+                                                (size_t)kvh * D + h * 64 + c * 32);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint4 o;
+            o.x = pack_bf16(__uint_as_float(r[8 * j]), __uint_as_float(r[8 * j + 1]));
+            o.y = pack_bf16(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
+            o.z = pack_bf16(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
+            o.w = pack_bf16(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
+            dst[j] = o;
+          }
+        }
+      }
+      tc_fence_before();
+    }
+  } else {
+    // ================= dQ^T drain: warp w owns head-dim lanes 32w .. 32w+31 =================
+    const int w = warp & 3;   // warps 6..9 -> TMEM lane quarters 2,3,0,1
+    const uint32_t lane_off = (uint32_t)(w * 32) << 16;
+    uint8_t* my_box = sDQ + w * 2 * SM::kDQBox;
+    const uint32_t chunk = lane_id() >> 2, sub = (lane_id() & 3) * 4;
+    for (int it = 0; it < n_iter; ++it) {
+      const int s = it & 1;
+      const int head = kvh * group + it / nqi;
+      const int q_row0 = doc_start + (i0 + it % nqi) * QB2;
+      mbar_wait(&dq_full[s], (it >> 1) & 1);
+      tc_fence_after();
+      uint32_t r0[32], r1[32];
+      tmem_ld_32x32b_x32(tm_dP[s] + lane_off, r0);
+      tmem_ld_32x32b_x32(tm_dP[s] + lane_off + 32, r1);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane_id() == 0) {
+        mbar_arrive(&dq_free[s]);
+        tma_store_wait_read<1>();   // the reduce issued two steps ago has finished reading this box
+      }
+      __syncwarp();
+      // box [64 q rows][32 d] fp32, 128 B rows, 128B swizzle; lane = d: one row per store instruction
+      const uint32_t box = smem_u32(my_box + (it & 1) * SM::kDQBox);
+#pragma unroll
+      for (int q = 0; q < 32; ++q) {
+        asm volatile("st.shared.b32 [%0], %1;" ::"r"(box + q * 128 + ((chunk ^ (q & 7)) << 4) + sub), "r"(r0[q]) : "memory");
+        asm volatile("st.shared.b32 [%0], %1;" ::"r"(box + (q + 32) * 128 + ((chunk ^ (q & 7)) << 4) + sub), "r"(r1[q]) : "memory");
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane_id() == 0) {
+        tma_reduce_add_2d(&tmDQ, my_box + (it & 1) * SM::kDQBox, head * D + w * 32, q_row0);
+        tma_store_commit();
+      }
+    }
+    if (lane_id() == 0) tma_store_wait<0>();
+    // ---- drain dK: lane = kv row ----
+    if (n_iter > 0) {
+      const int kv_idx = kv0 + w * 32 + (int)lane_id();
+      mbar_wait(done_bar, 0);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(tm_dK + lane_off + c * 32, r);
+        tmem_ld_wait();
+        if (kv_idx < doc_len) {
+          uint4* dst = reinterpret_cast<uint4*>(p.dk + (size_t)(doc_start + kv_idx) * p.dk_stride +
+                                                (size_t)kvh * D + c * 32);
+          const float sc = p.scale;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint4 o;
+            o.x = pack_bf16(__uint_as_float(r[8 * j]) * sc, __uint_as_float(r[8 * j + 1]) * sc);
+            o.y = pack_bf16(__uint_as_float(r[8 * j + 2]) * sc, __uint_as_float(r[8 * j + 3]) * sc);
+            o.z = pack_bf16(__uint_as_float(r[8 * j + 4]) * sc, __uint_as_float(r[8 * j + 5]) * sc);
+            o.w = pack_bf16(__uint_as_float(r[8 * j + 6]) * sc, __uint_as_float(r[8 * j + 7]) * sc);
+            dst[j] = o;
+          }
+        }
+      }
+      tc_fence_before();
+    }
+  }
+
+  __syncwarp();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<1>(tmem_base, 512);
+  }
+}
+
+static int launch_attn_bwd2(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
+                            const CUtensorMap& tmDO, const CUtensorMap& tmDQ, const AttnBwdParams& prm,
+                            int max_kblocks, int ndocs, cudaStream_t stream) {
+  using SM = AttnBwd2Smem;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B2_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       SM::kTotal));
+    attr_set = true;
+  }
+  dim3 grid(max_kblocks * prm.Hkv * ndocs);
+  attn_bwd2_kernel<<<grid, kBwdThreads, SM::kTotal, stream>>>(tmQ, tmK, tmV, tmDO, tmDQ, prm);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
 template <int D>
 static int launch_attn_bwd(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
                            const CUtensorMap& tmDO, const CUtensorMap& tmDQ,
@@ -485,13 +906,22 @@ int b2_attn_bwd(void* dq, void* dk, void* dv, float* dq_accum, float* delta, con
         D, do_stride, o_stride);
     B2_CUDA_CHECK(cudaGetLastError());
   }
+  // head_dim 128 runs the second-generation kernel (B200TRAIN_ATTN_BWD=1 selects the first one; the
+  // dk / dv rows are written with 16-byte stores there, so their strides must allow it)
+  static const bool want_v2 = [] {
+    const char* e = getenv("B200TRAIN_ATTN_BWD");
+    return !(e && e[0] == '1');
+  }();
+  const bool v2 = want_v2 && D == 128 && dk_stride % 8 == 0 && dv_stride % 8 == 0 &&
+                  (reinterpret_cast<uintptr_t>(dk) & 15) == 0 && (reinterpret_cast<uintptr_t>(dv) & 15) == 0;
+  const int qb = v2 ? QB2 : QB, kb = v2 ? KB2 : KB;
   CUtensorMap tmQ, tmK, tmV, tmDO, tmDQ;
   int rc;
-  if ((rc = make_tmap_2d_f32(&tmDQ, dq_accum, T, (uint64_t)Hq * D, (uint64_t)Hq * D, QB, 32))) return rc;
-  if ((rc = make_tmap_2d_bf16(&tmQ, q, T, (uint64_t)Hq * D, q_stride, QB, 64))) return rc;
-  if ((rc = make_tmap_2d_bf16(&tmDO, dout, T, (uint64_t)Hq * D, do_stride, QB, 64))) return rc;
-  if ((rc = make_tmap_2d_bf16(&tmK, k, T, (uint64_t)Hkv * D, k_stride, KB, 64))) return rc;
-  if ((rc = make_tmap_2d_bf16(&tmV, v, T, (uint64_t)Hkv * D, v_stride, KB, 64))) return rc;
+  if ((rc = make_tmap_2d_f32(&tmDQ, dq_accum, T, (uint64_t)Hq * D, (uint64_t)Hq * D, qb, 32))) return rc;
+  if ((rc = make_tmap_2d_bf16(&tmQ, q, T, (uint64_t)Hq * D, q_stride, qb, 64))) return rc;
+  if ((rc = make_tmap_2d_bf16(&tmDO, dout, T, (uint64_t)Hq * D, do_stride, qb, 64))) return rc;
+  if ((rc = make_tmap_2d_bf16(&tmK, k, T, (uint64_t)Hkv * D, k_stride, kb, 64))) return rc;
+  if ((rc = make_tmap_2d_bf16(&tmV, v, T, (uint64_t)Hkv * D, v_stride, kb, 64))) return rc;
   AttnBwdParams prm;
   prm.dq_accum = dq_accum;
   prm.dk = static_cast<__nv_bfloat16*>(dk);
@@ -508,8 +938,9 @@ int b2_attn_bwd(void* dq, void* dk, void* dv, float* dq_accum, float* delta, con
   prm.scale = softmax_scale;
   prm.scale_log2 = softmax_scale * 1.4426950408889634f;
   prm.causal = causal;
-  const int max_kb = (max_seqlen + KB - 1) / KB;
-  if (D == 64) rc = launch_attn_bwd<64>(tmQ, tmK, tmV, tmDO, tmDQ, prm, max_kb, ndocs, stream);
+  const int max_kb = (max_seqlen + kb - 1) / kb;
+  if (v2) rc = launch_attn_bwd2(tmQ, tmK, tmV, tmDO, tmDQ, prm, max_kb, ndocs, stream);
+  else if (D == 64) rc = launch_attn_bwd<64>(tmQ, tmK, tmV, tmDO, tmDQ, prm, max_kb, ndocs, stream);
   else rc = launch_attn_bwd<128>(tmQ, tmK, tmV, tmDO, tmDQ, prm, max_kb, ndocs, stream);
   if (rc) return rc;
   {
@@ -518,8 +949,10 @@ int b2_attn_bwd(void* dq, void* dk, void* dv, float* dq_accum, float* delta, con
     int blocks = (int)((work + 255) / 256);
     const int cap = sm_count() * 16;
     if (blocks > cap) blocks = cap;
+    // the second-generation kernel leaves the softmax scale out of dS: it is applied here and in its
+    // dK drain
     attn_bwd_convert_dq_kernel<<<blocks, 256, 0, stream>>>(static_cast<__nv_bfloat16*>(dq), dq_accum,
-                                                           T, cols, dq_stride);
+                                                           T, cols, dq_stride, v2 ? softmax_scale : 1.f);
     B2_CUDA_CHECK(cudaGetLastError());
   }
   return 0;

@@ -226,7 +226,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       float alpha = 1.f;
       const bool need = mx > m_used + 8.f;
       if (need) {
-        alpha = (m_used == -INFINITY) ? 0.f : exp2f(m_used - mx);
+        alpha = (m_used == -INFINITY) ? 0.f : fast_exp2(m_used - mx);
         l *= alpha;
         m_used = mx;
       }
@@ -255,8 +255,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 #pragma unroll
         for (int e = 0; e < 16; ++e) {
           const int i = c * 32 + e * 2;
-          const float p0 = exp2f(fmaf(sv[i], p.scale_log2, -base));
-          const float p1 = exp2f(fmaf(sv[i + 1], p.scale_log2, -base));
+          const float p0 = fast_exp2(fmaf(sv[i], p.scale_log2, -base));
+          const float p1 = fast_exp2(fmaf(sv[i + 1], p.scale_log2, -base));
           psum += p0 + p1;
           pk[e] = pack_bf16(p0, p1);
         }
@@ -283,8 +283,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     float m_all, f_mine, l_all;
     if (wg == 0) {
       m_all = fmaxf(m_used, m1);
-      const float f0 = (m_used == -INFINITY) ? 0.f : exp2f(m_used - m_all);
-      const float f1 = (m1 == -INFINITY) ? 0.f : exp2f(m1 - m_all);
+      const float f0 = (m_used == -INFINITY) ? 0.f : fast_exp2(m_used - m_all);
+      const float f1 = (m1 == -INFINITY) ? 0.f : fast_exp2(m1 - m_all);
       l_all = f0 * l + f1 * l1;
       f_mine = f0;
     } else {
@@ -311,7 +311,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     }
     named_bar_sync(3, 256);
     if (wg == 0) {
-      const float f1 = (m1 == -INFINITY) ? 0.f : exp2f(m1 - m_all);
+      const float f1 = (m1 == -INFINITY) ? 0.f : fast_exp2(m1 - m_all);
       const float inv_l = l_all > 0.f ? 1.f / l_all : 0.f;
       const float a0 = f_mine * inv_l, a1 = f1 * inv_l;
       __nv_bfloat16* orow = p.o + (size_t)(doc_start + q_idx) * p.o_stride + (size_t)head * D;
