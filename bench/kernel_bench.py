@@ -146,9 +146,31 @@ def bench_elementwise(results):
     w = rnd(H)
     ms = timeit(lambda i: ops.rmsnorm(xs[i], w, 1e-5, rs[i]), n_rot)
     results["elementwise"]["rmsnorm_res_fwd"] = {"ms": ms, "gbs": 4 * T * H * 2 / ms / 1e6}
+    # raw C-ABI calls for the backward kernels (no autograd around them)
+    from b200train import _C
+
+    st = torch.cuda.current_stream().cuda_stream
+    rstd = torch.rand(T, device="cuda") + 0.5
+    dx = torch.empty(T, H, device="cuda", dtype=torch.bfloat16)
+    dw = torch.empty(H, device="cuda", dtype=torch.bfloat16)
+    nrows = _C.load().b2_rmsnorm_bwd_partial_rows(T)
+    partial = torch.empty(nrows * H, device="cuda", dtype=torch.float32)
+    yb, hb = torch.empty_like(xs[0]), torch.empty_like(xs[0])
+    ms = timeit(lambda i: _C.call("b2_rmsnorm_fwd", yb.data_ptr(), rstd.data_ptr(), hb.data_ptr(), xs[i].data_ptr(),
+                                  rs[i].data_ptr(), w.data_ptr(), T, H, 1e-5, st), n_rot)
+    results["elementwise"]["rmsnorm_res_fwd_raw"] = {"ms": ms, "gbs": 4 * T * H * 2 / ms / 1e6}
+    ms = timeit(lambda i: _C.call("b2_rmsnorm_bwd", dx.data_ptr(), dw.data_ptr(), partial.data_ptr(),
+                                  xs[i].data_ptr(), rs[i].data_ptr(), w.data_ptr(), rstd.data_ptr(),
+                                  rs[(i + 1) % n_rot].data_ptr(), T, H, 0, st), n_rot)
+    results["elementwise"]["rmsnorm_res_bwd"] = {"ms": ms, "gbs": 4 * T * H * 2 / ms / 1e6}
     gus = [rnd(T, 2 * I) for _ in range(3)]
     ms = timeit(lambda i: ops.swiglu(gus[i]), 3)
     results["elementwise"]["swiglu_fwd"] = {"ms": ms, "gbs": 3 * T * I * 2 / ms / 1e6}
+    douts = [rnd(T, I) for _ in range(3)]
+    dgu = torch.empty(T, 2 * I, device="cuda", dtype=torch.bfloat16)
+    ms = timeit(lambda i: _C.call("b2_swiglu_bwd", dgu.data_ptr(), douts[i].data_ptr(), gus[i].data_ptr(), T, I, st), 3)
+    results["elementwise"]["swiglu_bwd"] = {"ms": ms, "gbs": 5 * T * I * 2 / ms / 1e6}
+    del douts, dgu
     n = 218_112_000
     p, g, m, v = (rnd(n) for _ in range(4))
     ms = timeit(lambda i: ops.adamw_step(p, g, m, v, 1e-4, step=3), 1)

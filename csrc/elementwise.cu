@@ -86,48 +86,74 @@ __device__ __forceinline__ float block_max(float v, float* red) {
 // ------------------------------------------------------------------------------------------------
 // RMSNorm.  y = w * bf16(h * rsqrt(mean(h^2) + eps)),  h = x (+ res)   [HF LlamaRMSNorm rounding]
 // ------------------------------------------------------------------------------------------------
+template <int MV>  // 16-byte vectors per thread: sized to H so a row lives in few registers
 __global__ void __launch_bounds__(kNormThreads)
 rmsnorm_fwd_kernel(__nv_bfloat16* __restrict__ y, float* __restrict__ rstd_out,
                    __nv_bfloat16* __restrict__ h_out, const __nv_bfloat16* __restrict__ x,
                    const __nv_bfloat16* __restrict__ res, const __nv_bfloat16* __restrict__ w,
-                   int H, float eps) {
+                   int T, int H, float eps) {
   __shared__ float red[33];
-  const int row = blockIdx.x;
   const int nvec = H >> 3;
-  const BF8* xr = reinterpret_cast<const BF8*>(x + (size_t)row * H);
-  const BF8* rr = res ? reinterpret_cast<const BF8*>(res + (size_t)row * H) : nullptr;
-  float v[kNormMaxVec][8];
-  float ss = 0.f;
+  // persistent blocks (4 per SM) walking rows blockIdx.x, +gridDim.x, ...: T rows split evenly over the
+  // SMs (one block per row leaves a 13 % tail at T = 4096), the next row's loads are in flight while
+  // this row is reduced and stored
+  BF8 nx[MV], nr[MV];
+  int row = blockIdx.x;
+  if (row < T) {
 #pragma unroll
-  for (int i = 0; i < kNormMaxVec; ++i) {
-    const int idx = threadIdx.x + i * kNormThreads;
-    if (idx < nvec) {
-      bf8_to_f(xr[idx], v[i]);
-      if (rr) {
-        float r[8];
-        bf8_to_f(rr[idx], r);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[i][j] = bf16_round(v[i][j] + r[j]);
-        if (h_out) reinterpret_cast<BF8*>(h_out + (size_t)row * H)[idx] = f_to_bf8(v[i]);
+    for (int i = 0; i < MV; ++i) {
+      const int idx = threadIdx.x + i * kNormThreads;
+      if (idx < nvec) {
+        nx[i] = ld_stream(reinterpret_cast<const BF8*>(x + (size_t)row * H) + idx);
+        if (res) nr[i] = ld_stream(reinterpret_cast<const BF8*>(res + (size_t)row * H) + idx);
       }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) ss += v[i][j] * v[i][j];
     }
   }
-  ss = block_sum(ss, red);
-  const float rstd = rsqrtf(ss / (float)H + eps);
-  if (threadIdx.x == 0 && rstd_out) rstd_out[row] = rstd;
-  const BF8* wr = reinterpret_cast<const BF8*>(w);
-  BF8* yr = reinterpret_cast<BF8*>(y + (size_t)row * H);
+  for (; row < T; row += gridDim.x) {
+    float v[MV][8];
+    float ss = 0.f;
 #pragma unroll
-  for (int i = 0; i < kNormMaxVec; ++i) {
-    const int idx = threadIdx.x + i * kNormThreads;
-    if (idx < nvec) {
-      float wf[8], o[8];
-      bf8_to_f(wr[idx], wf);
+    for (int i = 0; i < MV; ++i) {
+      const int idx = threadIdx.x + i * kNormThreads;
+      if (idx < nvec) {
+        bf8_to_f(nx[i], v[i]);
+        if (res) {
+          float r[8];
+          bf8_to_f(nr[i], r);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) o[j] = wf[j] * bf16_round(v[i][j] * rstd);
-      yr[idx] = f_to_bf8(o);
+          for (int j = 0; j < 8; ++j) v[i][j] = bf16_round(v[i][j] + r[j]);
+          if (h_out) reinterpret_cast<BF8*>(h_out + (size_t)row * H)[idx] = f_to_bf8(v[i]);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) ss += v[i][j] * v[i][j];
+      }
+    }
+    const int next = row + gridDim.x;
+    if (next < T) {
+#pragma unroll
+      for (int i = 0; i < MV; ++i) {
+        const int idx = threadIdx.x + i * kNormThreads;
+        if (idx < nvec) {
+          nx[i] = ld_stream(reinterpret_cast<const BF8*>(x + (size_t)next * H) + idx);
+          if (res) nr[i] = ld_stream(reinterpret_cast<const BF8*>(res + (size_t)next * H) + idx);
+        }
+      }
+    }
+    ss = block_sum(ss, red);
+    const float rstd = rsqrtf(ss / (float)H + eps);
+    if (threadIdx.x == 0 && rstd_out) rstd_out[row] = rstd;
+    const BF8* wr = reinterpret_cast<const BF8*>(w);
+    BF8* yr = reinterpret_cast<BF8*>(y + (size_t)row * H);
+#pragma unroll
+    for (int i = 0; i < MV; ++i) {
+      const int idx = threadIdx.x + i * kNormThreads;
+      if (idx < nvec) {
+        float wf[8], o[8];
+        bf8_to_f(wr[idx], wf);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = wf[j] * bf16_round(v[i][j] * rstd);
+        yr[idx] = f_to_bf8(o);
+      }
     }
   }
 }
@@ -136,7 +162,7 @@ rmsnorm_fwd_kernel(__nv_bfloat16* __restrict__ y, float* __restrict__ rstd_out,
 // then writes one fp32 partial row into `partial` [gridDim.x, H]; a second kernel folds those rows.
 //   dx = rstd * (dy*w - xhat * mean(dy*w*xhat)) (+ dres)
 template <int MV>
-__global__ void __launch_bounds__(kNormThreads)
+__global__ void __launch_bounds__(kNormThreads, MV <= 2 ? 3 : 1)
 rmsnorm_bwd_kernel(__nv_bfloat16* __restrict__ dx, float* __restrict__ partial,
                    const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ h,
                    const __nv_bfloat16* __restrict__ w, const float* __restrict__ rstd,
@@ -144,38 +170,63 @@ rmsnorm_bwd_kernel(__nv_bfloat16* __restrict__ dx, float* __restrict__ partial,
   __shared__ float red[33];
   const int nvec = H >> 3;
   float dw[MV][8];
-  float wf[MV][8];
 #pragma unroll
-  for (int i = 0; i < MV; ++i) {
-    const int idx = threadIdx.x + i * kNormThreads;
+  for (int i = 0; i < MV; ++i)
 #pragma unroll
     for (int j = 0; j < 8; ++j) dw[i][j] = 0.f;
-    if (idx < nvec) bf8_to_f(reinterpret_cast<const BF8*>(w)[idx], wf[i]);
+  // The loads of the next row are issued before this row's block reduction: a block keeps two rows
+  // (2 x 2 x H bf16) in flight, which is what the HBM latency-bandwidth product asks of the two or
+  // three blocks an SM holds at this register count.
+  BF8 nh[MV], ng[MV], nr[MV];
+  int row = blockIdx.x;
+  if (row < T) {
+#pragma unroll
+    for (int i = 0; i < MV; ++i) {
+      const int idx = threadIdx.x + i * kNormThreads;
+      if (idx < nvec) {
+        nh[i] = ld_stream(reinterpret_cast<const BF8*>(h + (size_t)row * H) + idx);
+        ng[i] = ld_stream(reinterpret_cast<const BF8*>(dy + (size_t)row * H) + idx);
+        if (dres) nr[i] = ld_stream(reinterpret_cast<const BF8*>(dres + (size_t)row * H) + idx);
+      }
+    }
   }
-  for (int row = blockIdx.x; row < T; row += gridDim.x) {
-    const BF8* hr = reinterpret_cast<const BF8*>(h + (size_t)row * H);
-    const BF8* gr = reinterpret_cast<const BF8*>(dy + (size_t)row * H);
+  for (; row < T; row += gridDim.x) {
     const float rs = rstd[row];
     float xh[MV][8], g[MV][8];
+    BF8 rcur[MV];
     float dot = 0.f;
 #pragma unroll
     for (int i = 0; i < MV; ++i) {
       const int idx = threadIdx.x + i * kNormThreads;
       if (idx < nvec) {
-        bf8_to_f(hr[idx], xh[i]);
-        bf8_to_f(gr[idx], g[i]);
+        float wf[8];
+        bf8_to_f(reinterpret_cast<const BF8*>(w)[idx], wf);  // 2 * H bytes: stays in L1
+        bf8_to_f(nh[i], xh[i]);
+        bf8_to_f(ng[i], g[i]);
+        rcur[i] = nr[i];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           xh[i][j] *= rs;
           dw[i][j] += g[i][j] * xh[i][j];
-          g[i][j] *= wf[i][j];
+          g[i][j] *= wf[j];
           dot += g[i][j] * xh[i][j];
+        }
+      }
+    }
+    const int next = row + gridDim.x;
+    if (next < T) {
+#pragma unroll
+      for (int i = 0; i < MV; ++i) {
+        const int idx = threadIdx.x + i * kNormThreads;
+        if (idx < nvec) {
+          nh[i] = ld_stream(reinterpret_cast<const BF8*>(h + (size_t)next * H) + idx);
+          ng[i] = ld_stream(reinterpret_cast<const BF8*>(dy + (size_t)next * H) + idx);
+          if (dres) nr[i] = ld_stream(reinterpret_cast<const BF8*>(dres + (size_t)next * H) + idx);
         }
       }
     }
     dot = block_sum(dot, red) / (float)H;
     BF8* dxr = reinterpret_cast<BF8*>(dx + (size_t)row * H);
-    const BF8* drr = dres ? reinterpret_cast<const BF8*>(dres + (size_t)row * H) : nullptr;
 #pragma unroll
     for (int i = 0; i < MV; ++i) {
       const int idx = threadIdx.x + i * kNormThreads;
@@ -183,9 +234,9 @@ rmsnorm_bwd_kernel(__nv_bfloat16* __restrict__ dx, float* __restrict__ partial,
         float o[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) o[j] = rs * (g[i][j] - xh[i][j] * dot);
-        if (drr) {
+        if (dres) {
           float r[8];
-          bf8_to_f(drr[idx], r);
+          bf8_to_f(rcur[i], r);
 #pragma unroll
           for (int j = 0; j < 8; ++j) o[j] += r[j];
         }
@@ -774,10 +825,25 @@ int b2_rmsnorm_fwd(void* y, float* rstd, void* h_out, const void* x, const void*
                    const void* w, int T, int H, float eps, cudaStream_t stream) {
   B2_REQUIRE(H % 8 == 0 && H <= kNormThreads * kNormMaxVec * 8, "rmsnorm: unsupported H=%d", H);
   if (T == 0) return 0;
-  rmsnorm_fwd_kernel<<<T, kNormThreads, 0, stream>>>((bf16*)y, rstd, (bf16*)h_out, (const bf16*)x,
-                                                     (const bf16*)res, (const bf16*)w, H, eps);
+  const int grid = T < sm_count() * 4 ? T : sm_count() * 4;
+#define B2_RMS_FWD(MV)                                                                       \
+  rmsnorm_fwd_kernel<MV><<<grid, kNormThreads, 0, stream>>>((bf16*)y, rstd, (bf16*)h_out,    \
+                                                            (const bf16*)x, (const bf16*)res, \
+                                                            (const bf16*)w, T, H, eps)
+  if (H <= kNormThreads * 8) B2_RMS_FWD(1);
+  else if (H <= kNormThreads * 8 * 2) B2_RMS_FWD(2);
+  else if (H <= kNormThreads * 8 * 4) B2_RMS_FWD(4);
+  else B2_RMS_FWD(8);
+#undef B2_RMS_FWD
   B2_CUDA_CHECK(cudaGetLastError());
   return 0;
+}
+
+// one wave of resident blocks (3 per SM up to H = 4096, 1 above: register footprint); the scratch is
+// sized for b2_rmsnorm_bwd_partial_rows(T) >= this many rows
+static int rms_bwd_blocks(int T, int H) {
+  int nb = sm_count() * (H <= kNormThreads * 8 * 2 ? 3 : 1);
+  return nb < T ? nb : T;
 }
 
 // partial: caller-provided fp32 scratch of b2_rmsnorm_bwd_partial_rows(T) * H floats
@@ -786,7 +852,7 @@ int b2_rmsnorm_bwd(void* dx, void* dw, float* partial, const void* dy, const voi
                    int accumulate_dw, cudaStream_t stream) {
   B2_REQUIRE(H % 8 == 0 && H <= kNormThreads * kNormMaxVec * 8, "rmsnorm: unsupported H=%d", H);
   if (T == 0) return 0;
-  const int nb = b2_rmsnorm_bwd_partial_rows(T);
+  const int nb = rms_bwd_blocks(T, H);
 #define B2_RMS_BWD(MV)                                                                     \
   rmsnorm_bwd_kernel<MV><<<nb, kNormThreads, 0, stream>>>(                                 \
       (bf16*)dx, partial, (const bf16*)dy, (const bf16*)h, (const bf16*)w, rstd,           \
@@ -1022,8 +1088,9 @@ int b2_rmsnorm_bwd_static(void* dx, void* dw, const void* dy, const void* h, con
              (size_t)nb * (size_t)H, nb, H, (size_t)kStaticScratchFloats);
   float* partial = nullptr;
   if (int rc = static_scratch_for_current_device(&partial)) return rc;
+  const int grid = rms_bwd_blocks(T, H);  // same launch as b2_rmsnorm_bwd (<= nb partial rows)
 #define B2_RMS_BWD(MV)                                                                     \
-  rmsnorm_bwd_kernel<MV><<<nb, kNormThreads, 0, stream>>>(                                 \
+  rmsnorm_bwd_kernel<MV><<<grid, kNormThreads, 0, stream>>>(                                 \
       (bf16*)dx, partial, (const bf16*)dy, (const bf16*)h, (const bf16*)w, rstd,           \
       (const bf16*)dres, T, H)
   if (H <= kNormThreads * 8 * 2) B2_RMS_BWD(2);
@@ -1031,7 +1098,7 @@ int b2_rmsnorm_bwd_static(void* dx, void* dw, const void* dy, const void* h, con
   else B2_RMS_BWD(8);
 #undef B2_RMS_BWD
   B2_CUDA_CHECK(cudaGetLastError());
-  fold_partials_kernel<<<(H + 31) / 32, 256, 0, stream>>>((bf16*)dw, partial, nb, H,
+  fold_partials_kernel<<<(H + 31) / 32, 256, 0, stream>>>((bf16*)dw, partial, grid, H,
                                                           accumulate_dw);
   B2_CUDA_CHECK(cudaGetLastError());
   return 0;
