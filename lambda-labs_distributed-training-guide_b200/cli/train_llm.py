@@ -8,7 +8,8 @@ optimizer / cosine schedule -> resume from ``state.json`` -> metrics sink -> epo
 
 Flags keep the reference's names and defaults. Additions are optional:
 ``--strategy``, ``--device``, ``--num-workers``, ``--prefetch-factor``, ``--wandb-mode``, ``--timers``,
-``--activation-checkpointing``, ``--grad-accum-steps``, ``--deterministic``, ``--zero1``, ``--max-steps``.
+``--activation-checkpointing``, ``--grad-accum-steps``, ``--deterministic``, ``--zero1``, ``--max-steps``,
+``--sharding-strategy`` / ``--replicas`` (FSDP chapters).
 """
 from __future__ import annotations
 
@@ -57,6 +58,12 @@ def get_parser(chapter: str = "generic") -> argparse.ArgumentParser:
                        help="Only applies FSDP to modules with numel > this value.")
     if chapter in ("04-fsdp", "05-405b", "generic"):
         p.add_argument("--cpu-offload", default="on" if chapter == "05-405b" else "off", choices=["on", "off"])
+        # the strategies tabulated in 04-fully-sharded-data-parallel/README.md:146-151 (the reference
+        # hard-codes FULL_SHARD)
+        p.add_argument("--sharding-strategy", default="full_shard",
+                       choices=["full_shard", "shard_grad_op", "no_shard", "hybrid_shard"])
+        p.add_argument("--replicas", default=None, type=int,
+                       help="hybrid_shard: number of replica groups (default: one per node)")
     if chapter in ("07-2d-parallel", "generic"):
         p.add_argument("--tp", default=8 if chapter == "07-2d-parallel" else 1, type=int)
     if chapter == "deepspeed":
@@ -146,9 +153,18 @@ def main(chapter: str = "generic", argv=None):
     if device.type == "cpu":
         kw["dtype"] = torch.bfloat16 if os.environ.get("B200TRAIN_CPU_BF16") else torch.float32
     act = args.activation_checkpointing or ("on" if chapter == "05-405b" else "off")
+    sharding = getattr(args, "sharding_strategy", "full_shard") if strategy_name == "fsdp" else "full_shard"
+    if sharding == "no_shard":          # replicated parameters, gradients and optimizer state = plain DDP
+        strategy_name = "ddp"
+        args.zero1 = "off"
     if strategy_name == "fsdp":
         kw.update(cpu_offload=getattr(args, "cpu_offload", "off") == "on", activation_checkpointing=act == "on",
                   numel_to_wrap=getattr(args, "numel_to_wrap", 0))
+        if sharding == "shard_grad_op":  # parameters stay gathered between forward and backward (ZeRO-2)
+            kw.update(reshard_after_forward=False)
+        elif sharding == "hybrid_shard":
+            strategy_name = "hsdp"
+            kw.update(replicas=args.replicas)
     elif strategy_name == "ddp":
         kw.update(zero1=(args.zero1 or "on") == "on")
     elif strategy_name in ("tp", "2d"):
@@ -182,7 +198,7 @@ def main(chapter: str = "generic", argv=None):
     LOGGER.info(f"{len(dataloader)} batches per epoch")
 
     exp_dir = Path(args.save_dir) / args.experiment_name
-    sharded_ckpt = strategy_name in ("fsdp", "tp", "2d") or (strategy_name == "ddp" and kw.get("zero1"))
+    sharded_ckpt = strategy_name in ("fsdp", "hsdp", "tp", "2d") or (strategy_name == "ddp" and kw.get("zero1"))
 
     # ---- resume ----
     state = ckpt.new_state()

@@ -14,6 +14,9 @@ def make_strategy(name: str, cfg, device, **kw) -> Strategy:
     if name == "fsdp":
         from .fsdp import FSDP
         return FSDP(cfg, device, **kw)
+    if name in ("hsdp", "hybrid_shard"):
+        from .fsdp import HSDP
+        return HSDP(cfg, device, **kw)
     if name == "tp":
         from .tp import TensorParallel
         return TensorParallel(cfg, device, **kw)

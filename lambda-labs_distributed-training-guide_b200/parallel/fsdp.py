@@ -173,6 +173,13 @@ class FSDP(Strategy):
     def pre_reduce(self, i):
         """Called when unit ``i``'s gradients are complete, before they are reduced over this group."""
 
+    # set by strategies that reduce the gradient shard over a second group (hybrid shard): the fused
+    # reduce-scatter + AdamW kernel is then bypassed, the update must see the fully reduced shard
+    has_post_reduce = False
+
+    def post_reduce(self, i, shard):
+        """Called on the comm stream with unit ``i``'s reduced gradient shard, before it is consumed."""
+
     # ------------------------------------------------------------------------------------------------
     @property
     def rank(self):
@@ -313,7 +320,7 @@ class FSDP(Strategy):
             full.add_(self._local_acc.pop(i))
         ready = self._record()
         slot = self._grad_slot.pop(i)
-        if self.fuse_optimizer and self.fuse_in_kernel and self.W > 1:
+        if self.fuse_optimizer and self.fuse_in_kernel and self.W > 1 and not self.has_post_reduce:
             # one kernel: pull + reduce the peers' gradient slices and apply AdamW to the owned shard
             with self._on(self.comm_stream):
                 self._wait(ready, self.comm_stream)
@@ -334,9 +341,11 @@ class FSDP(Strategy):
                     self.comm.reduce_scatter(dev, full, average=True)
                 else:
                     dev = full[:n]
+                self.post_reduce(i, dev)
                 self.shard_grad[i].copy_(dev, non_blocking=True)      # D2H into pinned memory
             else:
                 self.comm.reduce_scatter(self.shard_grad[i], full, average=True)
+                self.post_reduce(i, self.shard_grad[i])
             done = self._record(self.comm_stream)
         if self._cpu_worker is not None:
             self._submit_cpu_step(i, done)
@@ -560,3 +569,69 @@ class _Layout(FlatUnit):
         for p in self.params:
             if not getattr(p, "_b2_grad_ready", False):
                 p.grad.zero_()
+
+
+class HSDP(FSDP):
+    """Hybrid shard: FULL_SHARD inside a replica group (by default one node), replicas kept identical by
+    averaging the reduced gradient shards across them.
+
+    Reference: the ``HYBRID_SHARD`` row of the sharding-strategy table
+    (``04-fully-sharded-data-parallel/README.md:146-151``; not exposed as a flag there). Ranks
+    ``[r * S, (r + 1) * S)`` form replica ``r`` and shard over the peer-memory communicator (NVLink inside
+    the node); the ranks holding the same shard index in different replicas all-reduce that shard
+    (inter-node traffic is 1/S of a DDP all-reduce). Every replica initialises from the same seed, so
+    no parameter broadcast is needed.
+    """
+
+    name = "hsdp"
+    has_post_reduce = True
+
+    def __init__(self, cfg, device, lr=3e-5, seed=0, dtype=torch.bfloat16, replicas: Optional[int] = None, **kw):
+        import torch.distributed as dist
+
+        if not dist.is_initialized():
+            raise RuntimeError("HSDP needs an initialised process group")
+        world, rank = dist.get_world_size(), dist.get_rank()
+        if replicas is None:  # one replica per node
+            local = int(os.environ.get("LOCAL_WORLD_SIZE", world))
+            replicas = max(world // max(local, 1), 1)
+        if world % replicas:
+            raise ValueError(f"world size {world} is not a multiple of {replicas} replicas")
+        S = world // replicas
+        if S < 2:
+            raise ValueError("hybrid shard needs at least 2 ranks per replica (use DDP otherwise)")
+        self.replicas, self.replica_id = replicas, rank // S
+        self.global_rank, self.global_world = rank, world
+        # every rank creates every group, in the same order
+        shard_groups = [dist.new_group(list(range(r * S, (r + 1) * S))) for r in range(replicas)]
+        rep_groups = [dist.new_group(list(range(k, world, S))) for k in range(S)]
+        self.rep_group = rep_groups[rank % S] if replicas > 1 else None
+        kw.pop("comm", None)
+        super().__init__(cfg, device, lr=lr, seed=seed, dtype=dtype, group=shard_groups[rank // S], **kw)
+
+    def post_reduce(self, i, shard):
+        if self.rep_group is None:
+            return
+        import torch.distributed as dist
+
+        dist.all_reduce(shard, group=self.rep_group)   # SUM: gloo has no AVG
+        shard.div_(self.replicas)
+
+    @property
+    def rank(self):
+        return self.global_rank
+
+    @property
+    def world_size(self):
+        return self.global_world
+
+    def data_parallel_coords(self):
+        return self.global_rank, self.global_world
+
+    def tokens_per_step(self, batch_size, seq_len):
+        return self.global_world * batch_size * seq_len
+
+    def barrier(self):
+        import torch.distributed as dist
+
+        dist.barrier()

@@ -40,6 +40,8 @@ COMMON = ["-d", "synthetic:64", "-m", "llama-tiny", "--device", "cpu", "-b", "2"
     ("01-single-gpu/train_llm.py", 1, [], False),
     ("02-distributed-data-parallel/train_llm.py", 2, [], True),
     ("04-fully-sharded-data-parallel/train_llm.py", 2, ["--cpu-offload", "off", "--numel-to-wrap", "1000"], True),
+    ("04-fully-sharded-data-parallel/train_llm.py", 4, ["--sharding-strategy", "hybrid_shard", "--replicas", "2"], True),
+    ("04-fully-sharded-data-parallel/train_llm.py", 2, ["--sharding-strategy", "shard_grad_op"], True),
     ("05-training-llama-405b/train_llm.py", 2, ["--num-workers", "0"], True),
     ("06-tensor-parallel/train_llm.py", 2, ["--num-workers", "0"], True),
     ("07-2d-parallel/train_llm.py", 4, ["--tp", "2", "--num-workers", "0"], True),

@@ -255,3 +255,41 @@ def test_fsdp_size_based_wrap_groups_layers():
     got = _dist_losses("fsdp", kw)
     for a, b in zip(ref, got):
         assert abs(a - b) < 2e-3, (ref, got)
+
+
+def w_hsdp(rank, world, tmp):
+    """2 replicas x 2 shards: losses of 3 steps, then a DCP round trip into a fresh engine."""
+    from b200train.ckpt.dcp import load_sharded, save_sharded
+    from b200train.models import load_config
+    from b200train.parallel import make_strategy
+
+    cfg = load_config("llama-tiny")
+    eng = make_strategy("hsdp", cfg, "cpu", lr=1e-3, dtype=torch.float32, replicas=2)
+    assert eng.world_size == 4 and eng.W == 2 and eng.tokens_per_step(1, 32) == 4 * 32
+    out = []
+    for ids in _batches(cfg, 3, 4, 32):
+        mine = ids[rank:rank + 1]
+        t = eng.train_step({"input_ids": mine, "labels": mine}).detach().clone()
+        dist.all_reduce(t)
+        out.append((t / world).item())
+    # replicas hold identical shards after training
+    same = [torch.zeros_like(eng.shard_param[1]) for _ in range(2)]
+    dist.all_gather(same, eng.shard_param[1], group=eng.rep_group)
+    assert torch.equal(same[0], same[1])
+    save_sharded(tmp, eng)
+    eng2 = make_strategy("hsdp", cfg, "cpu", lr=1e-3, dtype=torch.float32, replicas=2, seed=123)
+    load_sharded(tmp, eng2)
+    for a, b in zip(eng.shard_param, eng2.shard_param):
+        assert torch.equal(a, b)
+    ids = _batches(cfg, 1, 4, 32, seed=9)[0][rank:rank + 1]
+    la = eng.train_step({"input_ids": ids, "labels": ids}).item()
+    lb = eng2.train_step({"input_ids": ids, "labels": ids}).item()
+    assert abs(la - lb) < 1e-5, (la, lb)
+    return out
+
+
+def test_hybrid_shard_matches_single_process(tmp_path):
+    ref = _single_losses("fsdp", {})
+    got = run_dist("w_hsdp", str(tmp_path), world=4)[0]
+    for a, b in zip(ref, got):
+        assert abs(a - b) < 2e-3, (ref, got)
