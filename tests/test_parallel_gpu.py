@@ -74,6 +74,7 @@ CASES = [
     ("fsdp", dict(), 2), ("fsdp", dict(fuse_optimizer="kernel"), 2), ("fsdp", dict(fuse_optimizer="stream"), 2),
     ("fsdp", dict(cpu_offload=True), 2), ("fsdp", dict(activation_checkpointing=True), 2),
     ("tp", dict(tp=2), 2), ("2d", dict(tp=2), 4),
+    ("hsdp", dict(replicas=2, fuse_optimizer="stream"), 4), ("fsdp", dict(numel_to_wrap=10_000_000), 2),
 ]
 
 
@@ -81,7 +82,7 @@ CASES = [
 def test_strategy_matches_single_gpu(strategy, kw, world):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
-    if strategy in ("fsdp", "2d"):
+    if strategy in ("fsdp", "2d", "hsdp"):
         # per-unit init differs from the single-device init: same batch repeated must be learned
         got = _run(strategy, kw, world, steps=6, repeat=True)
         assert got[-1] < got[0] - 0.5 and abs(got[0] - 6.93) < 0.3, got
