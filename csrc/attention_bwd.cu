@@ -55,24 +55,52 @@ struct AttnBwdParams {
 };
 
 // delta[h, t] = sum_d dO[t, h, d] * O[t, h, d]
-__global__ void attn_bwd_delta_kernel(float* __restrict__ delta, const __nv_bfloat16* __restrict__ dO,
-                                      const __nv_bfloat16* __restrict__ O, int T, int Hq, int D,
-                                      int do_stride, int o_stride) {
-  const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  if (warp_global >= T * Hq) return;
-  const int t = warp_global / Hq, h = warp_global % Hq;
-  const __nv_bfloat16* a = dO + (size_t)t * do_stride + (size_t)h * D;
-  const __nv_bfloat16* b = O + (size_t)t * o_stride + (size_t)h * D;
-  float s = 0.f;
-  for (int i = lane * 2; i < D; i += 64) {
-    const float2 x = unpack_bf16(*reinterpret_cast<const uint32_t*>(a + i));
-    const float2 y = unpack_bf16(*reinterpret_cast<const uint32_t*>(b + i));
-    s += x.x * y.x + x.y * y.y;
-  }
+// D / 8 lanes per (t, h) row, one 16-byte load of each tensor per lane, four rows in flight per lane
+// group (the first version used a whole warp per row with 4-byte loads and ran at a third of the
+// memory bandwidth).
+template <int D>
+__global__ void __launch_bounds__(256)
+attn_bwd_delta_kernel(float* __restrict__ delta, const __nv_bfloat16* __restrict__ dO,
+                      const __nv_bfloat16* __restrict__ O, int T, int Hq, int do_stride,
+                      int o_stride) {
+  constexpr int kLanes = D / 8;                 // lanes per row: 16 (D = 128) or 8 (D = 64)
+  constexpr int kRowsPerBlock = 256 / kLanes;   // rows handled concurrently by a block
+  constexpr int kUnroll = 4;
+  const int sub = threadIdx.x % kLanes;
+  const int grp = threadIdx.x / kLanes;
+  const int total = T * Hq;  // rows (checked on the host to fit 31 bits)
+  for (int base = blockIdx.x * kRowsPerBlock * kUnroll; base < total;
+       base += gridDim.x * kRowsPerBlock * kUnroll) {
+    uint4 a[kUnroll], b[kUnroll];
+    int rows[kUnroll];
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-  if (lane == 0) delta[(size_t)h * T + t] = s;
+    for (int u = 0; u < kUnroll; ++u) {
+      rows[u] = base + u * kRowsPerBlock + grp;
+      if (rows[u] < total) {
+        const int t = rows[u] / Hq, h = rows[u] - t * Hq;
+        a[u] = *reinterpret_cast<const uint4*>(dO + (size_t)t * do_stride + (size_t)h * D + sub * 8);
+        b[u] = *reinterpret_cast<const uint4*>(O + (size_t)t * o_stride + (size_t)h * D + sub * 8);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      float s = 0.f;
+      if (rows[u] < total) {
+        const uint32_t av[4] = {a[u].x, a[u].y, a[u].z, a[u].w}, bv[4] = {b[u].x, b[u].y, b[u].z, b[u].w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 x = unpack_bf16(av[j]), y = unpack_bf16(bv[j]);
+          s += x.x * y.x + x.y * y.y;
+        }
+      }
+#pragma unroll
+      for (int o = kLanes / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+      if (sub == 0 && rows[u] < total) {
+        const int t = rows[u] / Hq, h = rows[u] - t * Hq;
+        delta[(size_t)h * T + t] = s;
+      }
+    }
+  }
 }
 
 // dq[t, :] = bf16(dq_accum[t, :])
@@ -898,12 +926,22 @@ int b2_attn_bwd(void* dq, void* dk, void* dv, float* dq_accum, float* delta, con
   if (T == 0 || ndocs == 0) return 0;
   B2_CUDA_CHECK(cudaMemsetAsync(dq_accum, 0, (size_t)T * Hq * D * sizeof(float), stream));
   {
-    const int warps = T * Hq;
-    const int threads = 256;
-    const int blocks = (warps * 32 + threads - 1) / threads;
-    attn_bwd_delta_kernel<<<blocks, threads, 0, stream>>>(
-        delta, static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(o), T, Hq,
-        D, do_stride, o_stride);
+    B2_REQUIRE(do_stride % 8 == 0 && o_stride % 8 == 0 && ((uintptr_t)dout & 15) == 0 && ((uintptr_t)o & 15) == 0,
+               "attn bwd: dout / o rows must be 16-byte aligned (strides %d, %d)", do_stride, o_stride);
+    B2_REQUIRE((long long)T * Hq < (1ll << 31), "attn bwd: T * Hq = %lld rows exceed 31 bits", (long long)T * Hq);
+    const long long rows = (long long)T * Hq;
+    const int rows_per_block = (256 / (D / 8)) * 4;
+    long long blocks = (rows + rows_per_block - 1) / rows_per_block;
+    const int cap = sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    if (D == 128)
+      attn_bwd_delta_kernel<128><<<(int)blocks, 256, 0, stream>>>(
+          delta, static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(o), T, Hq,
+          do_stride, o_stride);
+    else
+      attn_bwd_delta_kernel<64><<<(int)blocks, 256, 0, stream>>>(
+          delta, static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(o), T, Hq,
+          do_stride, o_stride);
     B2_CUDA_CHECK(cudaGetLastError());
   }
   // head_dim 128 runs the second-generation kernel (B200TRAIN_ATTN_BWD=1 selects the first one; the
