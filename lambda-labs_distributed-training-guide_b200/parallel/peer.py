@@ -9,6 +9,12 @@ kernels in ``csrc/comm.cu`` with loads from the mapped peer pointers and flags i
 ``reduce_scatter_adamw``. Tensors passed to its collectives must come from :meth:`empty` (strategies
 allocate shards and gradient buffers through ``comm.empty``); anything else falls back to NCCL.
 
+``B200TRAIN_COMM_DEBUG=1`` turns on a checking mode for the hand-written cross-GPU signalling (the
+reference has nothing to check: SURVEY 5.2): every reduce-scatter / all-reduce / all-gather is repeated
+through NCCL on copies of its inputs and the two results are compared on the device; a mismatch beyond
+bf16 rounding raises with the collective's name, rank and worst element. It synchronises every call and
+is meant for tests and bring-up, not for timing.
+
 Reference: the implicit NCCL all-gather / reduce-scatter / all-reduce of FSDP and DDP
 (``04-fully-sharded-data-parallel/train_llm.py:87-95``, ``02-distributed-data-parallel/train_llm.py:65``).
 """
@@ -22,6 +28,7 @@ import torch
 import torch.distributed as dist
 
 from .. import _C
+from ..obs import nvtx
 from .comm import TorchComm
 
 _ARENA_MIN_BYTES = 256 << 20
@@ -68,6 +75,8 @@ class PeerComm(TorchComm):
         self.nvls = mode == "1" or (mode == "auto" and self.world >= 4)
         # the switch saturates with few blocks in flight; fewer blocks leave more of the SMs to the GEMMs
         self.nvls_blocks = int(os.environ.get("B200TRAIN_NVLS_BLOCKS", "16"))
+        self.debug = os.environ.get("B200TRAIN_COMM_DEBUG", "0") == "1"
+        self.debug_checks = 0
         pad = self.empty(64 * 16, torch.int32)   # signal pad: [channel][16 ranks]
         pad.zero_()
         self._pad = pad
@@ -138,12 +147,12 @@ class PeerComm(TorchComm):
         _C.call("b2_peer_barrier", self._pad_ptrs, self.rank, self.world, CHAN_BARRIER,
                 self._epoch(CHAN_BARRIER), self._stream())
 
-    def all_gather(self, full, shard, max_blocks: int = 64, copy_engine: Optional[bool] = None):
+    def _all_gather(self, full, shard, max_blocks: int = 64, copy_engine: Optional[bool] = None):
         """``full`` is local; ``shard`` must be symmetric. Source shards must be stable: the caller
         orders them against their last writer with :meth:`barrier` (FSDP does this once per step)."""
         srcs = self._peer_array(shard) if self.world > 1 else None
         if srcs is None:
-            return super().all_gather(full, shard)
+            return TorchComm.all_gather(self, full, shard)
         n = shard.numel() * shard.element_size()
         skip_self = int(full.data_ptr() + self.rank * n == shard.data_ptr())
         if self.copy_engine if copy_engine is None else copy_engine:
@@ -167,10 +176,10 @@ class PeerComm(TorchComm):
             _C.call("b2_peer_all_gather", full.data_ptr(), srcs, n, self.rank, self.world, 1, max_blocks,
                     self._stream())
 
-    def reduce_scatter(self, shard, full, average=True, max_blocks: int = 0, nvls: Optional[bool] = None):
+    def _reduce_scatter(self, shard, full, average=True, max_blocks: int = 0, nvls: Optional[bool] = None):
         fulls = self._peer_array(full) if self.world > 1 else None
         if fulls is None or shard.dtype != torch.bfloat16:
-            return super().reduce_scatter(shard, full, average)
+            return TorchComm.reduce_scatter(self, shard, full, average)
         mc = self._mc_ptr(full) if (self.nvls if nvls is None else nvls) else 0
         if mc:
             _C.call("b2_nvls_reduce_scatter", shard.data_ptr(), mc, shard.numel(), self.rank, self.world,
@@ -201,10 +210,10 @@ class PeerComm(TorchComm):
                 self._stream())
         return True
 
-    def all_reduce(self, t, average=True, max_blocks: int = 64, nvls: Optional[bool] = None):
+    def _all_reduce(self, t, average=True, max_blocks: int = 64, nvls: Optional[bool] = None):
         bufs = self._peer_array(t) if self.world > 1 else None
         if bufs is None or t.dtype != torch.bfloat16 or t.numel() % (8 * self.world):
-            return super().all_reduce(t, average)
+            return TorchComm.all_reduce(self, t, average)
         # the one-pass multimem all-reduce beats the two-phase peer kernel at every W measured
         mc = self._mc_ptr(t) if ((os.environ.get("B200TRAIN_NVLS", "auto") != "0") if nvls is None else nvls) else 0
         if mc:
@@ -216,3 +225,48 @@ class PeerComm(TorchComm):
                 (1.0 / self.world) if average else 1.0, self._pad_ptrs, CHAN_AR, self._epoch(CHAN_AR),
                 self._counter().data_ptr(), max_blocks, self._stream())
         return t
+
+    # ---- public surface: NVTX range + optional cross-check against NCCL --------------------------------
+    def _check(self, what: str, got: torch.Tensor, want: torch.Tensor, tol: float):
+        torch.cuda.synchronize(self.device)
+        err = (got.float() - want.float()).abs()
+        bound = tol * want.float().abs().clamp_min(1.0)
+        bad = err > bound
+        self.debug_checks += 1
+        if bool(bad.any()):
+            i = int(err.argmax())
+            raise RuntimeError(f"peer collective mismatch in {what} on rank {self.rank}/{self.world}: element {i} "
+                               f"is {float(got.flatten()[i])}, NCCL gives {float(want.flatten()[i])} "
+                               f"({int(bad.sum())} of {got.numel()} elements outside tolerance)")
+
+    def all_gather(self, full, shard, **kw):
+        with nvtx.range("comm.all_gather"):
+            self._all_gather(full, shard, **kw)
+        if self.debug and self.world > 1:
+            want = torch.empty_like(full)
+            dist.all_gather_into_tensor(want, shard.clone(), group=self.group)
+            self._check("all_gather", full, want, 0.0)
+
+    def reduce_scatter(self, shard, full, average=True, **kw):
+        snap = full.clone() if self.debug and self.world > 1 else None
+        with nvtx.range("comm.reduce_scatter"):
+            self._reduce_scatter(shard, full, average, **kw)
+        if snap is not None:
+            want = snap.float()                         # exact fp32 sum: NCCL's bf16 reduction rounds per hop
+            dist.all_reduce(want, group=self.group)
+            if average:
+                want /= self.world
+            n = shard.numel()
+            self._check("reduce_scatter", shard, want[self.rank * n:(self.rank + 1) * n], 2 ** -6)
+
+    def all_reduce(self, t, average=True, **kw):
+        snap = t.clone() if self.debug and self.world > 1 else None
+        with nvtx.range("comm.all_reduce"):
+            out = self._all_reduce(t, average, **kw)
+        if snap is not None:
+            want = snap.float()
+            dist.all_reduce(want, group=self.group)
+            if average:
+                want /= self.world
+            self._check("all_reduce", t, want, 2 ** -6)
+        return out

@@ -38,6 +38,7 @@ def _worker(rank, world, port, ret, nvls=False):
         g = torch.Generator(device="cuda").manual_seed(100 + rank)
         errs = {}
         for it in range(3):  # repeated calls exercise the epoch / counter protocol
+            comm.debug = it == 2  # last round: the built-in NCCL cross-check must agree too
             full = comm.empty(n * world)
             full.copy_(torch.randn(n * world, device="cuda", generator=g).to(torch.bfloat16))
             ref_full = full.clone()
@@ -79,6 +80,7 @@ def _worker(rank, world, port, ret, nvls=False):
             torch.cuda.synchronize()
             errs[f"rsadam{it}"] = (p.float() - p2.float()).abs().max().item()
             dist.barrier()
+        assert comm.debug_checks >= 3, comm.debug_checks
         ret[rank] = errs
     finally:
         dist.destroy_process_group()
