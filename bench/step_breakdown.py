@@ -39,18 +39,20 @@ for e in evs:
     name = e.name.split("<")[0].split("(")[0][:60]
     by[name][0] += 1
     by[name][1] += e.device_time
-    ivals.append((e.time_range.start, e.time_range.end))
+    ivals.append((e.time_range.start, e.time_range.end, name))
 ivals.sort()
-span = (max(b for _, b in ivals) - ivals[0][0]) / 1e3
-busy, cur_s, cur_e = 0.0, *ivals[0]
-gaps = []
-for s, e_ in ivals[1:]:
+span = (max(b for _, b, _ in ivals) - ivals[0][0]) / 1e3
+busy, cur_s, cur_e, cur_n = 0.0, *ivals[0]
+gaps, gap_where = [], []
+for s, e_, n_ in ivals[1:]:
     if s > cur_e:
         busy += cur_e - cur_s
         gaps.append(s - cur_e)
-        cur_s, cur_e = s, e_
+        gap_where.append((s - cur_e, cur_n, n_))
+        cur_s, cur_e, cur_n = s, e_, n_
     else:
-        cur_e = max(cur_e, e_)
+        if e_ > cur_e:
+            cur_e, cur_n = e_, n_
 busy += cur_e - cur_s
 rows = sorted(((v[1] / 1e3, v[0], k) for k, v in by.items()), reverse=True)
 out = {"model": args.model, "span_ms": span, "union_busy_ms": busy / 1e3, "idle_ms": span - busy / 1e3,
@@ -61,3 +63,6 @@ Path(args.out).write_text(json.dumps(out, indent=1))
 print(json.dumps({k: v for k, v in out.items() if k != "kernels"}))
 for ms, n, k in rows[:25]:
     print(f"{ms:9.3f} ms  {n:5d}  {k}")
+print("largest idle gaps (us, kernel before -> kernel after):")
+for g, a, b in sorted(gap_where, reverse=True)[:12]:
+    print(f"{g:9.1f}  {a} -> {b}")

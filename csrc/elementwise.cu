@@ -419,22 +419,176 @@ layernorm_bwd_kernel(__nv_bfloat16* __restrict__ dx, float* __restrict__ partial
   }
 }
 
-__global__ void fold_partials2_kernel(__nv_bfloat16* __restrict__ dw, __nv_bfloat16* __restrict__ db,
-                                      const float* __restrict__ partial, int nblocks, int H,
-                                      int accumulate) {
-  const int hcol = blockIdx.x * blockDim.x + threadIdx.x;
-  if (hcol >= H) return;
-  float s = 0.f, t = 0.f;
-  for (int b = 0; b < nblocks; ++b) {
-    s += partial[(size_t)b * 2 * H + hcol];
-    t += partial[(size_t)b * 2 * H + H + hcol];
+// partial [nblocks, 2H] (dw row | db row): block = 32 columns x 8 row slices, like fold_partials_kernel
+__global__ void __launch_bounds__(256)
+fold_partials2_kernel(__nv_bfloat16* __restrict__ dw, __nv_bfloat16* __restrict__ db,
+                      const float* __restrict__ partial, int nblocks, int H, int accumulate) {
+  __shared__ float red[8][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int col = blockIdx.x * 32 + tx;  // column in [0, 2H)
+  float s = 0.f;
+  if (col < 2 * H)
+    for (int b = ty; b < nblocks; b += 8) s += partial[(size_t)b * 2 * H + col];
+  red[ty][tx] = s;
+  __syncthreads();
+  if (ty == 0 && col < 2 * H) {
+#pragma unroll
+    for (int k = 1; k < 8; ++k) s += red[k][tx];
+    __nv_bfloat16* out = col < H ? dw + col : db + (col - H);
+    if (accumulate) s += __bfloat162float(*out);
+    *out = __float2bfloat16_rn(s);
   }
-  if (accumulate) {
-    s += __bfloat162float(dw[hcol]);
-    t += __bfloat162float(db[hcol]);
+}
+
+// ---- H <= 1024 (GPT-2 scale): one warp per row, the row in registers, shuffles only ----------------
+// The block-per-row kernels above leave most of a 256-thread block idle at H = 768 (96 vectors) and pay
+// two block reductions per row; here a warp owns a row (MV <= 4 vectors per lane) and a block of eight
+// warps walks eight rows at a time.
+template <int MV>
+__global__ void __launch_bounds__(256)
+layernorm_fwd_warp_kernel(__nv_bfloat16* __restrict__ y, float* __restrict__ mean_out,
+                          float* __restrict__ rstd_out, __nv_bfloat16* __restrict__ h_out,
+                          const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res,
+                          const __nv_bfloat16* __restrict__ w, const __nv_bfloat16* __restrict__ b,
+                          int T, int H, float eps) {
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int nvec = H >> 3;
+  const float inv_h = 1.f / (float)H;
+  for (int row = blockIdx.x * 8 + wib; row < T; row += gridDim.x * 8) {
+    const BF8* xr = reinterpret_cast<const BF8*>(x + (size_t)row * H);
+    const BF8* rr = res ? reinterpret_cast<const BF8*>(res + (size_t)row * H) : nullptr;
+    float v[MV][8];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < MV; ++i) {
+      const int idx = lane + i * 32;
+      if (idx < nvec) {
+        bf8_to_f(ld_stream(xr + idx), v[i]);
+        if (rr) {
+          float r[8];
+          bf8_to_f(ld_stream(rr + idx), r);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[i][j] = bf16_round(v[i][j] + r[j]);
+          if (h_out) reinterpret_cast<BF8*>(h_out + (size_t)row * H)[idx] = f_to_bf8(v[i]);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += v[i][j];
+      }
+    }
+    const float mean = warp_sum(s) * inv_h;
+    float ss = 0.f;
+#pragma unroll
+    for (int i = 0; i < MV; ++i)
+      if (lane + i * 32 < nvec) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float d = v[i][j] - mean;
+          ss += d * d;
+        }
+      }
+    const float rstd = rsqrtf(warp_sum(ss) * inv_h + eps);
+    if (lane == 0) {
+      if (mean_out) mean_out[row] = mean;
+      if (rstd_out) rstd_out[row] = rstd;
+    }
+    BF8* yr = reinterpret_cast<BF8*>(y + (size_t)row * H);
+#pragma unroll
+    for (int i = 0; i < MV; ++i) {
+      const int idx = lane + i * 32;
+      if (idx < nvec) {
+        float wf[8], bf[8], o[8];
+        bf8_to_f(reinterpret_cast<const BF8*>(w)[idx], wf);
+        bf8_to_f(reinterpret_cast<const BF8*>(b)[idx], bf);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mean) * rstd * wf[j] + bf[j];
+        yr[idx] = f_to_bf8(o);
+      }
+    }
   }
-  dw[hcol] = __float2bfloat16_rn(s);
-  db[hcol] = __float2bfloat16_rn(t);
+}
+
+// Backward, same layout. Each warp keeps its dw / db partial sums in registers over its rows; at the end
+// the eight warps of a block add them into a shared [2H] fp32 row, which becomes one partial row.
+template <int MV>
+__global__ void __launch_bounds__(256, 2)
+layernorm_bwd_warp_kernel(__nv_bfloat16* __restrict__ dx, float* __restrict__ partial,
+                          const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ h,
+                          const __nv_bfloat16* __restrict__ w, const float* __restrict__ mean,
+                          const float* __restrict__ rstd, const __nv_bfloat16* __restrict__ dres,
+                          int T, int H) {
+  extern __shared__ float acc[];  // [2H]
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int nvec = H >> 3;
+  const float inv_h = 1.f / (float)H;
+  for (int i = threadIdx.x; i < 2 * H; i += 256) acc[i] = 0.f;
+  __syncthreads();
+  float dw[MV][8], db[MV][8];
+#pragma unroll
+  for (int i = 0; i < MV; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { dw[i][j] = 0.f; db[i][j] = 0.f; }
+  for (int row = blockIdx.x * 8 + wib; row < T; row += gridDim.x * 8) {
+    const BF8* hr = reinterpret_cast<const BF8*>(h + (size_t)row * H);
+    const BF8* gr = reinterpret_cast<const BF8*>(dy + (size_t)row * H);
+    const BF8* drr = dres ? reinterpret_cast<const BF8*>(dres + (size_t)row * H) : nullptr;
+    const float mu = mean[row], rs = rstd[row];
+    float xh[MV][8], g[MV][8];
+    BF8 rraw[MV];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < MV; ++i) {
+      const int idx = lane + i * 32;
+      if (idx < nvec) {
+        bf8_to_f(ld_stream(hr + idx), xh[i]);
+        bf8_to_f(ld_stream(gr + idx), g[i]);
+        if (drr) rraw[i] = ld_stream(drr + idx);
+        float wf[8];
+        bf8_to_f(reinterpret_cast<const BF8*>(w)[idx], wf);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          xh[i][j] = (xh[i][j] - mu) * rs;
+          dw[i][j] += g[i][j] * xh[i][j];
+          db[i][j] += g[i][j];
+          g[i][j] *= wf[j];
+          s1 += g[i][j];
+          s2 += g[i][j] * xh[i][j];
+        }
+      }
+    }
+    s1 = warp_sum(s1) * inv_h;
+    s2 = warp_sum(s2) * inv_h;
+    BF8* dxr = reinterpret_cast<BF8*>(dx + (size_t)row * H);
+#pragma unroll
+    for (int i = 0; i < MV; ++i) {
+      const int idx = lane + i * 32;
+      if (idx < nvec) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = rs * (g[i][j] - s1 - xh[i][j] * s2);
+        if (drr) {
+          float r[8];
+          bf8_to_f(rraw[i], r);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] += r[j];
+        }
+        dxr[idx] = f_to_bf8(o);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < MV; ++i) {
+    const int idx = lane + i * 32;
+    if (idx < nvec) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        atomicAdd(&acc[idx * 8 + j], dw[i][j]);
+        atomicAdd(&acc[H + idx * 8 + j], db[i][j]);
+      }
+    }
+  }
+  __syncthreads();
+  float* prow = partial + (size_t)blockIdx.x * 2 * H;
+  for (int i = threadIdx.x; i < 2 * H; i += 256) prow[i] = acc[i];
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -873,6 +1027,21 @@ int b2_layernorm_fwd(void* y, float* mean, float* rstd, void* h_out, const void*
                      cudaStream_t stream) {
   B2_REQUIRE(H % 8 == 0 && H <= kNormThreads * kNormMaxVec * 8, "layernorm: unsupported H=%d", H);
   if (T == 0) return 0;
+  if (H <= 1024) {
+    const int want = (T + 7) / 8, cap = sm_count() * 8;
+    const int grid = want < cap ? want : cap;
+#define B2_LN_FWD(MV)                                                                          \
+  layernorm_fwd_warp_kernel<MV><<<grid, 256, 0, stream>>>(                                     \
+      (bf16*)y, mean, rstd, (bf16*)h_out, (const bf16*)x, (const bf16*)res, (const bf16*)w,    \
+      (const bf16*)b, T, H, eps)
+    if (H <= 256) B2_LN_FWD(1);
+    else if (H <= 512) B2_LN_FWD(2);
+    else if (H <= 768) B2_LN_FWD(3);
+    else B2_LN_FWD(4);
+#undef B2_LN_FWD
+    B2_CUDA_CHECK(cudaGetLastError());
+    return 0;
+  }
   layernorm_fwd_kernel<<<T, kNormThreads, 0, stream>>>((bf16*)y, mean, rstd, (bf16*)h_out,
                                                        (const bf16*)x, (const bf16*)res,
                                                        (const bf16*)w, (const bf16*)b, H, eps);
@@ -886,13 +1055,28 @@ int b2_layernorm_bwd(void* dx, void* dw, void* db, float* partial, const void* d
                      int H, int accumulate, cudaStream_t stream) {
   B2_REQUIRE(H % 8 == 0 && H <= kNormThreads * 2 * 8, "layernorm bwd: unsupported H=%d", H);
   if (T == 0) return 0;
-  const int nb = b2_rmsnorm_bwd_partial_rows(T);
-  layernorm_bwd_kernel<<<nb, kNormThreads, 0, stream>>>((bf16*)dx, partial, (const bf16*)dy,
-                                                        (const bf16*)h, (const bf16*)w, mean, rstd,
-                                                        (const bf16*)dres, T, H);
+  int nb = b2_rmsnorm_bwd_partial_rows(T);
+  if (H <= 1024) {
+    // warp-per-row: at most 2 blocks per SM (each keeps its rows' dw / db in registers), nb <= scratch rows
+    const int want = (T + 7) / 8, cap = sm_count() * 2;
+    nb = want < cap ? want : cap;
+#define B2_LN_BWD(MV)                                                                            \
+  layernorm_bwd_warp_kernel<MV><<<nb, 256, 2 * H * sizeof(float), stream>>>(                     \
+      (bf16*)dx, partial, (const bf16*)dy, (const bf16*)h, (const bf16*)w, mean, rstd,           \
+      (const bf16*)dres, T, H)
+    if (H <= 256) B2_LN_BWD(1);
+    else if (H <= 512) B2_LN_BWD(2);
+    else if (H <= 768) B2_LN_BWD(3);
+    else B2_LN_BWD(4);
+#undef B2_LN_BWD
+  } else {
+    layernorm_bwd_kernel<<<nb, kNormThreads, 0, stream>>>((bf16*)dx, partial, (const bf16*)dy,
+                                                          (const bf16*)h, (const bf16*)w, mean, rstd,
+                                                          (const bf16*)dres, T, H);
+  }
   B2_CUDA_CHECK(cudaGetLastError());
-  fold_partials2_kernel<<<(H + 255) / 256, 256, 0, stream>>>((bf16*)dw, (bf16*)db, partial, nb, H,
-                                                             accumulate);
+  fold_partials2_kernel<<<(2 * H + 31) / 32, 256, 0, stream>>>((bf16*)dw, (bf16*)db, partial, nb, H,
+                                                               accumulate);
   B2_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
