@@ -944,10 +944,10 @@ int b2_attn_bwd(void* dq, void* dk, void* dv, float* dq_accum, float* delta, con
           do_stride, o_stride);
     B2_CUDA_CHECK(cudaGetLastError());
   }
-  // head_dim 128 runs the second-generation kernel (B200TRAIN_ATTN_BWD=1 selects the first one; the
+  // head_dim 128 runs the second-generation kernel (B200TRAIN_ATTN_BWD_GEN=1 selects the first one; the
   // dk / dv rows are written with 16-byte stores there, so their strides must allow it)
   static const bool want_v2 = [] {
-    const char* e = getenv("B200TRAIN_ATTN_BWD");
+    const char* e = getenv("B200TRAIN_ATTN_BWD_GEN");
     return !(e && e[0] == '1');
   }();
   const bool v2 = want_v2 && D == 128 && dk_stride % 8 == 0 && dv_stride % 8 == 0 &&

@@ -688,10 +688,10 @@ int b2_attn_fwd(void* o, float* lse, const void* q, const void* k, const void* v
   prm.scale_log2 = softmax_scale * 1.4426950408889634f;
   prm.causal = causal;
   const int max_qb = (max_seqlen + ABM - 1) / ABM;
-  // default: one warpgroup per CTA, two CTAs per SM; B200TRAIN_ATTN_FWD=2 selects the ping-pong kernel
+  // default: one warpgroup per CTA, two CTAs per SM; B200TRAIN_ATTN_FWD_PINGPONG=1 selects the ping-pong kernel
   static const bool pingpong = [] {
-    const char* e = getenv("B200TRAIN_ATTN_FWD");
-    return e && e[0] == '2';
+    const char* e = getenv("B200TRAIN_ATTN_FWD_PINGPONG");
+    return e && e[0] == '1';
   }();
   if (pingpong) {
     if (D == 64) return launch_attn_fwd<64>(tmQ, tmK, tmV, prm, max_qb, ndocs, stream);
