@@ -592,6 +592,39 @@ layernorm_bwd_warp_kernel(__nv_bfloat16* __restrict__ dx, float* __restrict__ pa
 }
 
 // ------------------------------------------------------------------------------------------------
+// Column sums of a [T, N] bf16 matrix (bias gradients of GPT-2's Conv1D layers: db = sum_t dy[t, :]).
+// grid (ceil(N / 256), R): a warp reads 256 consecutive columns of one row (16 bytes per lane), the eight
+// warps of a block take every eighth row of the block's slice, the block writes one fp32 partial row;
+// fold_partials_kernel adds the R rows up (and accumulates into an existing gradient).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+colsum_partial_kernel(float* __restrict__ partial, const __nv_bfloat16* __restrict__ x, int T, int N,
+                      int ld) {
+  __shared__ float red[8][257];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int col = blockIdx.x * 256 + lane * 8;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (col < N) {
+    for (int row = blockIdx.y * 8 + wib; row < T; row += gridDim.y * 8) {
+      float v[8];
+      bf8_to_f(ld_stream(reinterpret_cast<const BF8*>(x + (size_t)row * ld + col)), v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += v[j];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[wib][lane * 8 + j] = acc[j];
+  __syncthreads();
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c < N) {
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += red[k][threadIdx.x];
+    partial[(size_t)blockIdx.y * N + c] = s;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // SwiGLU on a fused [T, 2I] gate|up buffer, and gelu_new
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ BF8 swiglu_vec(const BF8& gv, const BF8& uv) {
@@ -1077,6 +1110,27 @@ int b2_layernorm_bwd(void* dx, void* dw, void* db, float* partial, const void* d
   B2_CUDA_CHECK(cudaGetLastError());
   fold_partials2_kernel<<<(2 * H + 31) / 32, 256, 0, stream>>>((bf16*)dw, (bf16*)db, partial, nb, H,
                                                                accumulate);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// out[N] (bf16) (+)= sum over rows of x[T, N] (row stride ld). partial: fp32 scratch of
+// b2_colsum_partial_rows(T, N) * N floats.
+int b2_colsum_partial_rows(int T, int N) {
+  const int tiles = (N + 255) / 256;
+  int r = (sm_count() * 4 + tiles - 1) / tiles;
+  const int max_r = (T + 7) / 8;
+  if (r > max_r) r = max_r;
+  return r < 1 ? 1 : r;
+}
+int b2_colsum(void* out, float* partial, const void* x, int T, int N, int ld, int accumulate,
+              cudaStream_t stream) {
+  B2_REQUIRE(N % 8 == 0 && ld % 8 == 0, "colsum: N=%d ld=%d must be multiples of 8", N, ld);
+  if (T == 0 || N == 0) return 0;
+  const int R = b2_colsum_partial_rows(T, N);
+  colsum_partial_kernel<<<dim3((N + 255) / 256, R), 256, 0, stream>>>(partial, (const bf16*)x, T, N, ld);
+  B2_CUDA_CHECK(cudaGetLastError());
+  fold_partials_kernel<<<(N + 31) / 32, 256, 0, stream>>>((bf16*)out, partial, R, N, accumulate);
   B2_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

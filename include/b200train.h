@@ -111,6 +111,14 @@ int b2_adamw(void* p, void* m, void* v, const void* g, size_t n, float lr, float
              b2_stream_t stream);
 int b2_add(void* out, const void* a, const void* b, size_t n, b2_stream_t stream);
 
+/* ---- column sums (bias gradients) ---------------------------------------------------------------
+ * out[N] (+)= sum_t x[t, :]; partial: fp32 scratch of b2_colsum_partial_rows(T, N) * N floats.
+ * Reference: the bias gradients of GPT-2's Conv1D layers, computed by ATen reductions under
+ * loss.backward() (02-distributed-data-parallel/train_llm.py:160). */
+int b2_colsum_partial_rows(int T, int N);
+int b2_colsum(void* out, float* partial, const void* x, int T, int N, int ld, int accumulate,
+              b2_stream_t stream);
+
 /* ---- host AdamW for CPU-offloaded shards (OpenMP) -----------------------------------------------
  * Reference: AdamW(fused=True) running on CPU under CPUOffload, 05-training-llama-405b/README.md:147-153. */
 int b2_cpu_adamw_bf16(void* p, void* m, void* v, const void* g, size_t n, float lr, float beta1,

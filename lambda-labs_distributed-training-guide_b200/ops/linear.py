@@ -73,6 +73,22 @@ def _direct_grad(w) -> bool:
     return getattr(w, "_b2_direct_grad", False) and w.grad is not None
 
 
+_colsum_scratch = {}
+
+
+def _colsum(x2: torch.Tensor, out: torch.Tensor, accumulate: bool):
+    """out[N] (+)= x2.sum(0) with fp32 accumulation (``b2_colsum``)."""
+    T, N = x2.shape
+    lib = _C.load()
+    need = lib.b2_colsum_partial_rows(T, N) * N
+    buf = _colsum_scratch.get(x2.device)
+    if buf is None or buf.numel() < need:
+        buf = torch.empty(need, dtype=torch.float32, device=x2.device)
+        _colsum_scratch[x2.device] = buf
+    _C.call("b2_colsum", out.data_ptr(), buf.data_ptr(), x2.data_ptr(), T, N, x2.stride(0), int(accumulate),
+            stream(x2))
+
+
 class _Linear(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, bias, w_is_kn):
@@ -104,15 +120,14 @@ class _Linear(torch.autograd.Function):
             else:
                 dw = gemm(a, b, a_mn=True, b_mn=True)
         if bias is not None and ctx.needs_input_grad[2]:
-            db_new = dy2.sum(0, dtype=torch.float32).to(torch.bfloat16)
-            if _direct_grad(bias):
-                if getattr(bias, "_b2_grad_ready", False):
-                    bias.grad.add_(db_new)
-                else:
-                    bias.grad.copy_(db_new)
+            direct = _direct_grad(bias)
+            acc = direct and getattr(bias, "_b2_grad_ready", False)
+            db_out = bias.grad if direct else torch.empty_like(bias)
+            _colsum(dy2, db_out, acc)      # one pass + fold, written straight into the flat gradient
+            if direct:
                 bias._b2_grad_ready = True
             else:
-                db = db_new
+                db = db_out
         return dx, dw, db, None
 
 

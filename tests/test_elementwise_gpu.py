@@ -170,3 +170,24 @@ def test_adamw_matches_torch_fused():
     st = opt.state[p_ref]
     _close(m, st["exp_avg"], 1e-5, 1e-2)
     _close(v, st["exp_avg_sq"], 1e-8, 1e-2)
+
+
+@pytest.mark.parametrize("T,N", [(8192, 2304), (1000, 776), (7, 8), (300, 50264)])
+def test_colsum_bias_gradient(T, N):
+    """b2_colsum (bias gradients) against an fp32 column sum, with a strided input and accumulation."""
+    from b200train import _C
+    from b200train.ops.linear import _colsum
+
+    g = torch.Generator(device="cuda").manual_seed(T + N)
+    wide = (torch.randn(T, N + 64, device="cuda", generator=g)).to(torch.bfloat16)
+    x = wide[:, :N]                       # row stride N + 64
+    out = torch.zeros(N, device="cuda", dtype=torch.bfloat16)
+    _colsum(x, out, False)
+    ref = x.float().sum(0)
+    tol = 2e-2 * max(1.0, ref.abs().max().item())
+    assert (out.float() - ref).abs().max().item() <= tol
+    base = torch.randn(N, device="cuda").to(torch.bfloat16)
+    out2 = base.clone()
+    _colsum(x, out2, True)
+    assert (out2.float() - (ref + base.float())).abs().max().item() <= tol
+    assert _C.launch_count() > 0
