@@ -25,7 +25,14 @@ def use_kernels(t: torch.Tensor) -> bool:
     return True
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def stream(t: torch.Tensor) -> int:
+    """cudaStream_t of the current stream on ``t``'s device. The raw accessor skips building a
+    ``torch.cuda.Stream`` object per kernel call (this function runs once per launch)."""
+    if _raw_stream is not None:
+        return _raw_stream(t.device.index if t.device.index is not None else torch.cuda.current_device())
     return torch.cuda.current_stream(t.device).cuda_stream
 
 
