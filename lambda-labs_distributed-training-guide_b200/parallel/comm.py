@@ -143,11 +143,22 @@ class TorchComm(Comm):
             dist.barrier(group=self.group)
 
 
+def _single_node(group) -> bool:
+    """True when every rank of ``group`` runs on this host: peer-mapped memory (and the NVSwitch
+    multicast) only spans one NVLink domain; groups that cross nodes use NCCL (or hybrid shard: peer
+    memory inside the node, NCCL across)."""
+    import socket
+
+    names = [None] * dist.get_world_size(group)
+    dist.all_gather_object(names, socket.gethostname(), group=group)
+    return len(set(names)) == 1
+
+
 def make_comm(group=None, prefer_peer: bool = True, device=None) -> Comm:
     if not dist.is_initialized():
         return Comm()
     if prefer_peer and device is not None and torch.device(device).type == "cuda" \
-            and os.environ.get("B200TRAIN_COMM", "peer") == "peer":
+            and os.environ.get("B200TRAIN_COMM", "peer") == "peer" and _single_node(group):
         try:
             from .peer import PeerComm
 
