@@ -293,3 +293,37 @@ def test_hybrid_shard_matches_single_process(tmp_path):
     got = run_dist("w_hsdp", str(tmp_path), world=4)[0]
     for a, b in zip(ref, got):
         assert abs(a - b) < 2e-3, (ref, got)
+
+
+def w_hsdp_variants(rank, world):
+    """Hybrid shard: CPU offload, activation checkpointing and no_sync accumulation follow the same curve."""
+    from b200train.models import load_config
+    from b200train.parallel import make_strategy
+
+    cfg = load_config("llama-tiny")
+    ids = _batches(cfg, 1, 4, 32)[0][rank:rank + 1]
+    out = {}
+    for name, kw in (("plain", {}), ("offload", dict(cpu_offload=True)), ("ckpt", dict(activation_checkpointing=True)),
+                     ("accum", {})):
+        eng = make_strategy("hsdp", cfg, "cpu", lr=1e-2, dtype=torch.float32, replicas=2, **kw)
+        ls = []
+        for _ in range(3):
+            if name == "accum":   # two identical half-weight micro-batches == one step
+                with eng.no_sync():
+                    eng.backward(eng.forward({"input_ids": ids, "labels": ids}).loss / 2)
+                o = eng.forward({"input_ids": ids, "labels": ids})
+                eng.backward(o.loss / 2)
+                eng.optimizer_step()
+                eng.zero_grad()
+                ls.append(o.loss.item())
+            else:
+                ls.append(eng.train_step({"input_ids": ids, "labels": ids}).item())
+        out[name] = ls
+    return out
+
+
+def test_hybrid_shard_variants_agree():
+    got = run_dist("w_hsdp_variants", world=4)[0]
+    for name in ("offload", "ckpt", "accum"):
+        for a, b in zip(got["plain"], got[name]):
+            assert abs(a - b) < 1e-4, got
