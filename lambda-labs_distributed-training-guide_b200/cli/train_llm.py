@@ -127,8 +127,17 @@ def main(chapter: str = "generic", argv=None):
         ds_cfg = json.loads(Path(args.deepspeed_config).read_text()) if args.deepspeed_config else {}
         args.batch_size = ds_cfg.get("train_micro_batch_size_per_gpu", 1)
         args.lr = ds_cfg.get("optimizer", {}).get("params", {}).get("lr", 3e-5)
-        args.cpu_offload = "on" if ds_cfg.get("zero_optimization", {}).get("offload_param", {}).get(
-            "device", "none") == "cpu" else "off"
+        zero = ds_cfg.get("zero_optimization", {})
+        args.cpu_offload = "on" if zero.get("offload_param", {}).get("device", "none") == "cpu" else "off"
+        # ZeRO stage -> sharding: 3 = parameters + gradients + optimizer state (full shard), 2 = gradients +
+        # optimizer state (parameters stay gathered), 1 = optimizer state only (DDP + ZeRO-1), 0 = plain DDP
+        stage = int(zero.get("stage", 3))
+        if args.strategy is None and stage < 3:
+            if stage == 2:
+                args.sharding_strategy = "shard_grad_op"
+            else:
+                strategy_name = "ddp"
+                args.zero1 = "on" if stage == 1 else "off"
         if args.local_rank is not None:
             os.environ.setdefault("LOCAL_RANK", str(args.local_rank))
     rank, local_rank, world_size, device = init_distributed(args.device)
