@@ -46,7 +46,7 @@ def test_rmsnorm(H, with_res):
     _close(w.grad, wr.grad, 0.3, 3e-2)
 
 
-@pytest.mark.parametrize("H", [768, 2048])
+@pytest.mark.parametrize("H", [256, 512, 768, 1024, 2048])
 def test_layernorm(H):
     from b200train.ops.norm import layernorm
 
