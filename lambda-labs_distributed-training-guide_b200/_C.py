@@ -84,12 +84,20 @@ def load():
     global _LIB
     if _LIB is not None:
         return _LIB
-    if not _LIB_PATH.exists():
-        if os.environ.get("B200TRAIN_NO_AUTOBUILD") == "1":
+    if os.environ.get("B200TRAIN_NO_AUTOBUILD") == "1":
+        if not _LIB_PATH.exists():
             raise KernelError(f"{_LIB_PATH} is missing; run `python -m b200train.build`")
+    else:
+        # digest-incremental: a no-op when csrc/ is unchanged, a rebuild when the library is missing or stale
+        # (the .so is git-ignored, so a tree can carry a library older than its sources). All ranks of a job
+        # reach this at once: the build itself is serialised by a file lock (see build.build).
         from . import build as _build
 
-        _build.build()
+        try:
+            _build.build()
+        except RuntimeError:
+            if not _LIB_PATH.exists():
+                raise
     try:
         lib = ctypes.CDLL(str(_LIB_PATH))
     except OSError as e:  # pragma: no cover - depends on the machine

@@ -58,9 +58,22 @@ def _src_digest(src: Path, headers) -> str:
 
 
 def build(force: bool = False, verbose: bool = False) -> Path:
-    """Compile every ``csrc/*.cu`` for sm_100a and link ``libb200train.so``. Incremental per file."""
+    """Compile every ``csrc/*.cu`` for sm_100a and link ``libb200train.so``. Incremental per file.
+    Concurrent callers (the ranks of one job) are serialised by an exclusive lock on ``_lib/.lock``; the
+    ones that waited find everything up to date."""
     LIB_DIR.mkdir(exist_ok=True)
     OBJ_DIR.mkdir(exist_ok=True)
+    import fcntl
+
+    with open(LIB_DIR / ".lock", "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            return _build_locked(force, verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(force: bool, verbose: bool) -> Path:
     nvcc = _nvcc()
     headers = sorted(CSRC.glob("*.cuh")) + sorted(INCLUDE.glob("*.h"))
     srcs = _sources()

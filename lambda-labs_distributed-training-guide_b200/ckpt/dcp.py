@@ -149,6 +149,9 @@ def load_sharded(exp_dir: Path, strategy):
             strategy.unit_store_named(i, kind, tensors)
     steps = [float(_to_full(st["step"])) for st in opt_state.values() if "step" in st]
     strategy.set_optimizer_step_count(int(steps[0]) if steps else 0)
+    # the hyper-parameters travel in the checkpoint too (the reference restores them through the DCP
+    # optimizer state: 04-fully-sharded-data-parallel/train_llm.py:132-154)
+    strategy.set_optimizer_param_groups(sharded["optimizer"]["param_groups"])
     strategy.barrier()
 
 

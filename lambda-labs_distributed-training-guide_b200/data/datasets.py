@@ -14,6 +14,7 @@ Dataset names:
 from __future__ import annotations
 
 import json
+import logging
 import multiprocessing
 import os
 from itertools import chain
@@ -36,6 +37,9 @@ class SyntheticTokens(Dataset):
         g = torch.Generator().manual_seed(self.seed * 1_000_003 + int(i))
         ids = torch.randint(0, self.vocab_size, (self.seq_length,), generator=g)
         return {"input_ids": ids, "attention_mask": torch.ones_like(ids), "labels": ids.clone()}
+
+
+LOGGER = logging.getLogger(__name__)
 
 
 class TokenBlocks(Dataset):
@@ -73,13 +77,27 @@ def resolve_seq_length(requested, tokenizer_max, max_position_embeddings):
     return seq_length
 
 
-def _load_tokenizer(model_name: str):
-    try:
-        from transformers import AutoTokenizer
+# built-in test presets have no tokenizer files anywhere; they (and an explicit opt-in) use the byte tokenizer
+_BYTE_TOKENIZER_MODELS = ("llama-tiny", "llama-smoke", "gpt2-tiny")
 
-        return AutoTokenizer.from_pretrained(model_name, local_files_only=not os.environ.get("HF_ALLOW_NETWORK"))
-    except Exception:
+
+def _load_tokenizer(model_name: str):
+    """HF tokenizer of ``model_name`` (hub id or local directory), failing loudly when it cannot be loaded,
+    as ``AutoTokenizer.from_pretrained`` does in the reference (``01-single-gpu/train_llm.py:199``).
+    The 257-symbol byte tokenizer is used only for the built-in tiny presets or with
+    ``B200TRAIN_BYTE_TOKENIZER=1``: silently training a 128k-vocabulary model on bytes is never wanted."""
+    if model_name in _BYTE_TOKENIZER_MODELS or os.environ.get("B200TRAIN_BYTE_TOKENIZER") == "1":
+        LOGGER.warning(f"using the offline byte-level tokenizer (vocab 257) for {model_name!r}")
         return ByteTokenizer()
+    from transformers import AutoTokenizer
+
+    try:
+        return AutoTokenizer.from_pretrained(model_name, local_files_only=not os.environ.get("HF_ALLOW_NETWORK"))
+    except Exception as e:
+        raise RuntimeError(
+            f"cannot load a tokenizer for {model_name!r} ({type(e).__name__}: {e}). Pass a local directory with "
+            "tokenizer files as --model-name, set HF_ALLOW_NETWORK=1 to fetch it from the hub, or set "
+            "B200TRAIN_BYTE_TOKENIZER=1 to train on raw bytes on purpose.") from e
 
 
 def _read_local_texts(path: Path):

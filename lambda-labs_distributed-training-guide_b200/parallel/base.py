@@ -104,6 +104,21 @@ class Strategy:
         g["betas"] = list(g["betas"])
         return [g]
 
+    def set_optimizer_param_groups(self, groups):
+        """Write checkpointed hyper-parameters (lr, betas, eps, weight_decay, initial_lr) back into the live
+        optimizer: torch LR schedulers continue recursively from ``param_groups[0]['lr']``, so a resume that
+        leaves the freshly constructed lr in place walks a different schedule."""
+        if not groups:
+            return
+        src = groups[0]
+        dst = self.optimizer.param_groups[0]
+        for k in ("lr", "betas", "eps", "weight_decay", "initial_lr"):
+            if k in src:
+                v = src[k]
+                if isinstance(v, torch.Tensor):
+                    v = v.item() if v.numel() == 1 else v.tolist()
+                dst[k] = tuple(v) if k == "betas" else float(v)
+
     def optimizer_step_count(self) -> int:
         return self.optimizer._step
 

@@ -145,6 +145,7 @@ class FSDP(Strategy):
         self._opt_events = {}     # unit -> event after a side-stream optimizer update of its shard
         self._local_acc = {}      # unit -> unreduced gradient accumulator (no_sync)
         self._stepped = set()     # units already updated inside this backward (fuse_optimizer)
+        self._began = False       # optimizer.begin_step() already called for the step in flight
         self.comm_stream = torch.cuda.Stream(self.device) if self.is_cuda else None
         # CPU offload: the host AdamW of a unit starts on a worker thread as soon as its gradient shard
         # has landed in pinned memory, overlapping the rest of backward (the reference steps after it)
@@ -324,8 +325,7 @@ class FSDP(Strategy):
             # one kernel: pull + reduce the peers' gradient slices and apply AdamW to the owned shard
             with self._on(self.comm_stream):
                 self._wait(ready, self.comm_stream)
-                if not self._stepped:
-                    self.optimizer.begin_step()
+                self._begin_once()
                 g = self.optimizer.param_groups[0]
                 if self.comm.reduce_scatter_adamw(self.shard_param[i], self.optimizer.exp_avg[i],
                                                   self.optimizer.exp_avg_sq[i], full, g["lr"], g["betas"][0],
@@ -354,8 +354,7 @@ class FSDP(Strategy):
             self._fused_step(i, done)
 
     def _submit_cpu_step(self, i, landed):
-        if not self._stepped and not self._cpu_jobs:
-            self.optimizer.begin_step()
+        self._begin_once()
         self._stepped.add(i)
 
         def job():
@@ -366,8 +365,7 @@ class FSDP(Strategy):
 
     def _fused_step(self, i, after_event):
         """Sharded AdamW for unit ``i`` on the side stream as soon as its gradient shard is final."""
-        if not self._stepped:
-            self.optimizer.begin_step()
+        self._begin_once()
         self._stepped.add(i)
         with self._on(self.comm_stream):
             self._wait(after_event, self.comm_stream)
@@ -375,6 +373,13 @@ class FSDP(Strategy):
                                      max_blocks=(_FUSED_ADAMW_BLOCKS if self.is_cuda else 0))
             if self.resident:
                 self._opt_events[i] = self._record(self.comm_stream)
+
+    def _begin_once(self):
+        """Advance the optimizer's step counter exactly once per optimizer step, whichever path (fused kernel,
+        side-stream AdamW, host AdamW, end-of-step sweep) reaches a unit first."""
+        if not self._began:
+            self.optimizer.begin_step()
+            self._began = True
 
     # ---- phases ---------------------------------------------------------------------------------------
     def forward(self, batch):
@@ -414,12 +419,12 @@ class FSDP(Strategy):
                 self.comm_stream.synchronize()   # gradient shards must have landed in host memory
             else:
                 torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
-        if not self._stepped:
-            self.optimizer.begin_step()
+        self._begin_once()
         for i in range(len(self.units)):
             if i not in self._stepped:
                 self.optimizer.step_unit(i, grad=self.shard_grad[i], param=self.shard_param[i])
         self._stepped.clear()
+        self._began = False
         self.lr_scheduler.step()
         if self.is_cuda:
             self.comm_stream.wait_stream(torch.cuda.current_stream(self.device))

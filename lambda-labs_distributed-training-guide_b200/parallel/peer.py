@@ -75,6 +75,7 @@ class PeerComm(TorchComm):
         self.nvls = mode == "1" or (mode == "auto" and self.world >= 4)
         # the switch saturates with few blocks in flight; fewer blocks leave more of the SMs to the GEMMs
         self.nvls_blocks = int(os.environ.get("B200TRAIN_NVLS_BLOCKS", "16"))
+        self.rs_blocks = int(os.environ.get("B200TRAIN_RS_BLOCKS", "64"))
         self.debug = os.environ.get("B200TRAIN_COMM_DEBUG", "0") == "1"
         self.debug_checks = 0
         pad = self.empty(64 * 16, torch.int32)   # signal pad: [channel][16 ranks]
@@ -188,7 +189,7 @@ class PeerComm(TorchComm):
             return
         _C.call("b2_peer_reduce_scatter", shard.data_ptr(), fulls, shard.numel(), self.rank, self.world,
                 (1.0 / self.world) if average else 1.0, self._pad_ptrs, CHAN_RS, self._epoch(CHAN_RS),
-                self._counter().data_ptr(), max_blocks or 64, self._stream())
+                self._counter().data_ptr(), max_blocks or self.rs_blocks, self._stream())
 
     def reduce_scatter_adamw(self, p, m, v, full_grad, lr, beta1, beta2, eps, wd, step, average=True,
                              max_blocks: int = 128, nvls: Optional[bool] = None) -> bool:

@@ -86,6 +86,27 @@ def test_resume_continues_identically(tmp_path):
         assert abs(x - y) < 1e-5, (la, lb)
 
 
+def test_sharded_resume_restores_learning_rate(tmp_path):
+    """DCP (sharded) resume: the optimizer's lr must come back from the checkpoint, otherwise the cosine
+    schedule (recursive in ``param_groups[0]['lr']``) continues from the constructor's value."""
+    from b200train.cli.train_llm import main
+
+    def args(name, extra):
+        return ["-e", name, "-d", "synthetic:32", "-m", "llama-tiny", "--save-dir", str(tmp_path), "--device", "cpu",
+                "-b", "2", "-s", "32", "--log-freq", "1", "--ckpt-freq", "4", "--num-epochs", "1", "--wandb-mode", "off",
+                "--lr", "1e-3"] + extra
+
+    main("04-fsdp", args("a", ["--max-steps", "6"]))
+    main("04-fsdp", args("b", ["--max-steps", "4"]))
+    main("04-fsdp", args("b", ["--max-steps", "2"]))
+    ra = [json.loads(l) for l in (tmp_path / "a" / "metrics.jsonl").read_text().splitlines()]
+    rb = [json.loads(l) for l in (tmp_path / "b" / "metrics.jsonl").read_text().splitlines()]
+    assert len(ra) == len(rb) == 6
+    for x, y in zip(ra, rb):
+        assert math.isclose(x["lr"], y["lr"], rel_tol=1e-9), ([r["lr"] for r in ra], [r["lr"] for r in rb])
+        assert abs(x["running_loss"] - y["running_loss"]) < 1e-5
+
+
 def test_packed_collator_positions_and_mask():
     from b200train.data import block_diagonal_causal_mask, cu_seqlens_from_positions, packed_positions, pad_and_collate
 
@@ -110,6 +131,24 @@ def test_group_texts_and_seq_length_clamp():
     assert resolve_seq_length(None, 2048, 4096) == 2048
     assert resolve_seq_length(8192, 2048, 4096) == 1024           # > max positions -> min(1024, max)
     assert resolve_seq_length(8192, 2048, 512) == 512
+
+
+def test_tokenizer_failure_is_loud(tmp_path, monkeypatch):
+    """A model name without tokenizer files must raise (as AutoTokenizer does in the reference), not fall
+    back to byte-level tokens; the byte tokenizer is for the tiny presets or an explicit opt-in."""
+    from b200train.data.datasets import ByteTokenizer, _load_tokenizer, load_and_preprocess_data
+    from b200train.models import load_config
+
+    monkeypatch.delenv("B200TRAIN_BYTE_TOKENIZER", raising=False)
+    with pytest.raises(RuntimeError, match="cannot load a tokenizer"):
+        _load_tokenizer(str(tmp_path / "no-such-model"))
+    assert isinstance(_load_tokenizer("llama-tiny"), ByteTokenizer)
+    monkeypatch.setenv("B200TRAIN_BYTE_TOKENIZER", "1")
+    assert isinstance(_load_tokenizer(str(tmp_path / "no-such-model")), ByteTokenizer)
+    text = tmp_path / "corpus.txt"
+    text.write_text("hello world " * 200)
+    ds = load_and_preprocess_data(str(text), "llama-tiny", load_config("llama-tiny"), seq_length=32)
+    assert len(ds) > 0 and ds[0]["input_ids"].shape == (32,)
 
 
 def test_local_timer_cpu_branch_and_mem_stats():

@@ -119,6 +119,28 @@ def test_fsdp_no_sync_accumulation():
     assert abs(la - lb) < 2e-3, (la, lb)
 
 
+def w_fused_step_count(rank, world):
+    from b200train.models import load_config
+    from b200train.parallel import make_strategy
+
+    cfg = load_config("llama-tiny")
+    out = []
+    for fuse in (True, "kernel", "stream"):
+        # the gloo communicator has no reduce-scatter + AdamW kernel: the request falls back to a separate update
+        eng = make_strategy("fsdp", cfg, "cpu", lr=1e-3, dtype=torch.float32, fuse_optimizer=fuse)
+        ids = _batches(cfg, 1, 4, 32)[0][rank * 2:(rank + 1) * 2]
+        for _ in range(3):
+            eng.train_step({"input_ids": ids, "labels": ids})
+        out.append(eng.optimizer._step)
+    return out
+
+
+def test_fused_optimizer_fallback_counts_each_step_once():
+    """`fuse_optimizer` on a communicator without the fused kernel must not advance AdamW's step counter
+    twice per step (bias correction and the checkpointed `step` depend on it)."""
+    assert run_dist("w_fused_step_count")[0] == [3, 3, 3]
+
+
 def w_dcp(rank, world, tmp):
     if True:
         from pathlib import Path

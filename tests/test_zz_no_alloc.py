@@ -24,6 +24,7 @@ pytestmark = pytest.mark.gpu
 def _lib():
     from b200train import _C
 
+    _C.load()   # builds the library first when it is missing or older than csrc/ (fresh checkout, stale .so)
     lib = ctypes.CDLL(str(_C.lib_path()))
     P = c_void_p
     lib.b2_rmsnorm_bwd_static.argtypes = [P, P, P, P, P, P, P, c_int, c_int, c_int, P]
