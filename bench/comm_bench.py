@@ -58,7 +58,7 @@ def main():
     res["nccl_ag_ms"] = timed(lambda: dist.all_gather_into_tensor(full, shard))
     res["nccl_rs_ms"] = timed(lambda: dist.reduce_scatter_tensor(out_shard, full_sym, op=dist.ReduceOp.AVG))
     res["peer_ag_ce_ms"] = timed(lambda: comm.all_gather(full, shard, copy_engine=True))
-    for mb in (16, 32, 64, 128):
+    for mb in (32, 64, 128, 148, 296):
         res[f"peer_ag_ms_b{mb}"] = timed(lambda: comm.all_gather(full, shard, max_blocks=mb, copy_engine=False))
         res[f"peer_rs_ms_b{mb}"] = timed(lambda: comm.reduce_scatter(out_shard, full_sym, max_blocks=mb, nvls=False))
         res[f"peer_rs_adamw_ms_b{mb}"] = timed(
@@ -70,7 +70,7 @@ def main():
         ar_buf.normal_()
         res["nccl_ar_ms"] = timed(lambda: dist.all_reduce(ar_buf, op=dist.ReduceOp.AVG))
         res["peer_ar_ms_b64"] = timed(lambda: comm.all_reduce(ar_buf, max_blocks=64, nvls=False))
-        for mb in (16, 32, 64, 128):
+        for mb in (16, 32, 64, 148):
             res[f"nvls_rs_ms_b{mb}"] = timed(lambda: comm.reduce_scatter(out_shard, full_sym, max_blocks=mb, nvls=True))
             res[f"nvls_rs_adamw_ms_b{mb}"] = timed(lambda: comm.reduce_scatter_adamw(
                 p, m, v, full_sym, 1e-4, 0.9, 0.999, 1e-8, 0.01, 3, max_blocks=mb, nvls=True))
@@ -108,7 +108,11 @@ def main():
             res[f"gemm+peer_agce_nvls_rs_ms_b{mb}"] = timed(overlapped(
                 lambda: (comm.all_gather(full, shard, copy_engine=True),
                          comm.reduce_scatter(out_shard, full_sym, max_blocks=mb, nvls=True))))
-    for mb in (32, 64, 128):
+    for mb in (32, 148, 296):
+        res[f"gemm+peer_agce_rsadamw_ms_b{mb}"] = timed(overlapped(
+            lambda: (comm.all_gather(full, shard, copy_engine=True),
+                     comm.reduce_scatter_adamw(p, m, v, full_sym, 1e-4, 0.9, 0.999, 1e-8, 0.01, 3, max_blocks=mb))))
+    for mb in (64, 128):
         res[f"gemm+peer_ag_rs_ms_b{mb}"] = timed(overlapped(lambda: (comm.all_gather(full, shard, max_blocks=mb, copy_engine=False),
                                                                      comm.reduce_scatter(out_shard, full_sym,
                                                                                          max_blocks=mb, nvls=False))))

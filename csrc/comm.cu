@@ -19,6 +19,7 @@
 // / ZeroRedundancyOptimizer (02-distributed-data-parallel/train_llm.py:65,81-83,
 // 04-fully-sharded-data-parallel/train_llm.py:87-95) and the separate optimizer.step() at :213.
 #include "common.cuh"
+#include <cstdio>
 
 namespace b2 {
 
@@ -70,11 +71,38 @@ __device__ __forceinline__ void signal_peers(const PeerPtrs& pads, int rank, int
     st_flag_sys(pad + channel * kMaxPeers + rank, epoch);
   }
 }
+// A peer that died (or never launched its half of the collective) would leave this spin running for
+// ever, as an unkillable kernel with no diagnostic. The wait is therefore bounded: after
+// g_spin_timeout_ns (default 120 s, b2_comm_set_timeout_ms) the waiting thread prints who it is waiting
+// for and traps, which surfaces on the host as a launch failure of this rank.
+__device__ unsigned long long g_spin_timeout_ns = 120ull * 1000ull * 1000ull * 1000ull;
+
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+__device__ __noinline__ void spin_timeout_trap(int rank, int peer, int channel, uint32_t epoch,
+                                               uint32_t seen) {
+  printf("b200train comm: rank %d timed out waiting for rank %d on channel %d (epoch %u, last seen %u)\n",
+         rank, peer, channel, epoch, seen);
+  __trap();
+}
+
 __device__ __forceinline__ void wait_peers(const PeerPtrs& pads, int rank, int W, int channel,
                                            uint32_t epoch) {
   if (threadIdx.x < W) {
     const uint32_t* pad = static_cast<const uint32_t*>(pads.p[rank]);
-    while ((int32_t)(ld_flag_sys(pad + channel * kMaxPeers + threadIdx.x) - epoch) < 0) {
+    uint32_t seen = ld_flag_sys(pad + channel * kMaxPeers + threadIdx.x);
+    if ((int32_t)(seen - epoch) < 0) {
+      const unsigned long long t0 = global_timer_ns();
+      uint32_t polls = 0;
+      do {
+        seen = ld_flag_sys(pad + channel * kMaxPeers + threadIdx.x);
+        if ((++polls & 0x3ff) == 0 && global_timer_ns() - t0 > g_spin_timeout_ns)
+          spin_timeout_trap(rank, (int)threadIdx.x, channel, epoch, seen);
+      } while ((int32_t)(seen - epoch) < 0);
     }
   }
   __syncthreads();
@@ -399,6 +427,115 @@ nvls_all_reduce_kernel(V4* __restrict__ mc, size_t n16_slice, int rank, int W, f
   }
 }
 
+
+// ---- local shard copy ---------------------------------------------------------------------------------
+// The FSDP gather also places the rank's own shard into the full buffer. A cudaMemcpyAsync for that
+// local device-to-device copy holds back every kernel launch of the other streams for its whole
+// duration (measured: the next GEMM of the compute stream starts when the 218 MB copy ends, 75 us per
+// unit at 2 ranks); a few copy blocks beside the GEMM CTAs do not.
+__global__ void __launch_bounds__(kCommThreads, 3)
+local_copy_kernel(V4* __restrict__ dst, const V4* __restrict__ src, size_t n16) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + 7 * stride < n16; i += 8 * stride) {
+    V4 t[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) t[u] = ld_peer(src + i + u * stride);
+#pragma unroll
+    for (int u = 0; u < 8; ++u) dst[i + u * stride] = t[u];
+  }
+  for (; i < n16; i += stride) dst[i] = ld_peer(src + i);
+}
+
+// ---- software-pipelined reduce-scatter (+ AdamW) ------------------------------------------------------
+// Per 16-byte output vector there is ONE long-latency fetch -- the peer's copy of the slice at 2 ranks,
+// or an in-switch multimem.ld_reduce over all ranks (NVLS) -- and up to four short-latency local ones
+// (own gradient slice, p, m, v). The long fetch runs D trips ahead in a register ring, the local loads
+// are issued just in time, so an NVLink round trip (2-4 us) no longer gates the HBM traffic (~1 us) and
+// the kernel needs neither many blocks nor many registers to keep both busy. 256 threads x <= 85
+// registers: one such block fits beside a resident GEMM CTA on every SM.
+__device__ __forceinline__ V4 ld_local(const V4* ptr) {
+  V4 r;
+  asm volatile("ld.global.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.u[0]), "=r"(r.u[1]), "=r"(r.u[2]), "=r"(r.u[3])
+               : "l"(ptr));
+  return r;
+}
+
+template <bool kAdam, bool kNvls, int U, int D>
+__global__ void __launch_bounds__(kCommThreads, 3)
+rs_pipe_kernel(V4* __restrict__ out_shard, const V4* __restrict__ remote, const V4* __restrict__ local,
+               size_t n16, int rank, int W, float scale, PeerPtrs pads, int chan_base, uint32_t epoch,
+               unsigned int* counter, AdamArgs adam) {
+  if (blockIdx.x == 0) {
+    __threadfence_system();
+    signal_peers(pads, rank, W, chan_base + kChanIn, epoch);
+  }
+  wait_peers(pads, rank, W, chan_base + kChanIn, epoch);
+
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  const size_t lane0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t trips = (n16 + U * stride - 1) / (U * stride);
+  auto index = [&](size_t t, int u) { return (t * U + u) * stride + lane0; };
+  auto fetch = [&](size_t i) {
+    if constexpr (kNvls) return multimem_ld_reduce_bf16x8(remote + i);
+    else return ld_peer_coherent(remote + i);
+  };
+  V4 ring[D][U];
+#pragma unroll
+  for (int d = 0; d < D; ++d)
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = index(d, u);
+      if (d < trips && i < n16) ring[d][u] = fetch(i);
+    }
+  for (size_t t0 = 0; t0 < trips; t0 += D) {
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+      const size_t t = t0 + d;
+      if (t >= trips) break;
+      V4 gl[U], pv[U], mv[U], vv[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const size_t i = index(t, u);
+        if (i < n16) {
+          if constexpr (!kNvls) gl[u] = ld_local(local + i);
+          if constexpr (kAdam) {
+            pv[u] = ld_local(reinterpret_cast<const V4*>(adam.p) + i);
+            mv[u] = ld_local(reinterpret_cast<const V4*>(adam.m) + i);
+            vv[u] = ld_local(reinterpret_cast<const V4*>(adam.v) + i);
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const size_t i = index(t, u);
+        if (i < n16) {
+          float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+          acc_bf16x8(acc, ring[d][u]);
+          if constexpr (!kNvls) acc_bf16x8(acc, gl[u]);
+          rs_finish<kAdam>(acc, i, scale, out_shard, adam, pv[u], mv[u], vv[u]);
+        }
+        const size_t inext = index(t + D, u);
+        if (t + D < trips && inext < n16) ring[d][u] = fetch(inext);
+      }
+    }
+  }
+  if (last_block_done(counter)) {  // every rank has finished reading: the full buffers may be reused
+    __threadfence_system();
+    signal_peers(pads, rank, W, chan_base + kChanOut, epoch);
+    wait_peers(pads, rank, W, chan_base + kChanOut, epoch);
+  }
+}
+
+static bool rs_pipe_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("B200TRAIN_RS_PIPE");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
+
 static int clamp_blocks(size_t work16, int max_blocks) {
   size_t b = (work16 + kCommThreads - 1) / kCommThreads;
   int cap = max_blocks > 0 ? max_blocks : 64;
@@ -442,15 +579,33 @@ int b2_peer_all_gather(void* dst, void* const* srcs, size_t shard_bytes, int ran
 
 // Same gather driven by the copy engines: one cudaMemcpyAsync per peer from the mapped peer pointer
 // (DMA over NVLink, no SM time). The source shards must already be final (see b2_peer_barrier).
+// The rank's own shard is placed by `self_blocks` copy blocks (see local_copy_kernel; 0 = cudaMemcpyAsync).
 int b2_peer_all_gather_ce(void* dst, void* const* srcs, size_t shard_bytes, int rank, int W,
-                          int skip_self, cudaStream_t stream) {
+                          int skip_self, int self_blocks, cudaStream_t stream) {
   B2_REQUIRE(W >= 1 && W <= kMaxPeers, "peer collectives support up to %d ranks (got %d)", kMaxPeers, W);
   for (int k = 0; k < W; ++k) {
     const int peer = (rank + k) % W;
     if (peer == rank && skip_self) continue;
-    B2_CUDA_CHECK(cudaMemcpyAsync(static_cast<char*>(dst) + (size_t)peer * shard_bytes, srcs[peer],
-                                  shard_bytes, cudaMemcpyDeviceToDevice, stream));
+    char* d = static_cast<char*>(dst) + (size_t)peer * shard_bytes;
+    if (peer == rank && self_blocks > 0 && shard_bytes % 16 == 0 &&
+        (reinterpret_cast<uintptr_t>(d) & 15) == 0 && (reinterpret_cast<uintptr_t>(srcs[peer]) & 15) == 0) {
+      const size_t n16 = shard_bytes / 16;
+      if (n16 > 0) {
+        local_copy_kernel<<<clamp_blocks(n16, self_blocks), kCommThreads, 0, stream>>>(
+            reinterpret_cast<V4*>(d), static_cast<const V4*>(srcs[peer]), n16);
+        B2_CUDA_CHECK(cudaGetLastError());
+      }
+      continue;
+    }
+    B2_CUDA_CHECK(cudaMemcpyAsync(d, srcs[peer], shard_bytes, cudaMemcpyDeviceToDevice, stream));
   }
+  return 0;
+}
+
+// Spin bound of every cross-rank wait in this file (milliseconds; applies to the current device).
+int b2_comm_set_timeout_ms(unsigned long long ms) {
+  const unsigned long long ns = ms * 1000000ull;
+  B2_CUDA_CHECK(cudaMemcpyToSymbol(g_spin_timeout_ns, &ns, sizeof(ns)));
   return 0;
 }
 
@@ -463,6 +618,14 @@ int b2_peer_reduce_scatter(void* out_shard, void* const* fulls, size_t shard_ele
   B2_REQUIRE(shard_elems % 8 == 0, "reduce_scatter: shard of %zu elements is not a multiple of 8", shard_elems);
   const size_t n16 = shard_elems / 8;
   AdamArgs none = {};
+  if (W == 2 && rs_pipe_enabled()) {
+    rs_pipe_kernel<false, false, 4, 2><<<clamp_blocks(n16, max_blocks), kCommThreads, 0, stream>>>(
+        static_cast<V4*>(out_shard), static_cast<const V4*>(fulls[1 - rank]) + (size_t)rank * n16,
+        static_cast<const V4*>(fulls[rank]) + (size_t)rank * n16, n16, rank, W, scale, to_ptrs(pads, W),
+        chan_base, epoch, counter, none);
+    B2_CUDA_CHECK(cudaGetLastError());
+    return 0;
+  }
   return launch_rs<false>(W, clamp_blocks(n16, max_blocks), stream, static_cast<V4*>(out_shard),
                           to_ptrs(fulls, W), n16, rank, scale, to_ptrs(pads, W), chan_base, epoch,
                           counter, none);
@@ -487,6 +650,14 @@ int b2_peer_reduce_scatter_adamw(void* p, void* m, void* v, void* const* fulls, 
   a.eps = eps;
   a.step_size = lr / (1.f - powf(beta1, (float)step));
   a.inv_bc2_sqrt = 1.f / sqrtf(1.f - powf(beta2, (float)step));
+  if (W == 2 && rs_pipe_enabled()) {
+    rs_pipe_kernel<true, false, 2, 3><<<clamp_blocks(n16, max_blocks), kCommThreads, 0, stream>>>(
+        nullptr, static_cast<const V4*>(fulls[1 - rank]) + (size_t)rank * n16,
+        static_cast<const V4*>(fulls[rank]) + (size_t)rank * n16, n16, rank, W, grad_scale,
+        to_ptrs(pads, W), chan_base, epoch, counter, a);
+    B2_CUDA_CHECK(cudaGetLastError());
+    return 0;
+  }
   return launch_rs<true>(W, clamp_blocks(n16, max_blocks), stream, nullptr, to_ptrs(fulls, W), n16,
                          rank, grad_scale, to_ptrs(pads, W), chan_base, epoch, counter, a);
 }
@@ -514,9 +685,14 @@ int b2_nvls_reduce_scatter(void* out_shard, const void* mc_full, size_t shard_el
   B2_REQUIRE(shard_elems % 8 == 0, "reduce_scatter: shard of %zu elements is not a multiple of 8", shard_elems);
   const size_t n16 = shard_elems / 8;
   AdamArgs none = {};
-  nvls_reduce_scatter_kernel<false><<<clamp_blocks(n16, max_blocks), kCommThreads, 0, stream>>>(
-      static_cast<V4*>(out_shard), static_cast<const V4*>(mc_full), n16, rank, W, scale,
-      to_ptrs(pads, W), chan_base, epoch, counter, none);
+  if (rs_pipe_enabled())
+    rs_pipe_kernel<false, true, 4, 3><<<clamp_blocks(n16, max_blocks), kCommThreads, 0, stream>>>(
+        static_cast<V4*>(out_shard), static_cast<const V4*>(mc_full) + (size_t)rank * n16, nullptr, n16,
+        rank, W, scale, to_ptrs(pads, W), chan_base, epoch, counter, none);
+  else
+    nvls_reduce_scatter_kernel<false><<<clamp_blocks(n16, max_blocks), kCommThreads, 0, stream>>>(
+        static_cast<V4*>(out_shard), static_cast<const V4*>(mc_full), n16, rank, W, scale,
+        to_ptrs(pads, W), chan_base, epoch, counter, none);
   B2_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
@@ -540,9 +716,14 @@ int b2_nvls_reduce_scatter_adamw(void* p, void* m, void* v, const void* mc_full,
   a.eps = eps;
   a.step_size = lr / (1.f - powf(beta1, (float)step));
   a.inv_bc2_sqrt = 1.f / sqrtf(1.f - powf(beta2, (float)step));
-  nvls_reduce_scatter_kernel<true><<<clamp_blocks(n16, max_blocks), kCommThreads, 0, stream>>>(
-      nullptr, static_cast<const V4*>(mc_full), n16, rank, W, grad_scale, to_ptrs(pads, W), chan_base,
-      epoch, counter, a);
+  if (rs_pipe_enabled())
+    rs_pipe_kernel<true, true, 2, 4><<<clamp_blocks(n16, max_blocks), kCommThreads, 0, stream>>>(
+        nullptr, static_cast<const V4*>(mc_full) + (size_t)rank * n16, nullptr, n16, rank, W, grad_scale,
+        to_ptrs(pads, W), chan_base, epoch, counter, a);
+  else
+    nvls_reduce_scatter_kernel<true><<<clamp_blocks(n16, max_blocks), kCommThreads, 0, stream>>>(
+        nullptr, static_cast<const V4*>(mc_full), n16, rank, W, grad_scale, to_ptrs(pads, W), chan_base,
+        epoch, counter, a);
   B2_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

@@ -135,8 +135,12 @@ int b2_peer_barrier(void* const* pads, int rank, int W, int channel, unsigned in
                     b2_stream_t stream);
 int b2_peer_all_gather(void* dst, void* const* srcs, size_t shard_bytes, int rank, int W,
                        int skip_self, int max_blocks, b2_stream_t stream);
+/* copy-engine gather; the rank's own shard is placed by `self_blocks` copy blocks (0: cudaMemcpyAsync) */
 int b2_peer_all_gather_ce(void* dst, void* const* srcs, size_t shard_bytes, int rank, int W,
-                          int skip_self, b2_stream_t stream);
+                          int skip_self, int self_blocks, b2_stream_t stream);
+/* bound (ms) of every cross-rank spin wait on the current device; past it the waiting kernel reports the
+ * rank / channel / epoch it is stuck on and traps (a dead peer becomes a launch failure, not a hang) */
+int b2_comm_set_timeout_ms(unsigned long long ms);
 int b2_peer_reduce_scatter(void* out_shard, void* const* fulls, size_t shard_elems, int rank, int W,
                            float scale, void* const* pads, int chan_base, unsigned int epoch,
                            unsigned int* counter, int max_blocks, b2_stream_t stream);

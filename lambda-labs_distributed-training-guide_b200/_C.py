@@ -61,7 +61,8 @@ def _declare(lib):
         "b2_cpu_adamw_bf16": [P, P, P, P, Z, F, F, F, F, F, I, F],
         "b2_peer_barrier": [P, I, I, I, ctypes.c_uint, P],
         "b2_peer_all_gather": [P, P, Z, I, I, I, I, P],
-        "b2_peer_all_gather_ce": [P, P, Z, I, I, I, P],
+        "b2_peer_all_gather_ce": [P, P, Z, I, I, I, I, P],
+        "b2_comm_set_timeout_ms": [ctypes.c_ulonglong],
         "b2_peer_reduce_scatter": [P, P, Z, I, I, F, P, I, ctypes.c_uint, P, I, P],
         "b2_peer_reduce_scatter_adamw": [P, P, P, P, Z, I, I, F, F, F, F, F, F, I, P, I, ctypes.c_uint, P, I, P],
         "b2_peer_all_reduce": [P, Z, I, I, F, P, I, ctypes.c_uint, P, I, P],

@@ -146,7 +146,10 @@ class FSDP(Strategy):
         self._local_acc = {}      # unit -> unreduced gradient accumulator (no_sync)
         self._stepped = set()     # units already updated inside this backward (fuse_optimizer)
         self._began = False       # optimizer.begin_step() already called for the step in flight
+        # two side streams: parameter gathers (copy engines) must not queue behind a unit's reduce-scatter and
+        # optimizer update, or the prefetch of the next unit starts late
         self.comm_stream = torch.cuda.Stream(self.device) if self.is_cuda else None
+        self.ag_stream = torch.cuda.Stream(self.device) if self.is_cuda else None
         # CPU offload: the host AdamW of a unit starts on a worker thread as soon as its gradient shard
         # has landed in pinned memory, overlapping the rest of backward (the reference steps after it)
         self._cpu_worker = None
@@ -225,8 +228,8 @@ class FSDP(Strategy):
         slot, buf, free_ev = self.param_pool.acquire(i)
         full = buf[:u.numel]
         n = u.numel // self.W
-        with self._on(self.comm_stream):
-            self._wait(free_ev, self.comm_stream)
+        with self._on(self.ag_stream):
+            self._wait(free_ev, self.ag_stream)
             if self.cpu_offload:
                 src = full[self.R * n:(self.R + 1) * n]
                 src.copy_(self.shard_param[i], non_blocking=True)   # pinned H2D on the side stream
@@ -234,7 +237,7 @@ class FSDP(Strategy):
                 src = self.shard_param[i]
             if self.W > 1:
                 self.comm.all_gather(full, src)
-            ev = self._record(self.comm_stream)
+            ev = self._record(self.ag_stream)
         self._gathered[i] = (slot, ev, full)
 
     def _ensure(self, i: int):
@@ -387,6 +390,7 @@ class FSDP(Strategy):
             # every rank's parameter shards are final (optimizer of the previous step) before any pull
             with self._on(self.comm_stream):
                 self.comm.stream_barrier()
+                self._wait(self._record(self.comm_stream), self.ag_stream)
         return self.model(**batch)
 
     def backward(self, loss):

@@ -76,6 +76,13 @@ class PeerComm(TorchComm):
         # the switch saturates with few blocks in flight; fewer blocks leave more of the SMs to the GEMMs
         self.nvls_blocks = int(os.environ.get("B200TRAIN_NVLS_BLOCKS", "16"))
         self.rs_blocks = int(os.environ.get("B200TRAIN_RS_BLOCKS", "64"))
+        # blocks of the fused reduce-scatter + AdamW kernel: wide at 2 ranks (the peer slice is half the unit and
+        # the update is HBM bound), thin through the switch (each rank's NVLink egress bounds it anyway)
+        self.rsadam_blocks = int(os.environ.get("B200TRAIN_RSADAM_BLOCKS", "0"))
+        # the own shard of an all-gather is placed by this many copy blocks (0: cudaMemcpyAsync, which holds
+        # back the kernel launches of every other stream while it runs)
+        self.self_copy_blocks = int(os.environ.get("B200TRAIN_SELF_COPY_BLOCKS", "16"))
+        self.rs_blocks = int(os.environ.get("B200TRAIN_RS_BLOCKS", "64"))
         self.debug = os.environ.get("B200TRAIN_COMM_DEBUG", "0") == "1"
         self.debug_checks = 0
         pad = self.empty(64 * 16, torch.int32)   # signal pad: [channel][16 ranks]
@@ -158,7 +165,7 @@ class PeerComm(TorchComm):
         skip_self = int(full.data_ptr() + self.rank * n == shard.data_ptr())
         if self.copy_engine if copy_engine is None else copy_engine:
             _C.call("b2_peer_all_gather_ce", full.data_ptr(), srcs, n, self.rank, self.world, skip_self,
-                    self._stream())
+                    self.self_copy_blocks, self._stream())
             return
         _C.call("b2_peer_all_gather", full.data_ptr(), srcs, n, self.rank, self.world, skip_self, max_blocks,
                 self._stream())
@@ -172,7 +179,7 @@ class PeerComm(TorchComm):
         n = full.numel() // self.world * full.element_size()
         srcs = (ctypes.c_void_p * self.world)(*[bases[q] + q * n for q in range(self.world)])
         if self.copy_engine:
-            _C.call("b2_peer_all_gather_ce", full.data_ptr(), srcs, n, self.rank, self.world, 1, self._stream())
+            _C.call("b2_peer_all_gather_ce", full.data_ptr(), srcs, n, self.rank, self.world, 1, 0, self._stream())
         else:
             _C.call("b2_peer_all_gather", full.data_ptr(), srcs, n, self.rank, self.world, 1, max_blocks,
                     self._stream())
@@ -192,13 +199,14 @@ class PeerComm(TorchComm):
                 self._counter().data_ptr(), max_blocks or self.rs_blocks, self._stream())
 
     def reduce_scatter_adamw(self, p, m, v, full_grad, lr, beta1, beta2, eps, wd, step, average=True,
-                             max_blocks: int = 128, nvls: Optional[bool] = None) -> bool:
+                             max_blocks: int = 0, nvls: Optional[bool] = None) -> bool:
         """Fused gradient reduce-scatter + AdamW on the owned shard. Returns False when the buffers are not
         eligible (caller then runs the two steps separately)."""
         fulls = self._peer_array(full_grad) if self.world > 1 else None
         if fulls is None or p.dtype != torch.bfloat16:
             return False
         mc = self._mc_ptr(full_grad) if (self.nvls if nvls is None else nvls) else 0
+        max_blocks = max_blocks or self.rsadam_blocks or (32 if mc else 148)
         if mc:
             _C.call("b2_nvls_reduce_scatter_adamw", p.data_ptr(), m.data_ptr(), v.data_ptr(), mc, p.numel(),
                     self.rank, self.world, (1.0 / self.world) if average else 1.0, lr, beta1, beta2, eps, wd,
