@@ -602,6 +602,21 @@ int b2_peer_all_gather_ce(void* dst, void* const* srcs, size_t shard_bytes, int 
   return 0;
 }
 
+// dst[0 .. bytes) = src on `blocks` copy blocks (0 or unaligned: cudaMemcpyAsync).
+int b2_local_copy(void* dst, const void* src, size_t bytes, int blocks, cudaStream_t stream) {
+  if (bytes == 0) return 0;
+  if (blocks > 0 && bytes % 16 == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0 &&
+      (reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+    const size_t n16 = bytes / 16;
+    local_copy_kernel<<<clamp_blocks(n16, blocks), kCommThreads, 0, stream>>>(
+        static_cast<V4*>(dst), static_cast<const V4*>(src), n16);
+    B2_CUDA_CHECK(cudaGetLastError());
+    return 0;
+  }
+  B2_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, stream));
+  return 0;
+}
+
 // Spin bound of every cross-rank wait in this file (milliseconds; applies to the current device).
 int b2_comm_set_timeout_ms(unsigned long long ms) {
   const unsigned long long ns = ms * 1000000ull;

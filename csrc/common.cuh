@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
+#include <cstdio>
 
 namespace b2 {
 
@@ -63,6 +64,33 @@ __device__ __forceinline__ void cluster_wait_acquire() {
 __device__ __forceinline__ void cluster_sync_all() {
   cluster_arrive_release();
   cluster_wait_acquire();
+}
+
+// ----------------------------------------------------------------------------------------------
+// arrival flags in global memory (written by a stream memory operation or by another GPU)
+// ----------------------------------------------------------------------------------------------
+static __device__ __noinline__ void flag_timeout_trap(const uint32_t* flag, uint32_t want, uint32_t seen) {
+  printf("b200train: block %d timed out waiting for flag %p >= %u (last seen %u)\n", (int)blockIdx.x,
+         (const void*)flag, want, seen);
+  __trap();
+}
+// Spin until *flag >= epoch (wrap-safe). timeout_ns == 0: wait for ever.
+__device__ __forceinline__ void wait_flag_geq(const uint32_t* flag, uint32_t epoch,
+                                              unsigned long long timeout_ns) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+  if ((int32_t)(v - epoch) >= 0) return;
+  unsigned long long t0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  uint32_t polls = 0;
+  do {
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+    if (timeout_ns != 0 && (++polls & 0xff) == 0) {
+      unsigned long long t1;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+      if (t1 - t0 > timeout_ns) flag_timeout_trap(flag, epoch, v);
+    }
+  } while ((int32_t)(v - epoch) < 0);
 }
 
 // ----------------------------------------------------------------------------------------------

@@ -56,7 +56,24 @@ struct FuseScatterC {
   CUtensorMap cm[kMaxTP];  // cm[r]: rank r's slot `rank`, shape [rows_per_rank, N]
   int rows_per_rank, rank, W;
 };
+// kFuse = 3 (FSDP parameter all-gather -> GEMM): the weight (B operand) is a slice of a flat unit buffer
+//   that the copy engines are still filling from the peers' shards, chunk by chunk, while the kernel
+//   runs; chunk c is present once flags[c] >= epoch (the gathering stream writes the flag after the
+//   chunk's copy). The TMA producer waits for the chunks that hold a tile's weight rows before the
+//   tile's first load, and the n-blocks are visited starting with the rows that arrive first (the
+//   rank's own shard, then the peers in the order they are pulled). All loads are from local memory.
+struct FuseBWait {
+  const uint32_t* flags;
+  uint32_t epoch;
+  long long b_off;        // element offset of B[0][0] in the flat buffer the flags describe
+  long long chunk_elems;  // elements per flag
+  int n_chunks;
+  int nb_start;           // first n-block to visit
+  int ldb;
+  unsigned long long timeout_ns;
+};
 template <class F> struct FuseKind { static constexpr int v = 0; };
+template <> struct FuseKind<FuseBWait> { static constexpr int v = 3; };
 template <> struct FuseKind<FuseAWait> { static constexpr int v = 1; };
 template <> struct FuseKind<FuseScatterC> { static constexpr int v = 2; };
 
@@ -164,6 +181,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int blocks_per_rank = fuse.rows_per_rank / (BM * kCta);
       mb = (mb + fuse.rank * blocks_per_rank) % num_m;
     }
+    if constexpr (kFuse == 3) {
+      nb += fuse.nb_start;
+      if (nb >= num_n) nb -= num_n;
+    }
   };
 
   if (warp == 0) {
@@ -171,6 +192,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
+      unsigned long long known = 0;  // kFuse == 3: chunks already seen present
       for (int u = worker; u < num_units; u += num_workers) {
         int t, n_off, bn_cur, mb, nb;
         unit_tile(u, t, n_off, bn_cur);
@@ -183,14 +205,34 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           // rows of this m-block come from rank `owner`: wait until its chunk has landed
           const int owner = min(m0 / fuse.rows_per_rank, fuse.W - 1);
           if (owner != fuse.rank) {
-            uint32_t v;
-            do {
-              asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(fuse.flags + owner)
-                           : "memory");
-            } while ((int32_t)(v - fuse.epoch) < 0);
+            wait_flag_geq(fuse.flags + owner, fuse.epoch, 0);
             // the chunk was written by the copy engine: order it before the async-proxy (TMA) reads
             asm volatile("fence.proxy.async.global;" ::: "memory");
           }
+        }
+        if constexpr (kFuse == 3) {
+          // flat range of the weight rows this CTA loads for the tile (K-major: rows n0.. of length
+          // ldb; MN-major: the tile's columns run through every row, i.e. the whole matrix)
+          long long lo, hi;
+          if constexpr (kBK) {
+            lo = fuse.b_off + (long long)n0 * fuse.ldb;
+            hi = fuse.b_off + (long long)(min(n0 + bn_cur / kCta, N) - 1) * fuse.ldb + K;
+          } else {
+            lo = fuse.b_off;
+            hi = fuse.b_off + (long long)(K - 1) * fuse.ldb + N;
+          }
+          int c_lo = (int)(lo / fuse.chunk_elems);
+          int c_hi = (int)((hi - 1) / fuse.chunk_elems);
+          if (c_hi > fuse.n_chunks - 1) c_hi = fuse.n_chunks - 1;
+          bool waited = false;
+          for (int c = c_lo; c <= c_hi; ++c) {
+            if (!((known >> c) & 1ull)) {
+              wait_flag_geq(fuse.flags + c, fuse.epoch, fuse.timeout_ns);
+              known |= 1ull << c;
+              waited = true;
+            }
+          }
+          if (waited) asm volatile("fence.proxy.async.global;" ::: "memory");
         }
         for (int kb = 0; kb < num_k; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -498,7 +540,8 @@ static int launch_gemm(void* C, const void* A, const void* B, int M, int N, int 
   // more round; the fused variants order their tiles by chunk arrival and keep whole tiles
   int split_from = num_tiles;
   CUtensorMap tmBh = tmB;
-  if (allow_split && tail_split_enabled() && BN == 256 && FuseKind<Fuse>::v == 0 && num_tiles > workers) {
+  if (allow_split && tail_split_enabled() && BN == 256 && (FuseKind<Fuse>::v == 0 || FuseKind<Fuse>::v == 3) &&
+      num_tiles > workers) {
     const int rem = num_tiles % workers;
     if (rem > 0 && 2 * rem <= workers) {
       if constexpr (kBK) rc = make_tmap_2d_bf16(&tmBh, B, N, K, ldb, BN / 2 / kCta, BK);
@@ -575,6 +618,31 @@ static WriteValue32Fn get_write_value() {
   return fn;
 }
 
+typedef CUresult (*WaitValue32Fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+static WaitValue32Fn get_wait_value() {
+  static WaitValue32Fn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<WaitValue32Fn>(p);
+  });
+  return fn;
+}
+
+// bound of the in-kernel waits on arrival flags (B200TRAIN_FLAG_TIMEOUT_MS, default 30 s): a gather that
+// never arrives turns into a trap with a message instead of a GEMM that spins for ever
+static unsigned long long flag_wait_timeout_ns() {
+  static const unsigned long long ns = [] {
+    const char* e = getenv("B200TRAIN_FLAG_TIMEOUT_MS");
+    const unsigned long long ms = e ? strtoull(e, nullptr, 10) : 30000ull;
+    return ms * 1000000ull;
+  }();
+  return ns;
+}
+
 // out[i] = sum_w slots[w * n + i]   (bf16, fp32 accumulate): the local half of a scattered reduction
 __global__ void sum_slots_kernel(uint4* __restrict__ out, const uint4* __restrict__ slots, size_t n16,
                                  int W) {
@@ -603,6 +671,8 @@ __global__ void sum_slots_kernel(uint4* __restrict__ out, const uint4* __restric
 }  // namespace b2
 
 extern "C" {
+
+int b2_local_copy(void* dst, const void* src, size_t bytes, int blocks, cudaStream_t stream);  // comm.cu
 
 const char* b2_last_error() { return b2::last_error(); }
 
@@ -660,6 +730,52 @@ int b2_gemm_rs(void* const* slot_bases, const void* A, const void* B, int M, int
                                                                  ld_slot, epi, 0, stream, f);
 }
 
+// FSDP all-gather -> GEMM. B is a weight inside a flat unit buffer that is being gathered chunk by chunk
+// (b2_peer_all_gather_flagged): flags[c] >= epoch marks chunk c (chunk_elems elements, chunks_per_rank
+// consecutive chunks per owning rank) as present in local memory. C[M, N] = epilogue(A * B^T), A [M, K]
+// K-major; b_mn = 0: B stored [N, K] (forward), 1: B stored [K, N] (dgrad; waits for the whole matrix).
+// epilogue: 0 none, 1 + bias[N]. b_off: element offset of B inside the flat buffer.
+int b2_gemm_bf16_bwait(void* C, const void* A, const void* B, int M, int N, int K, int b_mn, int lda,
+                       int ldb, int ldc, int epilogue, const void* bias, const unsigned int* flags,
+                       unsigned int epoch, long long b_off, long long chunk_elems, int n_chunks,
+                       int chunks_per_rank, int rank, int W, cudaStream_t stream) {
+  using namespace b2;
+  B2_REQUIRE(M > BM, "gemm_bwait: M=%d must exceed %d (2-CTA tiles)", M, BM);
+  B2_REQUIRE(n_chunks >= 1 && n_chunks <= 64 && chunk_elems > 0 && chunks_per_rank >= 1,
+             "gemm_bwait: %d chunks (at most 64) of %lld elements", n_chunks, chunk_elems);
+  B2_REQUIRE(epilogue == EPI_NONE || epilogue == EPI_BIAS, "gemm_bwait: unsupported epilogue %d", epilogue);
+  FuseBWait f;
+  f.flags = flags;
+  f.epoch = epoch;
+  f.b_off = b_off;
+  f.chunk_elems = chunk_elems;
+  f.n_chunks = n_chunks;
+  f.ldb = ldb;
+  f.timeout_ns = flag_wait_timeout_ns();
+  f.nb_start = 0;
+  if (!b_mn) {  // visit first the n-blocks whose rows arrive first: own shard, then the peers in pull order
+    const int num_n = (N + 255) / 256;
+    int best = W + 1;
+    for (int nb = 0; nb < num_n; ++nb) {
+      long long c = (b_off + (long long)nb * 256 * ldb) / chunk_elems;
+      if (c > n_chunks - 1) c = n_chunks - 1;
+      const int owner = (int)(c / chunks_per_rank) % W;
+      const int dist = (owner - rank + W) % W;
+      if (dist < best) { best = dist; f.nb_start = nb; }
+    }
+  }
+  EpiArgs epi = {};
+  epi.bias = static_cast<const __nv_bfloat16*>(bias);
+  if (b_mn) {
+    if (epilogue == EPI_BIAS)
+      return launch_gemm<2, true, false, EPI_BIAS, 256, FuseBWait>(C, A, B, M, N, K, lda, ldb, ldc, epi, 0, stream, f);
+    return launch_gemm<2, true, false, EPI_NONE, 256, FuseBWait>(C, A, B, M, N, K, lda, ldb, ldc, epi, 0, stream, f);
+  }
+  if (epilogue == EPI_BIAS)
+    return launch_gemm<2, true, true, EPI_BIAS, 256, FuseBWait>(C, A, B, M, N, K, lda, ldb, ldc, epi, 0, stream, f);
+  return launch_gemm<2, true, true, EPI_NONE, 256, FuseBWait>(C, A, B, M, N, K, lda, ldb, ldc, epi, 0, stream, f);
+}
+
 int b2_sum_slots(void* out, const void* slots, size_t n_elems, int W, cudaStream_t stream) {
   using namespace b2;
   B2_REQUIRE(n_elems % 8 == 0, "sum_slots: n not a multiple of 8");
@@ -688,6 +804,59 @@ int b2_peer_all_gather_chunks(void* dst, void* const* peer_bases, size_t chunk_b
                                   chunk_bytes, cudaMemcpyDeviceToDevice, stream));
     CUresult r = wv((CUstream)stream, (CUdeviceptr)(flags + peer), epoch, 0);
     B2_REQUIRE(r == CUDA_SUCCESS, "cuStreamWriteValue32 failed: %d", (int)r);
+  }
+  return 0;
+}
+
+// FSDP parameter gather with an arrival flag per chunk. dst: local full buffer [W * shard_bytes];
+// srcs[r]: rank r's shard (peer-mapped). Every shard is cut into `sub` chunks; chunk (r, j) is copied by
+// the copy engines and then flags[r * sub + j] = epoch is written by the stream (no SM involved), in the
+// order own shard, rank+1, rank+2, ... The own shard is placed by `self_blocks` copy blocks.
+// part: 0 = own shard only, 1 = peers only, 2 = both (callers record an event between the two parts so that
+// consumers order themselves behind the local copy KERNEL with a normal event and only ever spin on flags
+// that copy engines and stream memory operations produce).
+int b2_peer_all_gather_flagged(void* dst, void* const* srcs, size_t shard_bytes, int rank, int W, int sub,
+                               int self_blocks, int part, unsigned int* flags, unsigned int epoch,
+                               cudaStream_t stream) {
+  using namespace b2;
+  WriteValue32Fn wv = get_write_value();
+  B2_REQUIRE(wv != nullptr, "cuStreamWriteValue32 entry point unavailable");
+  B2_REQUIRE(sub >= 1 && W * sub <= 64 && shard_bytes % ((size_t)sub * 16) == 0,
+             "all_gather_flagged: shard of %zu bytes in %d chunks", shard_bytes, sub);
+  const size_t piece = shard_bytes / sub;
+  for (int k = 0; k < W; ++k) {
+    const int peer = (rank + k) % W;
+    char* d = static_cast<char*>(dst) + (size_t)peer * shard_bytes;
+    const char* sp = static_cast<const char*>(srcs[peer]);
+    if (peer == rank && part == 1) continue;
+    if (peer != rank && part == 0) continue;
+    if (peer == rank) {
+      if (int rc = b2_local_copy(d, sp, shard_bytes, self_blocks, stream)) return rc;
+      for (int j = 0; j < sub; ++j) {
+        CUresult r = wv((CUstream)stream, (CUdeviceptr)(flags + peer * sub + j), epoch, 0);
+        B2_REQUIRE(r == CUDA_SUCCESS, "cuStreamWriteValue32 failed: %d", (int)r);
+      }
+      continue;
+    }
+    for (int j = 0; j < sub; ++j) {
+      B2_CUDA_CHECK(cudaMemcpyAsync(d + (size_t)j * piece, sp + (size_t)j * piece, piece,
+                                    cudaMemcpyDeviceToDevice, stream));
+      CUresult r = wv((CUstream)stream, (CUdeviceptr)(flags + peer * sub + j), epoch, 0);
+      B2_REQUIRE(r == CUDA_SUCCESS, "cuStreamWriteValue32 failed: %d", (int)r);
+    }
+  }
+  return 0;
+}
+
+// Make `stream` wait (cuStreamWaitValue32, no SM involved) until flags[first .. first + count) >= epoch.
+int b2_stream_wait_flags(const unsigned int* flags, int first, int count, unsigned int epoch,
+                         cudaStream_t stream) {
+  using namespace b2;
+  WaitValue32Fn wf = get_wait_value();
+  B2_REQUIRE(wf != nullptr, "cuStreamWaitValue32 entry point unavailable");
+  for (int c = first; c < first + count; ++c) {
+    CUresult r = wf((CUstream)stream, (CUdeviceptr)(flags + c), epoch, CU_STREAM_WAIT_VALUE_GEQ);
+    B2_REQUIRE(r == CUDA_SUCCESS, "cuStreamWaitValue32 failed: %d", (int)r);
   }
   return 0;
 }

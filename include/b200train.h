@@ -124,6 +124,26 @@ int b2_colsum(void* out, float* partial, const void* x, int T, int N, int ld, in
 int b2_cpu_adamw_bf16(void* p, void* m, void* v, const void* g, size_t n, float lr, float beta1,
                       float beta2, float eps, float wd, int step, float grad_scale);
 
+/* ---- FSDP parameter all-gather fused into the consuming GEMM ---------------------------------------
+ * b2_peer_all_gather_flagged pulls the peers' shards of a flat unit into the local full buffer with the
+ * copy engines, `sub` chunks per shard, and writes flags[r * sub + j] = epoch after chunk (r, j) with a
+ * stream memory operation. b2_gemm_bf16_bwait is the tcgen05 GEMM whose weight operand B lives in that
+ * buffer (element offset b_off): its TMA producer waits for the chunks that hold a tile's weight rows
+ * and visits first the n-blocks that arrive first. b2_stream_wait_flags makes a stream wait for chunks
+ * (for consumers that are not GEMMs, e.g. norm weights). Every load is from local memory.
+ * Reference: the implicit per-unit all-gather of FullyShardedDataParallel before forward / backward
+ * (04-fully-sharded-data-parallel/train_llm.py:87-95,206,210). */
+int b2_peer_all_gather_flagged(void* dst, void* const* srcs, size_t shard_bytes, int rank, int W, int sub,
+                               int self_blocks, int part, unsigned int* flags, unsigned int epoch,
+                               b2_stream_t stream);
+int b2_gemm_bf16_bwait(void* C, const void* A, const void* B, int M, int N, int K, int b_mn, int lda,
+                       int ldb, int ldc, int epilogue, const void* bias, const unsigned int* flags,
+                       unsigned int epoch, long long b_off, long long chunk_elems, int n_chunks,
+                       int chunks_per_rank, int rank, int W, b2_stream_t stream);
+int b2_stream_wait_flags(const unsigned int* flags, int first, int count, unsigned int epoch,
+                         b2_stream_t stream);
+int b2_local_copy(void* dst, const void* src, size_t bytes, int blocks, b2_stream_t stream);
+
 /* ---- NVLink / NVSwitch peer-memory collectives (one process per GPU, one node) -------------------
  * Pointer arrays hold W peer-mapped addresses of the same symmetric buffer, index = rank. `pads` is the
  * symmetric signal pad (uint32 [channel][16]); `epoch` increases by one per call and channel pair;

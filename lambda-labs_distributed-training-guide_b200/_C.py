@@ -57,6 +57,11 @@ def _declare(lib):
         "b2_gemm_ag": [P, P, P, I, I, I, I, I, I, I, P, ctypes.c_uint, I, I, I, P],
         "b2_gemm_rs": [P, P, P, I, I, I, I, I, I, I, I, I, I, P],
         "b2_sum_slots": [P, P, Z, I, P],
+        "b2_gemm_bf16_bwait": [P, P, P, I, I, I, I, I, I, I, I, P, P, ctypes.c_uint, ctypes.c_longlong,
+                               ctypes.c_longlong, I, I, I, I, P],
+        "b2_peer_all_gather_flagged": [P, P, Z, I, I, I, I, I, P, ctypes.c_uint, P],
+        "b2_stream_wait_flags": [P, I, I, ctypes.c_uint, P],
+        "b2_local_copy": [P, P, Z, I, P],
         "b2_peer_all_gather_chunks": [P, P, Z, I, I, P, ctypes.c_uint, P],
         "b2_cpu_adamw_bf16": [P, P, P, P, Z, F, F, F, F, F, I, F],
         "b2_peer_barrier": [P, I, I, I, ctypes.c_uint, P],

@@ -23,6 +23,7 @@ class Conv1D(nn.Module):
     def __init__(self, nf, nx, dtype, device):
         super().__init__()
         self.weight = nn.Parameter(torch.empty(nx, nf, dtype=dtype, device=device))
+        self.weight._b2_linear_only = True   # read by ops.linear GEMMs only (FSDP: gather fused into them)
         self.bias = nn.Parameter(torch.zeros(nf, dtype=dtype, device=device))
 
     def forward(self, x):

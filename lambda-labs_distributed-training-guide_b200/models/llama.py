@@ -33,6 +33,7 @@ class FusedLinearWeight(nn.Module):
     def __init__(self, in_features, out_features, dtype, device, parts=None):
         super().__init__()
         self.weight = nn.Parameter(torch.empty(out_features, in_features, dtype=dtype, device=device))
+        self.weight._b2_linear_only = True   # read by ops.linear GEMMs only (FSDP: gather fused into them)
         self.parts = parts or []
 
     def forward(self, x):

@@ -21,6 +21,40 @@ EPI_NONE, EPI_BIAS, EPI_BIAS_GELU, EPI_ACCUM = 0, 1, 2, 3
 GEMM_CONFIG = 0
 
 
+class GatherWait:
+    """Arrival flags of the flat unit buffer a weight lives in while FSDP is still gathering it
+    (``parallel/fsdp.py``). ``offset`` is the weight's element offset in that buffer."""
+
+    __slots__ = ("flags_ptr", "epoch", "offset", "chunk_elems", "n_chunks", "chunks_per_rank", "rank", "world")
+
+    def __init__(self, flags_ptr, epoch, offset, chunk_elems, n_chunks, chunks_per_rank, rank, world):
+        self.flags_ptr, self.epoch, self.offset, self.chunk_elems = flags_ptr, epoch, offset, chunk_elems
+        self.n_chunks, self.chunks_per_rank, self.rank, self.world = n_chunks, chunks_per_rank, rank, world
+
+    def stream_wait(self, numel: int, stream_ptr: int):
+        """Order ``stream`` behind the arrival of every chunk that holds ``numel`` elements from ``offset``."""
+        lo = self.offset // self.chunk_elems
+        hi = min((self.offset + numel - 1) // self.chunk_elems, self.n_chunks - 1)
+        _C.call("b2_stream_wait_flags", self.flags_ptr, lo, hi - lo + 1, self.epoch, stream_ptr)
+
+
+def gemm_gathered(a: torch.Tensor, w: torch.Tensor, ag: GatherWait, *, b_mn=False, bias=None) -> torch.Tensor:
+    """``a @ w^T`` (or ``a @ w`` with ``b_mn``) where ``w`` is still being all-gathered: the GEMM itself waits,
+    tile by tile, for the chunks of the gathered buffer that hold the weight rows it is about to load
+    (``b2_gemm_bf16_bwait``). Shapes the fused kernel does not cover wait on the stream and run the plain GEMM."""
+    M = a.shape[0]
+    N = w.shape[1] if b_mn else w.shape[0]
+    K = a.shape[1]
+    if M <= 128 or (b_mn and N % 64) or a.stride(1) != 1 or w.stride(1) != 1:
+        ag.stream_wait(w.numel(), stream(a))
+        return gemm(a, w, b_mn=b_mn, epilogue=EPI_BIAS if bias is not None else EPI_NONE, bias=bias)
+    out = torch.empty((M, N), dtype=torch.bfloat16, device=a.device)
+    _C.call("b2_gemm_bf16_bwait", out.data_ptr(), a.data_ptr(), w.data_ptr(), M, N, K, int(b_mn), a.stride(0),
+            w.stride(0), out.stride(0), EPI_BIAS if bias is not None else EPI_NONE, _C.ptr(bias), ag.flags_ptr,
+            ag.epoch, ag.offset, ag.chunk_elems, ag.n_chunks, ag.chunks_per_rank, ag.rank, ag.world, stream(a))
+    return out
+
+
 def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn=False, b_mn=False, out=None, epilogue=EPI_NONE,
          bias=None, config=None, max_ctas=0) -> torch.Tensor:
     """C[M,N] = epilogue(A B^T). ``a``: [M,K] (or [K,M] when a_mn), ``b``: [N,K] (or [K,N] when b_mn).
@@ -96,6 +130,9 @@ class _Linear(torch.autograd.Function):
         # x is 2-D [T, in]; the output is a fresh (non-view) tensor so callers may modify it in place
         ctx.w_is_kn = w_is_kn
         ctx.save_for_backward(x, w, bias)
+        ag = getattr(w, "_b2_ag", None)
+        if ag is not None:   # FSDP: the weight's all-gather may still be in flight
+            return gemm_gathered(x, w, ag, b_mn=w_is_kn, bias=bias)
         return gemm(x, w, b_mn=w_is_kn, epilogue=EPI_BIAS if bias is not None else EPI_NONE, bias=bias)
 
     @staticmethod
@@ -107,7 +144,9 @@ class _Linear(torch.autograd.Function):
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
             # dx[M, in] = dy[M, out] * W ; W as the "B" operand is [in, out]-logical
-            dx = gemm(dy2, w, b_mn=not ctx.w_is_kn)
+            ag = getattr(w, "_b2_ag", None)
+            dx = (gemm_gathered(dy2, w, ag, b_mn=not ctx.w_is_kn) if ag is not None
+                  else gemm(dy2, w, b_mn=not ctx.w_is_kn))
         if ctx.needs_input_grad[1]:
             if ctx.w_is_kn:   # dW[in, out] = x^T dy
                 a, b = x2, dy2

@@ -24,6 +24,10 @@ def init_distributed(device_type: Optional[str] = None, timeout_s: int = 1800):
     """Initialise the default process group from the launcher's environment. Returns
     ``(rank, local_rank, world_size, device)``; works without a launcher (world 1)."""
     env = os.environ
+    # kernels of this framework wait on flags that copy engines and other streams produce (fused gather ->
+    # GEMM); streams that share a hardware queue would serialise behind such a waiter, so ask for the
+    # maximum number of queues before the CUDA context exists
+    env.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
     if "RANK" not in env and "OMPI_COMM_WORLD_RANK" in env:  # mpirun
         env["RANK"] = env["OMPI_COMM_WORLD_RANK"]
         env["WORLD_SIZE"] = env["OMPI_COMM_WORLD_SIZE"]

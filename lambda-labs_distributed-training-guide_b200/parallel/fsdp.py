@@ -71,6 +71,16 @@ class _BufferPool:
         self.owner[i] = None
 
 
+class _Gathered:
+    """One in-flight / resident all-gather of a unit: pool slot, completion event, the full view and, for
+    the flag-gated (fused) gather, the event after the own-shard copy plus the arrival flags and epoch."""
+
+    __slots__ = ("slot", "ev", "full", "ev_local", "flags", "epoch")
+
+    def __init__(self, slot, ev, full, ev_local=None, flags=None, epoch=0):
+        self.slot, self.ev, self.full, self.ev_local, self.flags, self.epoch = slot, ev, full, ev_local, flags, epoch
+
+
 class FSDP(Strategy):
     name = "fsdp"
 
@@ -140,7 +150,21 @@ class FSDP(Strategy):
                 u.assign_grads(g)
         if self.is_cuda:
             torch.cuda.synchronize(self.device)
-        self._gathered = {}       # unit -> (pool slot, gather-finished event, full view)
+        self._gathered = {}       # unit -> _Gathered
+        # all-gather fused into the consuming GEMMs: the gather is issued in chunks with an arrival flag each
+        # and the linears of the unit wait for their own weight rows inside the GEMM (ops/linear.py,
+        # b2_gemm_bf16_bwait) instead of the compute stream waiting for the whole unit
+        self.fused_ag = (self.supports_fused_ag and self.is_cuda and self.W > 1 and not cpu_offload
+                         and not self.resident and type(self.comm).__name__ == "PeerComm" and dtype == torch.bfloat16
+                         and os.environ.get("B200TRAIN_FSDP_FUSED_AG", "1") != "0")
+        if self.fused_ag:
+            self._ag_flags = torch.zeros((self.param_pool.n, 64), dtype=torch.int32, device=self.device)
+            self._ag_epochs = [0] * self.param_pool.n
+            sub = max(1, min(16, 64) // self.W)
+            for u in self.units:
+                u.sub = sub
+                while u.sub > 1 and (u.numel // self.W) % (u.sub * 8):
+                    u.sub //= 2
         self._grad_slot = {}      # unit -> pool slot of its full gradient buffer
         self._opt_events = {}     # unit -> event after a side-stream optimizer update of its shard
         self._local_acc = {}      # unit -> unreduced gradient accumulator (no_sync)
@@ -176,6 +200,9 @@ class FSDP(Strategy):
 
     def pre_reduce(self, i):
         """Called when unit ``i``'s gradients are complete, before they are reduced over this group."""
+
+    # False for strategies whose linears are not ops.linear (the tensor-parallel fused linears of 2D)
+    supports_fused_ag = True
 
     # set by strategies that reduce the gradient shard over a second group (hybrid shard): the fused
     # reduce-scatter + AdamW kernel is then bypassed, the update must see the fully reduced shard
@@ -228,6 +255,19 @@ class FSDP(Strategy):
         slot, buf, free_ev = self.param_pool.acquire(i)
         full = buf[:u.numel]
         n = u.numel // self.W
+        if self.fused_ag and u.prefix < u.numel:
+            self._ag_epochs[slot] += 1
+            epoch, flags = self._ag_epochs[slot], self._ag_flags[slot]
+            with self._on(self.ag_stream):
+                self._wait(free_ev, self.ag_stream)
+                # own shard first (a copy KERNEL: consumers order themselves behind it with an event), then the
+                # peers' chunks by copy engine, a flag written by the stream after each
+                self.comm.all_gather_flagged(full, self.shard_param[i], flags, epoch, u.sub, part=0)
+                ev_local = self._record(self.ag_stream)
+                self.comm.all_gather_flagged(full, self.shard_param[i], flags, epoch, u.sub, part=1)
+                ev = self._record(self.ag_stream)
+            self._gathered[i] = _Gathered(slot, ev, full, ev_local, flags, epoch)
+            return
         with self._on(self.ag_stream):
             self._wait(free_ev, self.ag_stream)
             if self.cpu_offload:
@@ -238,22 +278,39 @@ class FSDP(Strategy):
             if self.W > 1:
                 self.comm.all_gather(full, src)
             ev = self._record(self.ag_stream)
-        self._gathered[i] = (slot, ev, full)
+        self._gathered[i] = _Gathered(slot, ev, full)
 
     def _ensure(self, i: int):
         if self.resident:
             self._wait(self._opt_events.pop(i, None))
             return
         self._gather(i)
-        slot, ev, full = self._gathered[i]
-        self._wait(ev)
-        self.units[i].repoint(full)
+        g = self._gathered[i]
+        u = self.units[i]
+        if g.flags is None:
+            self._wait(g.ev)
+            u.repoint(g.full)
+            return
+        # flag-gated gather: behind the own-shard copy, and behind the chunks that hold the parameters no
+        # GEMM consumes (norm weights, biases: laid out first in the unit); the linears wait in-kernel
+        from ..ops.linear import GatherWait
+
+        self._wait(g.ev_local)
+        n = u.numel // self.W
+        chunk = n // u.sub
+        if u.prefix > 0:
+            _C_call_wait(g.flags, 0, (u.prefix + chunk - 1) // chunk, g.epoch, self.device)
+        u.repoint(g.full)
+        fp = g.flags.data_ptr()
+        for p, o in zip(u.params, u.offsets):
+            p._b2_ag = (GatherWait(fp, g.epoch, o, chunk, self.W * u.sub, u.sub, self.R, self.W)
+                        if getattr(p, "_b2_linear_only", False) else None)
 
     def _release(self, i: int):
         if self.resident or i not in self._gathered:
             return
-        slot, _, _ = self._gathered.pop(i)
-        self.param_pool.release(slot, self._record())
+        g = self._gathered.pop(i)
+        self.param_pool.release(g.slot, self._record())
 
     def _tied_head(self, i: int) -> bool:
         return self.cfg.tie_word_embeddings and i == len(self.units) - 1
@@ -488,6 +545,13 @@ class FSDP(Strategy):
         shard.copy_(full[self.R * n:(self.R + 1) * n])
 
 
+def _C_call_wait(flags, first, count, epoch, device):
+    from .. import _C
+
+    _C.call("b2_stream_wait_flags", flags.data_ptr(), first, count, epoch,
+            torch.cuda.current_stream(device).cuda_stream)
+
+
 class _Layout(FlatUnit):
     """A FlatUnit whose storage is transient: ``repoint``/``assign_grads`` attach it to pool buffers."""
 
@@ -502,12 +566,22 @@ class _Layout(FlatUnit):
                 self.params.append(p)
         from ..utils.flat import ALIGN, _round_up
 
+        # parameters that only GEMMs read (tagged by the model) go last: whatever precedes them -- norm
+        # weights, biases, embeddings -- is what the compute stream has to wait for before the unit runs,
+        # the linears wait for their own rows inside the GEMM (fused all-gather)
+        self.params.sort(key=lambda p: bool(getattr(p, "_b2_linear_only", False)))
         self.offsets = []
         off = 0
+        self.prefix = None
         for p in self.params:
+            if self.prefix is None and getattr(p, "_b2_linear_only", False):
+                self.prefix = off
             self.offsets.append(off)
             off += _round_up(p.numel(), ALIGN)
         self.numel = _round_up(off, ALIGN * world)
+        if self.prefix is None:
+            self.prefix = self.numel
+        self.sub = 1
         self.dtype = self.params[0].dtype
         self.device = None
         self.flat_param = None
@@ -542,7 +616,7 @@ class _Layout(FlatUnit):
             q.data = full[o:o + p.numel()].view(p.shape)
             q._b2_unit = self
             for k, v in vars(p).items():   # carry strategy tags (e.g. tp-replicated) over to the real parameter
-                if k.startswith("_b2_tp"):
+                if k.startswith("_b2_tp") or k == "_b2_linear_only":
                     setattr(q, k, v)
             swap[id(p)] = q
             new_params.append(q)

@@ -170,6 +170,18 @@ class PeerComm(TorchComm):
         _C.call("b2_peer_all_gather", full.data_ptr(), srcs, n, self.rank, self.world, skip_self, max_blocks,
                 self._stream())
 
+    def all_gather_flagged(self, full, shard, flags, epoch: int, sub: int, part: int = 2):
+        """Copy-engine gather of ``shard`` (symmetric) into the local ``full`` with an arrival flag per chunk
+        (``sub`` chunks per rank, ``flags[r * sub + j] = epoch`` written by the stream after the chunk).
+        ``part``: 0 own shard only, 1 peers only, 2 both."""
+        srcs = self._peer_array(shard)
+        if srcs is None:
+            raise RuntimeError("all_gather_flagged needs a symmetric shard (allocate it with comm.empty)")
+        n = shard.numel() * shard.element_size()
+        with nvtx.range("comm.all_gather_flagged"):
+            _C.call("b2_peer_all_gather_flagged", full.data_ptr(), srcs, n, self.rank, self.world, sub,
+                    self.self_copy_blocks, part, flags.data_ptr(), epoch, self._stream())
+
     def all_gather_inplace(self, full, max_blocks: int = 64):
         """In-place variant: slice q is pulled from rank q's copy of the same buffer (the owned slices sit
         at different offsets on different ranks, so the sources are ``peer_base[q] + q * slice``)."""

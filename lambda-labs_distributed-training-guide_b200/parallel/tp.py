@@ -156,6 +156,7 @@ class TwoD(FSDP):
 
     name = "2d"
     shards_over_dp = True
+    supports_fused_ag = False   # colwise / rowwise already fuse their own (sequence) collectives
 
     def __init__(self, cfg, device, lr=3e-5, seed=0, dtype=torch.bfloat16, tp: int = 2, **kw):
         self.mesh = Mesh2D(tp)
