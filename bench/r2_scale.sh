@@ -14,12 +14,17 @@ for l in sys.stdin:
 for s in ${STAGES:-peer comm bench tl}; do
   case $s in
     peer) run ${TAG}_peer python -m pytest tests/test_peer_gpu.py -x -q; tail -3 gpurun_out/${TAG}_peer.log ;;
-    par)  TMO=900 run ${TAG}_par python -m pytest tests/test_parallel_gpu.py -x -q; tail -5 gpurun_out/${TAG}_par.log ;;
+    fag)  run ${TAG}_fag python -m pytest tests/test_fused_ag_gpu.py -x -q; tail -3 gpurun_out/${TAG}_fag.log ;;
+    par)  TMO=900 run ${TAG}_par python -m pytest tests/test_parallel_gpu.py -q; tail -8 gpurun_out/${TAG}_par.log ;;
     comm) run ${TAG}_comm $TR bench/comm_bench.py; grep -E "rs_adamw|rs_ms|ag_ce|gemm|roofline" gpurun_out/${TAG}_comm.log ;;
     bench)
       run ${TAG}_b_stream $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer stream
-      run ${TAG}_b_kernel $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer kernel ;;
+      run ${TAG}_b_kernel $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer kernel
+      B200TRAIN_FSDP_FUSED_AG=0 run ${TAG}_b_kernel_nofag $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer kernel ;;
     sweep)
+      B200TRAIN_RS_PIPE=0 run ${TAG}_b_stream_nopipe $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer stream
+      B200TRAIN_RS_PIPE=0 B200TRAIN_RS_BLOCKS=128 run ${TAG}_b_stream_nopipe128 $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer stream
+      B200TRAIN_RS_BLOCKS=148 run ${TAG}_b_stream148 $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer stream
       B200TRAIN_RSADAM_BLOCKS=296 run ${TAG}_b_kernel296 $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer kernel
       B200TRAIN_RSADAM_BLOCKS=64 run ${TAG}_b_kernel64 $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer kernel
       B200TRAIN_SELF_COPY_BLOCKS=0 run ${TAG}_b_kernel_memcpy $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer kernel

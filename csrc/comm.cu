@@ -273,15 +273,19 @@ template <bool kAdam>
 static int launch_rs(int W, int blocks, cudaStream_t stream, V4* out, PeerPtrs full, size_t n16,
                      int rank, float scale, PeerPtrs pads, int chan_base, uint32_t epoch,
                      unsigned int* counter, AdamArgs a) {
-  if (W <= 2 && !kAdam)
+  if (W <= 2 && !kAdam) {
+    B2_SIDE_KERNEL((peer_reduce_scatter_kernel<kAdam, 4>));
     peer_reduce_scatter_kernel<kAdam, 4><<<blocks, kCommThreads, 0, stream>>>(
         out, full, n16, rank, W, scale, pads, chan_base, epoch, counter, a);
-  else if (W <= 4)
+  } else if (W <= 4) {
+    B2_SIDE_KERNEL((peer_reduce_scatter_kernel<kAdam, 2>));
     peer_reduce_scatter_kernel<kAdam, 2><<<blocks, kCommThreads, 0, stream>>>(
         out, full, n16, rank, W, scale, pads, chan_base, epoch, counter, a);
-  else
+  } else {
+    B2_SIDE_KERNEL((peer_reduce_scatter_kernel<kAdam, 1>));
     peer_reduce_scatter_kernel<kAdam, 1><<<blocks, kCommThreads, 0, stream>>>(
         out, full, n16, rank, W, scale, pads, chan_base, epoch, counter, a);
+  }
   B2_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
@@ -559,6 +563,7 @@ extern "C" {
 int b2_peer_barrier(void* const* pads, int rank, int W, int channel, unsigned int epoch,
                     cudaStream_t stream) {
   B2_REQUIRE(W >= 1 && W <= kMaxPeers, "peer collectives support up to %d ranks (got %d)", kMaxPeers, W);
+  B2_SIDE_KERNEL((peer_barrier_kernel));
   peer_barrier_kernel<<<1, 32, 0, stream>>>(to_ptrs(pads, W), rank, W, channel, epoch);
   B2_CUDA_CHECK(cudaGetLastError());
   return 0;
@@ -571,6 +576,7 @@ int b2_peer_all_gather(void* dst, void* const* srcs, size_t shard_bytes, int ran
   B2_REQUIRE(shard_bytes % 16 == 0, "all_gather: shard size %zu not a multiple of 16 bytes", shard_bytes);
   if (shard_bytes == 0) return 0;
   const size_t n16 = shard_bytes / 16;
+  B2_SIDE_KERNEL((peer_all_gather_kernel));
   peer_all_gather_kernel<<<clamp_blocks(n16, max_blocks), kCommThreads, 0, stream>>>(
       static_cast<V4*>(dst), to_ptrs(srcs, W), n16, rank, W, skip_self);
   B2_CUDA_CHECK(cudaGetLastError());
@@ -591,6 +597,7 @@ int b2_peer_all_gather_ce(void* dst, void* const* srcs, size_t shard_bytes, int 
         (reinterpret_cast<uintptr_t>(d) & 15) == 0 && (reinterpret_cast<uintptr_t>(srcs[peer]) & 15) == 0) {
       const size_t n16 = shard_bytes / 16;
       if (n16 > 0) {
+        B2_SIDE_KERNEL((local_copy_kernel));
         local_copy_kernel<<<clamp_blocks(n16, self_blocks), kCommThreads, 0, stream>>>(
             reinterpret_cast<V4*>(d), static_cast<const V4*>(srcs[peer]), n16);
         B2_CUDA_CHECK(cudaGetLastError());
@@ -608,6 +615,7 @@ int b2_local_copy(void* dst, const void* src, size_t bytes, int blocks, cudaStre
   if (blocks > 0 && bytes % 16 == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0 &&
       (reinterpret_cast<uintptr_t>(src) & 15) == 0) {
     const size_t n16 = bytes / 16;
+    B2_SIDE_KERNEL((local_copy_kernel));
     local_copy_kernel<<<clamp_blocks(n16, blocks), kCommThreads, 0, stream>>>(
         static_cast<V4*>(dst), static_cast<const V4*>(src), n16);
     B2_CUDA_CHECK(cudaGetLastError());
@@ -634,6 +642,7 @@ int b2_peer_reduce_scatter(void* out_shard, void* const* fulls, size_t shard_ele
   const size_t n16 = shard_elems / 8;
   AdamArgs none = {};
   if (W == 2 && rs_pipe_enabled()) {
+    B2_SIDE_KERNEL((rs_pipe_kernel<false, false, 4, 2>));
     rs_pipe_kernel<false, false, 4, 2><<<clamp_blocks(n16, max_blocks), kCommThreads, 0, stream>>>(
         static_cast<V4*>(out_shard), static_cast<const V4*>(fulls[1 - rank]) + (size_t)rank * n16,
         static_cast<const V4*>(fulls[rank]) + (size_t)rank * n16, n16, rank, W, scale, to_ptrs(pads, W),
@@ -666,6 +675,7 @@ int b2_peer_reduce_scatter_adamw(void* p, void* m, void* v, void* const* fulls, 
   a.step_size = lr / (1.f - powf(beta1, (float)step));
   a.inv_bc2_sqrt = 1.f / sqrtf(1.f - powf(beta2, (float)step));
   if (W == 2 && rs_pipe_enabled()) {
+    B2_SIDE_KERNEL((rs_pipe_kernel<true, false, 2, 3>));
     rs_pipe_kernel<true, false, 2, 3><<<clamp_blocks(n16, max_blocks), kCommThreads, 0, stream>>>(
         nullptr, static_cast<const V4*>(fulls[1 - rank]) + (size_t)rank * n16,
         static_cast<const V4*>(fulls[rank]) + (size_t)rank * n16, n16, rank, W, grad_scale,
@@ -684,6 +694,7 @@ int b2_peer_all_reduce(void* const* bufs, size_t elems, int rank, int W, float s
   B2_REQUIRE(W >= 1 && W <= kMaxPeers, "peer collectives support up to %d ranks (got %d)", kMaxPeers, W);
   B2_REQUIRE(elems % (8 * (size_t)W) == 0, "all_reduce: %zu elements not a multiple of 8*W", elems);
   const size_t n16_slice = elems / 8 / W;
+  B2_SIDE_KERNEL((peer_all_reduce_kernel));
   peer_all_reduce_kernel<<<clamp_blocks(n16_slice, max_blocks), 256, 0, stream>>>(
       to_ptrs(bufs, W), n16_slice, rank, W, scale, to_ptrs(pads, W), chan_base, epoch, counter);
   B2_CUDA_CHECK(cudaGetLastError());
@@ -700,14 +711,17 @@ int b2_nvls_reduce_scatter(void* out_shard, const void* mc_full, size_t shard_el
   B2_REQUIRE(shard_elems % 8 == 0, "reduce_scatter: shard of %zu elements is not a multiple of 8", shard_elems);
   const size_t n16 = shard_elems / 8;
   AdamArgs none = {};
-  if (rs_pipe_enabled())
+  if (rs_pipe_enabled()) {
+    B2_SIDE_KERNEL((rs_pipe_kernel<false, true, 4, 3>));
     rs_pipe_kernel<false, true, 4, 3><<<clamp_blocks(n16, max_blocks), kCommThreads, 0, stream>>>(
         static_cast<V4*>(out_shard), static_cast<const V4*>(mc_full) + (size_t)rank * n16, nullptr, n16,
         rank, W, scale, to_ptrs(pads, W), chan_base, epoch, counter, none);
-  else
+  } else {
+    B2_SIDE_KERNEL((nvls_reduce_scatter_kernel<false>));
     nvls_reduce_scatter_kernel<false><<<clamp_blocks(n16, max_blocks), kCommThreads, 0, stream>>>(
         static_cast<V4*>(out_shard), static_cast<const V4*>(mc_full), n16, rank, W, scale,
         to_ptrs(pads, W), chan_base, epoch, counter, none);
+  }
   B2_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
@@ -731,14 +745,17 @@ int b2_nvls_reduce_scatter_adamw(void* p, void* m, void* v, const void* mc_full,
   a.eps = eps;
   a.step_size = lr / (1.f - powf(beta1, (float)step));
   a.inv_bc2_sqrt = 1.f / sqrtf(1.f - powf(beta2, (float)step));
-  if (rs_pipe_enabled())
+  if (rs_pipe_enabled()) {
+    B2_SIDE_KERNEL((rs_pipe_kernel<true, true, 2, 4>));
     rs_pipe_kernel<true, true, 2, 4><<<clamp_blocks(n16, max_blocks), kCommThreads, 0, stream>>>(
         nullptr, static_cast<const V4*>(mc_full) + (size_t)rank * n16, nullptr, n16, rank, W, grad_scale,
         to_ptrs(pads, W), chan_base, epoch, counter, a);
-  else
+  } else {
+    B2_SIDE_KERNEL((nvls_reduce_scatter_kernel<true>));
     nvls_reduce_scatter_kernel<true><<<clamp_blocks(n16, max_blocks), kCommThreads, 0, stream>>>(
         nullptr, static_cast<const V4*>(mc_full), n16, rank, W, grad_scale, to_ptrs(pads, W), chan_base,
         epoch, counter, a);
+  }
   B2_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
@@ -750,6 +767,7 @@ int b2_nvls_all_reduce(void* mc_buf, size_t elems, int rank, int W, float scale,
   B2_REQUIRE(mc_buf != nullptr, "nvls all_reduce: no multicast mapping%s", "");
   B2_REQUIRE(elems % (8 * (size_t)W) == 0, "all_reduce: %zu elements not a multiple of 8*W", elems);
   const size_t n16_slice = elems / 8 / W;
+  B2_SIDE_KERNEL((nvls_all_reduce_kernel));
   nvls_all_reduce_kernel<<<clamp_blocks(n16_slice, max_blocks), kCommThreads, 0, stream>>>(
       static_cast<V4*>(mc_buf), n16_slice, rank, W, scale, to_ptrs(pads, W), chan_base, epoch, counter);
   B2_CUDA_CHECK(cudaGetLastError());

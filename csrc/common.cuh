@@ -32,6 +32,21 @@ void set_last_error(const char* fmt, ...);
     }                                                                                             \
   } while (0)
 
+// Kernels that run beside the persistent GEMM on other streams (collectives, copies, the optimizer) ask for
+// the same shared-memory carveout as the GEMM, i.e. all of it. An SM whose resident blocks were launched
+// with a small carveout has to drain before a 227 KB CTA can be placed on it: measured on a 2-GPU FSDP
+// step, every GEMM launched while a 148-block reduce-scatter (or a cudaMemcpy device-to-device kernel) was
+// resident started only when that kernel had finished, which turns "co-resident" into "serialised".
+#define B2_SIDE_KERNEL(kernel)                                                                     \
+  do {                                                                                             \
+    static bool _b2_once = false;                                                                  \
+    if (!_b2_once) {                                                                               \
+      cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout,                 \
+                           cudaSharedmemCarveoutMaxShared);                                        \
+      _b2_once = true;                                                                             \
+    }                                                                                              \
+  } while (0)
+
 // ----------------------------------------------------------------------------------------------
 // misc
 // ----------------------------------------------------------------------------------------------

@@ -1251,6 +1251,7 @@ int b2_adamw(void* p, void* m, void* v, const void* g, size_t n, float lr, float
   const float bc2 = 1.f - powf(beta2, (float)step);
   int grid = ew_grid(n / 8 + 1, 256);
   if (max_blocks > 0 && grid > max_blocks) grid = max_blocks;
+  B2_SIDE_KERNEL((adamw_kernel));   // runs beside the GEMMs of backward on the optimizer stream
   adamw_kernel<<<grid, 256, 0, stream>>>((bf16*)p, (bf16*)m, (bf16*)v, (const bf16*)g, n, lr,
                                          beta1, beta2, eps, wd, bc1, sqrtf(bc2), grad_scale);
   B2_CUDA_CHECK(cudaGetLastError());

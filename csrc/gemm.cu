@@ -783,6 +783,7 @@ int b2_sum_slots(void* out, const void* slots, size_t n_elems, int W, cudaStream
   int blocks = (int)((n16 + 255) / 256);
   if (blocks > sm_count() * 8) blocks = sm_count() * 8;
   if (blocks < 1) blocks = 1;
+  B2_SIDE_KERNEL((sum_slots_kernel));
   sum_slots_kernel<<<blocks, 256, 0, stream>>>((uint4*)out, (const uint4*)slots, n16, W);
   B2_CUDA_CHECK(cudaGetLastError());
   return 0;

@@ -17,7 +17,7 @@ import torch
 import torch.distributed as dist
 
 from .. import _C
-from .dispatch import check_bf16, stream, use_kernels
+from .dispatch import check_bf16, keep_params, real_param, stream, use_kernels
 from .linear import gemm, EPI_ACCUM, EPI_NONE, _direct_grad
 
 IGNORE = -100
@@ -48,11 +48,13 @@ class _LinearCrossEntropy(torch.autograd.Function):
         n_valid = (labels != IGNORE).sum().clamp_(min=1)
         loss = loss_rows.sum() / n_valid
         ctx.save_for_backward(x, w, labels, logits, lse, n_valid)
+        keep_params(ctx, w=w)
         return loss
 
     @staticmethod
     def backward(ctx, dloss):
         x, w, labels, logits, lse, n_valid = ctx.saved_tensors
+        w = real_param(ctx, "w", w)
         T, H = x.shape
         V = w.shape[0]
         ld = logits.shape[1]

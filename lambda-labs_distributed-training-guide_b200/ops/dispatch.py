@@ -40,3 +40,17 @@ def check_bf16(*tensors):
     for t in tensors:
         if t is not None and t.dtype != torch.bfloat16:
             raise TypeError(f"b200train kernels take bf16 tensors, got {t.dtype}")
+
+
+def keep_params(ctx, **params):
+    """Remember the parameter OBJECTS an autograd function was called with. ``ctx.saved_tensors`` does not
+    always give them back: under non-reentrant activation checkpointing a saved parameter is replaced by a
+    detached alias made during recomputation, which shares the storage but has neither ``.grad`` nor the
+    direct-gradient flags (``_b2_direct_grad`` / ``_b2_grad_ready``) -- a backward that looked at the alias
+    would hand the gradient to autograd and the unit's own bookkeeping would then zero it as "not produced"."""
+    ctx._b2_params = params
+
+
+def real_param(ctx, name, saved):
+    p = getattr(ctx, "_b2_params", {}).get(name)
+    return p if p is not None else saved

@@ -7,7 +7,7 @@ from __future__ import annotations
 import torch
 
 from .. import _C
-from .dispatch import check_bf16, stream, use_kernels
+from .dispatch import keep_params, real_param, check_bf16, stream, use_kernels
 
 
 class _Embedding(torch.autograd.Function):
@@ -20,11 +20,13 @@ class _Embedding(torch.autograd.Function):
         _C.call("b2_embedding_fwd", out.data_ptr(), table.data_ptr(), flat.data_ptr(), flat.numel(), H,
                 stream(table))
         ctx.save_for_backward(flat, table)
+        keep_params(ctx, table=table)
         return out.view(*ids.shape, H)
 
     @staticmethod
     def backward(ctx, dout):
         flat, table = ctx.saved_tensors
+        table = real_param(ctx, "table", table)
         H = table.shape[1]
         d2 = dout.reshape(-1, H)
         if not d2.is_contiguous():

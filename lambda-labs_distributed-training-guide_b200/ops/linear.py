@@ -13,7 +13,7 @@ from __future__ import annotations
 import torch
 
 from .. import _C
-from .dispatch import check_bf16, stream, use_kernels
+from .dispatch import check_bf16, keep_params, real_param, stream, use_kernels
 
 EPI_NONE, EPI_BIAS, EPI_BIAS_GELU, EPI_ACCUM = 0, 1, 2, 3
 
@@ -130,6 +130,7 @@ class _Linear(torch.autograd.Function):
         # x is 2-D [T, in]; the output is a fresh (non-view) tensor so callers may modify it in place
         ctx.w_is_kn = w_is_kn
         ctx.save_for_backward(x, w, bias)
+        keep_params(ctx, w=w, bias=bias)
         ag = getattr(w, "_b2_ag", None)
         if ag is not None:   # FSDP: the weight's all-gather may still be in flight
             return gemm_gathered(x, w, ag, b_mn=w_is_kn, bias=bias)
@@ -138,6 +139,7 @@ class _Linear(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy):
         x2, w, bias = ctx.saved_tensors
+        w, bias = real_param(ctx, "w", w), real_param(ctx, "bias", bias)
         dy2 = dy.reshape(-1, dy.shape[-1])
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()

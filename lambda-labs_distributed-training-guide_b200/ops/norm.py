@@ -10,7 +10,7 @@ from __future__ import annotations
 import torch
 
 from .. import _C
-from .dispatch import check_bf16, stream, use_kernels
+from .dispatch import check_bf16, keep_params, real_param, stream, use_kernels
 
 _scratch = {}
 
@@ -46,6 +46,7 @@ class _RMSNorm(torch.autograd.Function):
         _C.call("b2_rmsnorm_fwd", y.data_ptr(), rstd.data_ptr(), h.data_ptr() if r2 is not None else None,
                 x2.data_ptr(), _C.ptr(r2), w.data_ptr(), T, H, eps, stream(x))
         ctx.save_for_backward(h, w, rstd)
+        keep_params(ctx, w=w)
         ctx.has_res = residual is not None
         ctx.shape = x.shape
         if residual is None:
@@ -55,6 +56,7 @@ class _RMSNorm(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy, dh=None):
         h, w, rstd = ctx.saved_tensors
+        w = real_param(ctx, "w", w)
         T, H = h.shape
         dy2 = dy.reshape(T, H)
         if not dy2.is_contiguous():
@@ -107,6 +109,7 @@ class _LayerNorm(torch.autograd.Function):
                 h.data_ptr() if r2 is not None else None, x2.data_ptr(), _C.ptr(r2), w.data_ptr(),
                 b.data_ptr(), T, H, eps, stream(x))
         ctx.save_for_backward(h, w, b, mean, rstd)
+        keep_params(ctx, w=w, b=b)
         ctx.has_res = residual is not None
         ctx.shape = x.shape
         if residual is None:
@@ -116,6 +119,7 @@ class _LayerNorm(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy, dh=None):
         h, w, b, mean, rstd = ctx.saved_tensors
+        w, b = real_param(ctx, "w", w), real_param(ctx, "b", b)
         T, H = h.shape
         dy2 = dy.reshape(T, H).contiguous()
         dh2 = dh.reshape(T, H).contiguous() if dh is not None else None

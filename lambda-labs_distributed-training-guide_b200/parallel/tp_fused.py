@@ -19,6 +19,7 @@ from __future__ import annotations
 import torch
 
 from .. import _C
+from ..ops.dispatch import keep_params, real_param
 from ..ops.linear import EPI_ACCUM, EPI_NONE, _direct_grad, gemm
 from .peer import PeerComm
 
@@ -132,12 +133,14 @@ class _ColwiseFused(torch.autograd.Function):
         buf, epoch, _ = fz.gather_rows(x_local)
         y = fz.gemm_ag(buf, epoch, w)
         ctx.save_for_backward(x_local, w)
+        keep_params(ctx, w=w)
         ctx.fz = fz
         return y
 
     @staticmethod
     def backward(ctx, dy):
         x_local, w = ctx.saved_tensors
+        w = real_param(ctx, "w", w)
         fz = ctx.fz
         dy = dy.contiguous()
         # the gathered activations are needed again for dW: start re-gathering, overlap with the dX GEMM
@@ -154,12 +157,14 @@ class _RowwiseFused(torch.autograd.Function):
         x = x.contiguous()
         y_local = fz.gemm_rs(x, w)
         ctx.save_for_backward(x, w)
+        keep_params(ctx, w=w)
         ctx.fz = fz
         return y_local
 
     @staticmethod
     def backward(ctx, dy_local):
         x, w = ctx.saved_tensors
+        w = real_param(ctx, "w", w)
         fz = ctx.fz
         buf, epoch, done = fz.gather_rows(dy_local.contiguous())
         dx = fz.gemm_ag(buf, epoch, w, b_mn=True)          # dX = AG(dy) W
