@@ -64,6 +64,12 @@ def main():
         res[f"peer_rs_adamw_ms_b{mb}"] = timed(
             lambda: comm.reduce_scatter_adamw(p, m, v, full_sym, 1e-4, 0.9, 0.999, 1e-8, 0.01, 3, max_blocks=mb, nvls=False))
 
+    comm.rs_transport = "ce"
+    res["ce_rs_ms"] = timed(lambda: comm.reduce_scatter(out_shard, full_sym))
+    for mb in (148, 296):
+        res[f"ce_rs_adamw_ms_b{mb}"] = timed(
+            lambda: comm.reduce_scatter_adamw(p, m, v, full_sym, 1e-4, 0.9, 0.999, 1e-8, 0.01, 3, max_blocks=mb))
+    comm.rs_transport = "auto"
     res["nvls"] = bool(comm.has_nvls)
     if comm.has_nvls:
         ar_buf = comm.empty(numel)
@@ -108,6 +114,11 @@ def main():
             res[f"gemm+peer_agce_nvls_rs_ms_b{mb}"] = timed(overlapped(
                 lambda: (comm.all_gather(full, shard, copy_engine=True),
                          comm.reduce_scatter(out_shard, full_sym, max_blocks=mb, nvls=True))))
+    comm.rs_transport = "ce"
+    res["gemm+agce_ce_rsadamw_ms"] = timed(overlapped(
+        lambda: (comm.all_gather(full, shard, copy_engine=True),
+                 comm.reduce_scatter_adamw(p, m, v, full_sym, 1e-4, 0.9, 0.999, 1e-8, 0.01, 3))))
+    comm.rs_transport = "peer"
     for mb in (32, 148, 296):
         res[f"gemm+peer_agce_rsadamw_ms_b{mb}"] = timed(overlapped(
             lambda: (comm.all_gather(full, shard, copy_engine=True),

@@ -22,13 +22,12 @@ for s in ${STAGES:-peer comm bench tl}; do
       run ${TAG}_b_kernel $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer kernel
       B200TRAIN_FSDP_FUSED_AG=0 run ${TAG}_b_kernel_nofag $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer kernel ;;
     sweep)
-      B200TRAIN_RS_PIPE=0 run ${TAG}_b_stream_nopipe $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer stream
-      B200TRAIN_RS_PIPE=0 B200TRAIN_RS_BLOCKS=128 run ${TAG}_b_stream_nopipe128 $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer stream
-      B200TRAIN_RS_BLOCKS=148 run ${TAG}_b_stream148 $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer stream
-      B200TRAIN_RSADAM_BLOCKS=296 run ${TAG}_b_kernel296 $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer kernel
-      B200TRAIN_RSADAM_BLOCKS=64 run ${TAG}_b_kernel64 $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer kernel
-      B200TRAIN_SELF_COPY_BLOCKS=0 run ${TAG}_b_kernel_memcpy $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer kernel
-      B200TRAIN_SELF_COPY_BLOCKS=48 run ${TAG}_b_kernel_sc48 $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer kernel ;;
+      B200TRAIN_RS_TRANSPORT=peer run ${TAG}_b_kernel_peer $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer kernel
+      B200TRAIN_RS_TRANSPORT=ce run ${TAG}_b_kernel_ce $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer kernel
+      B200TRAIN_RS_TRANSPORT=ce B200TRAIN_RSADAM_BLOCKS=148 run ${TAG}_b_kernel_ce148 $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer kernel
+      B200TRAIN_RS_TRANSPORT=nvls run ${TAG}_b_kernel_nvls $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer kernel
+      B200TRAIN_RS_TRANSPORT=nvls run ${TAG}_b_stream_nvls $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer stream
+      B200TRAIN_RS_TRANSPORT=ce run ${TAG}_b_stream_ce $TR bench.py --gpus $N --steps 6 --warmup 3 --fuse-optimizer stream ;;
     tl) run ${TAG}_tl $TR bench/step_timeline.py --out gpurun_out/timeline_w${N}_${TAG}.json --windows 4 --fuse kernel
         grep -E "^---|kernel|Memcpy|us at" gpurun_out/${TAG}_tl.log | head -60 ;;
     b1) run ${TAG}_b1 python bench.py --steps 6 --warmup 3 ;;

@@ -532,6 +532,55 @@ rs_pipe_kernel(V4* __restrict__ out_shard, const V4* __restrict__ remote, const 
   }
 }
 
+
+// ---- copy-engine reduce-scatter (+ AdamW) -------------------------------------------------------------
+// Transport and arithmetic split by what each engine is good at. The peers' copies of this rank's slice
+// are PULLED by the copy engines into a local staging area (full NVLink rate, no SM, nothing resident
+// beside the GEMMs); cross-rank ordering is a one-warp signal kernel plus cuStreamWaitValue32 on the
+// local signal pad; the reduction is then a purely local, HBM-bound kernel that sums the W slices and --
+// fused -- applies AdamW to the owned shard, so the reduced gradient never exists in memory.
+//   b2_signal_peers      store `epoch` into slot [channel][rank] of every peer's pad (release, system scope)
+//   b2_stream_wait_pad   make the stream wait until every peer's slot of the LOCAL pad reached `epoch`
+//   b2_ce_pull_slices    staging[k-1] = slice `rank` of rank (rank+k)%W's full buffer, k = 1..W-1
+//   b2_reduce_adamw      p/m/v <- AdamW(scale * (g_local + sum staged))          (b2_reduce_slices: store)
+__global__ void signal_peers_kernel(PeerPtrs pads, int rank, int W, int channel, uint32_t epoch) {
+  __threadfence_system();
+  if (threadIdx.x < W && (int)threadIdx.x != rank) {
+    uint32_t* pad = static_cast<uint32_t*>(pads.p[threadIdx.x]);
+    st_flag_sys(pad + channel * kMaxPeers + rank, epoch);
+  }
+}
+
+constexpr int kMaxStaged = 15;
+struct StagedPtrs {
+  const V4* p[kMaxStaged];
+};
+
+template <bool kAdam>
+__global__ void __launch_bounds__(kCommThreads, 3)
+reduce_local_kernel(V4* __restrict__ out, const V4* __restrict__ g_local, StagedPtrs staged, int nstaged,
+                    size_t n16, float scale, AdamArgs adam) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) {
+    V4 pv, mv, vv;
+    if constexpr (kAdam) {
+      pv = ld_local(reinterpret_cast<const V4*>(adam.p) + i);
+      mv = ld_local(reinterpret_cast<const V4*>(adam.m) + i);
+      vv = ld_local(reinterpret_cast<const V4*>(adam.v) + i);
+    }
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    acc_bf16x8(acc, ld_local(g_local + i));
+    int k = 0;
+    for (; k + 1 < nstaged; k += 2) {  // two staged slices per trip: independent loads in flight
+      const V4 a = ld_local(staged.p[k] + i), b = ld_local(staged.p[k + 1] + i);
+      acc_bf16x8(acc, a);
+      acc_bf16x8(acc, b);
+    }
+    if (k < nstaged) acc_bf16x8(acc, ld_local(staged.p[k] + i));
+    rs_finish<kAdam>(acc, i, scale, out, adam, pv, mv, vv);
+  }
+}
+
 static bool rs_pipe_enabled() {
   static const bool on = [] {
     const char* e = getenv("B200TRAIN_RS_PIPE");
@@ -622,6 +671,101 @@ int b2_local_copy(void* dst, const void* src, size_t bytes, int blocks, cudaStre
     return 0;
   }
   B2_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, stream));
+  return 0;
+}
+
+int b2_signal_peers(void* const* pads, int rank, int W, int channel, unsigned int epoch,
+                    cudaStream_t stream) {
+  B2_REQUIRE(W >= 1 && W <= kMaxPeers, "peer collectives support up to %d ranks (got %d)", kMaxPeers, W);
+  B2_SIDE_KERNEL((signal_peers_kernel));
+  signal_peers_kernel<<<1, 32, 0, stream>>>(to_ptrs(pads, W), rank, W, channel, epoch);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+typedef CUresult (*CommWaitValue32Fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+static CommWaitValue32Fn comm_wait_value() {
+  static CommWaitValue32Fn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      return reinterpret_cast<CommWaitValue32Fn>(p);
+    return static_cast<CommWaitValue32Fn>(nullptr);
+  }();
+  return fn;
+}
+
+int b2_stream_wait_pad(const void* pad_local, int rank, int W, int channel, unsigned int epoch,
+                       cudaStream_t stream) {
+  CommWaitValue32Fn wf = comm_wait_value();
+  B2_REQUIRE(wf != nullptr, "cuStreamWaitValue32 entry point unavailable%s", "");
+  const uint32_t* pad = static_cast<const uint32_t*>(pad_local) + channel * kMaxPeers;
+  for (int q = 0; q < W; ++q) {
+    if (q == rank) continue;
+    CUresult r = wf((CUstream)stream, (CUdeviceptr)(pad + q), epoch, CU_STREAM_WAIT_VALUE_GEQ);
+    B2_REQUIRE(r == CUDA_SUCCESS, "cuStreamWaitValue32 failed: %d", (int)r);
+  }
+  return 0;
+}
+
+int b2_ce_pull_slices(void* staging, void* const* fulls, size_t shard_bytes, int rank, int W,
+                      cudaStream_t stream) {
+  B2_REQUIRE(W >= 1 && W <= kMaxPeers, "peer collectives support up to %d ranks (got %d)", kMaxPeers, W);
+  for (int k = 1; k < W; ++k) {
+    const int peer = (rank + k) % W;
+    B2_CUDA_CHECK(cudaMemcpyAsync(static_cast<char*>(staging) + (size_t)(k - 1) * shard_bytes,
+                                  static_cast<const char*>(fulls[peer]) + (size_t)rank * shard_bytes,
+                                  shard_bytes, cudaMemcpyDeviceToDevice, stream));
+  }
+  return 0;
+}
+
+static StagedPtrs staged_ptrs(const void* staging, size_t n16, int nstaged) {
+  StagedPtrs sp;
+  for (int k = 0; k < kMaxStaged; ++k)
+    sp.p[k] = k < nstaged ? static_cast<const V4*>(staging) + (size_t)k * n16 : nullptr;
+  return sp;
+}
+
+// out[shard_elems] = scale * (g_local + sum_k staging[k])   (bf16, fp32 accumulation)
+int b2_reduce_slices(void* out, const void* g_local, const void* staging, int nstaged, size_t shard_elems,
+                     float scale, int max_blocks, cudaStream_t stream) {
+  B2_REQUIRE(nstaged >= 0 && nstaged <= kMaxStaged, "reduce_slices: %d staged slices", nstaged);
+  B2_REQUIRE(shard_elems % 8 == 0, "reduce_slices: %zu elements is not a multiple of 8", shard_elems);
+  const size_t n16 = shard_elems / 8;
+  if (n16 == 0) return 0;
+  AdamArgs none = {};
+  B2_SIDE_KERNEL((reduce_local_kernel<false>));
+  reduce_local_kernel<false><<<clamp_blocks(n16, max_blocks > 0 ? max_blocks : 296), kCommThreads, 0, stream>>>(
+      static_cast<V4*>(out), static_cast<const V4*>(g_local), staged_ptrs(staging, n16, nstaged), nstaged, n16,
+      scale, none);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// AdamW on the owned shard with the gradient scale * (g_local + sum_k staging[k]) formed in registers.
+int b2_reduce_adamw(void* p, void* m, void* v, const void* g_local, const void* staging, int nstaged,
+                    size_t shard_elems, float grad_scale, float lr, float beta1, float beta2, float eps,
+                    float wd, int step, int max_blocks, cudaStream_t stream) {
+  B2_REQUIRE(nstaged >= 0 && nstaged <= kMaxStaged, "reduce_adamw: %d staged slices", nstaged);
+  B2_REQUIRE(shard_elems % 8 == 0, "reduce_adamw: %zu elements is not a multiple of 8", shard_elems);
+  const size_t n16 = shard_elems / 8;
+  if (n16 == 0) return 0;
+  AdamArgs a;
+  a.p = static_cast<__nv_bfloat16*>(p);
+  a.m = static_cast<__nv_bfloat16*>(m);
+  a.v = static_cast<__nv_bfloat16*>(v);
+  a.decay = 1.f - lr * wd;
+  a.beta1 = beta1;
+  a.beta2 = beta2;
+  a.eps = eps;
+  a.step_size = lr / (1.f - powf(beta1, (float)step));
+  a.inv_bc2_sqrt = 1.f / sqrtf(1.f - powf(beta2, (float)step));
+  B2_SIDE_KERNEL((reduce_local_kernel<true>));
+  reduce_local_kernel<true><<<clamp_blocks(n16, max_blocks > 0 ? max_blocks : 296), kCommThreads, 0, stream>>>(
+      nullptr, static_cast<const V4*>(g_local), staged_ptrs(staging, n16, nstaged), nstaged, n16, grad_scale, a);
+  B2_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
 

@@ -158,6 +158,22 @@ int b2_peer_all_gather(void* dst, void* const* srcs, size_t shard_bytes, int ran
 /* copy-engine gather; the rank's own shard is placed by `self_blocks` copy blocks (0: cudaMemcpyAsync) */
 int b2_peer_all_gather_ce(void* dst, void* const* srcs, size_t shard_bytes, int rank, int W,
                           int skip_self, int self_blocks, b2_stream_t stream);
+/* Copy-engine reduce-scatter: the peers' copies of this rank's slice are pulled into `staging` by the copy
+ * engines (b2_ce_pull_slices) between a signal / stream-wait handshake on the symmetric pad
+ * (b2_signal_peers + b2_stream_wait_pad: no kernel ever spins), then one local kernel sums the W slices
+ * and either stores the reduced shard (b2_reduce_slices) or applies AdamW to the owned parameters with the
+ * reduced gradient held in registers (b2_reduce_adamw). Reference: FSDP's reduce-scatter followed by a
+ * separate optimizer.step() (04-fully-sharded-data-parallel/train_llm.py:210,213). */
+int b2_signal_peers(void* const* pads, int rank, int W, int channel, unsigned int epoch, b2_stream_t stream);
+int b2_stream_wait_pad(const void* pad_local, int rank, int W, int channel, unsigned int epoch,
+                       b2_stream_t stream);
+int b2_ce_pull_slices(void* staging, void* const* fulls, size_t shard_bytes, int rank, int W,
+                      b2_stream_t stream);
+int b2_reduce_slices(void* out, const void* g_local, const void* staging, int nstaged, size_t shard_elems,
+                     float scale, int max_blocks, b2_stream_t stream);
+int b2_reduce_adamw(void* p, void* m, void* v, const void* g_local, const void* staging, int nstaged,
+                    size_t shard_elems, float grad_scale, float lr, float beta1, float beta2, float eps,
+                    float wd, int step, int max_blocks, b2_stream_t stream);
 /* bound (ms) of every cross-rank spin wait on the current device; past it the waiting kernel reports the
  * rank / channel / epoch it is stuck on and traps (a dead peer becomes a launch failure, not a hang) */
 int b2_comm_set_timeout_ms(unsigned long long ms);

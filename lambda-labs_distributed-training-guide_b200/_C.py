@@ -68,6 +68,11 @@ def _declare(lib):
         "b2_peer_all_gather": [P, P, Z, I, I, I, I, P],
         "b2_peer_all_gather_ce": [P, P, Z, I, I, I, I, P],
         "b2_comm_set_timeout_ms": [ctypes.c_ulonglong],
+        "b2_signal_peers": [P, I, I, I, ctypes.c_uint, P],
+        "b2_stream_wait_pad": [P, I, I, I, ctypes.c_uint, P],
+        "b2_ce_pull_slices": [P, P, Z, I, I, P],
+        "b2_reduce_slices": [P, P, P, I, Z, F, I, P],
+        "b2_reduce_adamw": [P, P, P, P, P, I, Z, F, F, F, F, F, F, I, I, P],
         "b2_peer_reduce_scatter": [P, P, Z, I, I, F, P, I, ctypes.c_uint, P, I, P],
         "b2_peer_reduce_scatter_adamw": [P, P, P, P, Z, I, I, F, F, F, F, F, F, I, P, I, ctypes.c_uint, P, I, P],
         "b2_peer_all_reduce": [P, Z, I, I, F, P, I, ctypes.c_uint, P, I, P],

@@ -33,7 +33,7 @@ from .comm import TorchComm
 
 _ARENA_MIN_BYTES = 256 << 20
 _ALIGN = 256
-CHAN_RS, CHAN_AR, CHAN_BARRIER = 0, 2, 4
+CHAN_RS, CHAN_AR, CHAN_BARRIER, CHAN_CE_IN, CHAN_CE_OUT = 0, 2, 4, 6, 7
 
 
 class _Arena:
@@ -79,10 +79,17 @@ class PeerComm(TorchComm):
         # blocks of the fused reduce-scatter + AdamW kernel: wide at 2 ranks (the peer slice is half the unit and
         # the update is HBM bound), thin through the switch (each rank's NVLink egress bounds it anyway)
         self.rsadam_blocks = int(os.environ.get("B200TRAIN_RSADAM_BLOCKS", "0"))
-        # the own shard of an all-gather is placed by this many copy blocks (0: cudaMemcpyAsync, which holds
-        # back the kernel launches of every other stream while it runs)
-        self.self_copy_blocks = int(os.environ.get("B200TRAIN_SELF_COPY_BLOCKS", "16"))
+        # the own shard of an all-gather is placed by this many copy blocks (0: cudaMemcpyAsync -- its copy kernel
+        # holds back the GEMM launches of the compute stream while it runs, 75 us per 218 MB, but copy blocks
+        # beside the GEMMs cost more: 200 vs 208-210 ms per Llama-8B step at 2 ranks)
+        self.self_copy_blocks = int(os.environ.get("B200TRAIN_SELF_COPY_BLOCKS", "0"))
         self.rs_blocks = int(os.environ.get("B200TRAIN_RS_BLOCKS", "64"))
+        # reduce-scatter transport. "ce": the copy engines pull the peers' slices into local staging and one
+        # local kernel reduces (+ AdamW) -- nothing resident beside the GEMMs but an HBM-bound kernel; "nvls":
+        # in-switch reduction by a thin kernel; "peer": SM loads from the peers. auto = ce at 2 ranks (measured
+        # 200 vs 208-216 ms per Llama-8B step against the SM kernels), nvls from 4 ranks when the fabric has it
+        self.rs_transport = os.environ.get("B200TRAIN_RS_TRANSPORT", "auto")
+        self._ce_staging = {}
         self.debug = os.environ.get("B200TRAIN_COMM_DEBUG", "0") == "1"
         self.debug_checks = 0
         pad = self.empty(64 * 16, torch.int32)   # signal pad: [channel][16 ranks]
@@ -196,11 +203,52 @@ class PeerComm(TorchComm):
             _C.call("b2_peer_all_gather", full.data_ptr(), srcs, n, self.rank, self.world, 1, max_blocks,
                     self._stream())
 
+    # ---- copy-engine reduce-scatter ---------------------------------------------------------------------
+    def _transport(self, nvls: Optional[bool], mc_available: bool) -> str:
+        if nvls is not None:
+            return "nvls" if (nvls and mc_available) else "peer"
+        t = self.rs_transport
+        if t == "auto":
+            t = "ce" if self.world == 2 else ("nvls" if (self.nvls and mc_available) else "ce")
+        if t == "nvls" and not mc_available:
+            t = "ce"
+        return t
+
+    def _ce_stage(self, nbytes: int) -> torch.Tensor:
+        key = self._stream()
+        buf = self._ce_staging.get(key)
+        if buf is None or buf.numel() < nbytes:
+            buf = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+            self._ce_staging[key] = buf
+        return buf
+
+    def _reduce_scatter_ce(self, fulls, shard_elems: int, local_slice: torch.Tensor, consume):
+        """Handshake + copy-engine pull of the peers' copies of this rank's slice, then ``consume(staging)``
+        (the local reduction kernel), then wait until the peers have finished pulling from this rank."""
+        st = self._stream()
+        e = self._epoch(CHAN_CE_IN)
+        nbytes = shard_elems * 2
+        _C.call("b2_signal_peers", self._pad_ptrs, self.rank, self.world, CHAN_CE_IN, e, st)
+        _C.call("b2_stream_wait_pad", self._pad.data_ptr(), self.rank, self.world, CHAN_CE_IN, e, st)
+        staging = self._ce_stage(nbytes * (self.world - 1))
+        _C.call("b2_ce_pull_slices", staging.data_ptr(), fulls, nbytes, self.rank, self.world, st)
+        _C.call("b2_signal_peers", self._pad_ptrs, self.rank, self.world, CHAN_CE_OUT, e, st)
+        consume(staging)
+        _C.call("b2_stream_wait_pad", self._pad.data_ptr(), self.rank, self.world, CHAN_CE_OUT, e, st)
+
     def _reduce_scatter(self, shard, full, average=True, max_blocks: int = 0, nvls: Optional[bool] = None):
         fulls = self._peer_array(full) if self.world > 1 else None
         if fulls is None or shard.dtype != torch.bfloat16:
             return TorchComm.reduce_scatter(self, shard, full, average)
         mc = self._mc_ptr(full) if (self.nvls if nvls is None else nvls) else 0
+        if self._transport(nvls, bool(self._mc_ptr(full))) == "ce":
+            n = shard.numel()
+            local = full[self.rank * n:(self.rank + 1) * n]
+            scale = (1.0 / self.world) if average else 1.0
+            self._reduce_scatter_ce(fulls, n, local, lambda stg: _C.call(
+                "b2_reduce_slices", shard.data_ptr(), local.data_ptr(), stg.data_ptr(), self.world - 1, n, scale,
+                max_blocks, self._stream()))
+            return
         if mc:
             _C.call("b2_nvls_reduce_scatter", shard.data_ptr(), mc, shard.numel(), self.rank, self.world,
                     (1.0 / self.world) if average else 1.0, self._pad_ptrs, CHAN_RS, self._epoch(CHAN_RS),
@@ -218,6 +266,15 @@ class PeerComm(TorchComm):
         if fulls is None or p.dtype != torch.bfloat16:
             return False
         mc = self._mc_ptr(full_grad) if (self.nvls if nvls is None else nvls) else 0
+        if self._transport(nvls, bool(self._mc_ptr(full_grad))) == "ce":
+            n = p.numel()
+            local = full_grad[self.rank * n:(self.rank + 1) * n]
+            scale = (1.0 / self.world) if average else 1.0
+            self._reduce_scatter_ce(fulls, n, local, lambda stg: _C.call(
+                "b2_reduce_adamw", p.data_ptr(), m.data_ptr(), v.data_ptr(), local.data_ptr(), stg.data_ptr(),
+                self.world - 1, n, scale, lr, beta1, beta2, eps, wd, step, max_blocks or self.rsadam_blocks,
+                self._stream()))
+            return True
         max_blocks = max_blocks or self.rsadam_blocks or (32 if mc else 148)
         if mc:
             _C.call("b2_nvls_reduce_scatter_adamw", p.data_ptr(), m.data_ptr(), v.data_ptr(), mc, p.numel(),

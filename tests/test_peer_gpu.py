@@ -17,7 +17,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, ret, nvls=False):
+def _worker(rank, world, port, ret, nvls=False, transport=None):
     import torch.distributed as dist
 
     os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
@@ -34,6 +34,9 @@ def _worker(rank, world, port, ret, nvls=False):
                 ret[rank] = {"skip": 1.0}
                 return
             comm.nvls = True       # reductions go through multimem.ld_reduce / multimem.st
+            comm.rs_transport = "nvls"
+        elif transport is not None:
+            comm.rs_transport = transport   # "ce": copy-engine pull + local reduce, "peer": SM loads from the peers
         n = 1 << 20
         g = torch.Generator(device="cuda").manual_seed(100 + rank)
         errs = {}
@@ -93,6 +96,22 @@ def test_peer_collectives_match_nccl():
     world = min(torch.cuda.device_count(), 8)
     ret = mp.Manager().dict()
     mp.spawn(_worker, args=(world, _free_port(), ret), nprocs=world, join=True)
+    for r in range(world):
+        for k, e in ret[r].items():
+            tol = 2e-3 if k.startswith("rsadam") else 2e-2
+            assert e <= tol, (r, k, e, dict(ret[r]))
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs at least 2 GPUs")
+@pytest.mark.parametrize("transport", ["ce", "peer"])
+def test_reduce_scatter_transports_match_nccl(transport):
+    """Every reduce-scatter transport (copy-engine pull + local reduce / AdamW, SM loads from the peers)
+    against the same oracle, whatever the automatic choice for this world size is."""
+    import torch.multiprocessing as mp
+
+    world = min(torch.cuda.device_count(), 8)
+    ret = mp.Manager().dict()
+    mp.spawn(_worker, args=(world, _free_port(), ret, False, transport), nprocs=world, join=True)
     for r in range(world):
         for k, e in ret[r].items():
             tol = 2e-3 if k.startswith("rsadam") else 2e-2
