@@ -427,8 +427,55 @@ static EncodeTiledFn get_encode() {
   return fn;
 }
 
+// Encoded tensor maps are cached: a training step launches ~1,500 GEMMs on buffers whose addresses and
+// shapes recur every step (flat parameter / gradient buffers, the caching allocator's activation blocks),
+// and cuTensorMapEncodeTiled is a driver call per map. The key is everything the encoding depends on.
+struct TmapKey {
+  const void* ptr;
+  uint64_t rows, cols, stride;
+  uint32_t box_rows, box_cols, kind;
+  bool operator==(const TmapKey& o) const {
+    return ptr == o.ptr && rows == o.rows && cols == o.cols && stride == o.stride &&
+           box_rows == o.box_rows && box_cols == o.box_cols && kind == o.kind;
+  }
+};
+struct TmapKeyHash {
+  size_t operator()(const TmapKey& k) const {
+    uint64_t h = reinterpret_cast<uint64_t>(k.ptr) * 0x9E3779B97F4A7C15ull;
+    h ^= (k.rows + 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2));
+    h ^= (k.cols + 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2));
+    h ^= (k.stride + 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2));
+    h ^= (((uint64_t)k.box_rows << 40) ^ ((uint64_t)k.box_cols << 8) ^ k.kind) * 0xC2B2AE3D27D4EB4Full;
+    return (size_t)h;
+  }
+};
+static thread_local std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> g_tmap_cache;
+constexpr size_t kTmapCacheMax = 8192;
+
+static bool tmap_cache_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("B200TRAIN_TMAP_CACHE");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
+static bool tmap_lookup(const TmapKey& k, CUtensorMap* out) {
+  if (!tmap_cache_enabled()) return false;
+  auto it = g_tmap_cache.find(k);
+  if (it == g_tmap_cache.end()) return false;
+  *out = it->second;
+  return true;
+}
+static void tmap_store(const TmapKey& k, const CUtensorMap& m) {
+  if (!tmap_cache_enabled()) return;
+  if (g_tmap_cache.size() >= kTmapCacheMax) g_tmap_cache.clear();
+  g_tmap_cache.emplace(k, m);
+}
+
 int make_tmap_2d_bf16(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols,
                       uint64_t row_stride_elems, uint32_t box_rows, uint32_t box_cols) {
+  const TmapKey key{ptr, rows, cols, row_stride_elems, box_rows, box_cols, 0u};
+  if (tmap_lookup(key, out)) return 0;
   EncodeTiledFn enc = get_encode();
   B2_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
   B2_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "TMA base %p not 16B aligned", ptr);
@@ -444,11 +491,14 @@ int make_tmap_2d_bf16(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t
   B2_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(2d) failed: %d (rows=%llu cols=%llu ld=%llu)",
              (int)r, (unsigned long long)rows, (unsigned long long)cols,
              (unsigned long long)row_stride_elems);
+  tmap_store(key, *out);
   return 0;
 }
 
 int make_tmap_mn_bf16(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols,
                       uint64_t row_stride_elems, uint32_t box_rows, uint32_t box_chunks) {
+  const TmapKey key{ptr, rows, cols, row_stride_elems, box_rows, box_chunks, 1u};
+  if (tmap_lookup(key, out)) return 0;
   EncodeTiledFn enc = get_encode();
   B2_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
   B2_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "TMA base %p not 16B aligned", ptr);
@@ -463,11 +513,14 @@ int make_tmap_mn_bf16(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t
                    box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   B2_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(3d) failed: %d", (int)r);
+  tmap_store(key, *out);
   return 0;
 }
 
 int make_tmap_2d_f32(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols,
                      uint64_t row_stride_elems, uint32_t box_rows, uint32_t box_cols) {
+  const TmapKey key{ptr, rows, cols, row_stride_elems, box_rows, box_cols, 2u};
+  if (tmap_lookup(key, out)) return 0;
   EncodeTiledFn enc = get_encode();
   B2_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
   B2_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "TMA base %p not 16B aligned", ptr);
@@ -480,17 +533,17 @@ int make_tmap_2d_f32(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t 
                    box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   B2_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(f32) failed: %d", (int)r);
+  tmap_store(key, *out);
   return 0;
 }
 
 int sm_count() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-  }
-  return n;
+  static int n[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (n[dev] == 0) cudaDeviceGetAttribute(&n[dev], cudaDevAttrMultiProcessorCount, dev);
+  return n[dev];
 }
 
 static bool tail_split_enabled() {
@@ -522,11 +575,14 @@ static int launch_gemm(void* C, const void* A, const void* B, int M, int N, int 
   }
 
   auto kern = gemm_bf16_kernel<kCta, kAK, kBK, kEpi, BN, Fuse>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static bool attr_set[64] = {};   // per device: a process may drive several GPUs
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (!attr_set[dev]) {
     B2_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        Cfg::kSmemBytes));
-    attr_set = true;
+    attr_set[dev] = true;
   }
   const int tile_m = BM * kCta;
   const int num_tiles = ((M + tile_m - 1) / tile_m) * ((N + BN - 1) / BN);

@@ -83,6 +83,10 @@ def get_parser(chapter: str = "generic") -> argparse.ArgumentParser:
     p.add_argument("--activation-checkpointing", default=None, choices=["on", "off"])
     p.add_argument("--grad-accum-steps", default=1, type=int)
     p.add_argument("--zero1", default=None, choices=["on", "off"], help="shard optimizer state (DDP)")
+    p.add_argument("--fuse-optimizer", default="kernel", choices=["kernel", "stream", "off"],
+                   help="FSDP: 'kernel' reduces a unit's gradient and applies AdamW to the owned shard in one kernel "
+                        "inside backward (the 'update' phase then only steps the schedule); 'stream' queues a separate "
+                        "AdamW launch behind the reduce-scatter; 'off' updates after backward like the reference")
     p.add_argument("--deterministic", action="store_true")
     p.add_argument("--packed", action="store_true", help="packed rows: derive position ids per document")
     p.add_argument("--max-steps", default=None, type=int, help="stop after this many optimizer steps")
@@ -169,6 +173,8 @@ def main(chapter: str = "generic", argv=None):
     if strategy_name == "fsdp":
         kw.update(cpu_offload=getattr(args, "cpu_offload", "off") == "on", activation_checkpointing=act == "on",
                   numel_to_wrap=getattr(args, "numel_to_wrap", 0))
+        if device.type == "cuda" and args.grad_accum_steps <= 1:
+            kw.update(fuse_optimizer=False if args.fuse_optimizer == "off" else args.fuse_optimizer)
         if sharding == "shard_grad_op":  # parameters stay gathered between forward and backward (ZeRO-2)
             kw.update(reshard_after_forward=False)
         elif sharding == "hybrid_shard":

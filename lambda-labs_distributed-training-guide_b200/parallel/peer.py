@@ -272,7 +272,7 @@ class PeerComm(TorchComm):
             scale = (1.0 / self.world) if average else 1.0
             self._reduce_scatter_ce(fulls, n, local, lambda stg: _C.call(
                 "b2_reduce_adamw", p.data_ptr(), m.data_ptr(), v.data_ptr(), local.data_ptr(), stg.data_ptr(),
-                self.world - 1, n, scale, lr, beta1, beta2, eps, wd, step, max_blocks or self.rsadam_blocks,
+                self.world - 1, n, scale, lr, beta1, beta2, eps, wd, step, max_blocks or self.rsadam_blocks or 148,
                 self._stream()))
             return True
         max_blocks = max_blocks or self.rsadam_blocks or (32 if mc else 148)

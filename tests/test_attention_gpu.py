@@ -18,6 +18,12 @@ CASES = [
     ([300, 77, 515], 4, 1, 128),
     ([512], 4, 4, 64),
     ([130, 1000], 6, 2, 64),
+    # the benchmarked shapes: Llama-3.1-8B heads (32 query : 8 key/value, head_dim 128) at 4096 and 8192 tokens
+    # (32 / 64 key blocks per query block: the long-row and tail paths), GPT-2 heads at 2048
+    ([4096], 32, 8, 128),
+    ([8192], 32, 8, 128),
+    ([2048], 12, 12, 64),
+    ([3000, 1096, 4096], 8, 2, 128),
 ]
 
 

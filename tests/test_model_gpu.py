@@ -1,6 +1,6 @@
-"""End-to-end parity on the GPU: the kernel path vs the same model evaluated with PyTorch reference
-math (``ops.dispatch._FORCE_REFERENCE``), forward loss and every parameter gradient; then a few
-optimizer steps must drive the loss down."""
+"""End-to-end parity on the GPU: the bf16 kernel path vs an fp32 copy of the same model (same weights,
+widened) evaluated with the PyTorch reference math (``ops.dispatch._FORCE_REFERENCE``): forward loss and
+every parameter gradient; then a few optimizer steps must drive the loss down."""
 import pytest
 import torch
 
@@ -26,9 +26,15 @@ def test_model_matches_reference_math(name):
     ids = torch.randint(0, cfg.vocab_size, (2, S), device="cuda")
     batch = {"input_ids": ids, "labels": ids}
     loss_k, grads_k = _run(model, batch)
+    # the oracle: the same weights in fp32, PyTorch reference math in fp32 end to end
+    model32 = build_model(cfg, device="cuda", seed=0, dtype=torch.float32)
+    with torch.no_grad():
+        src = dict(model.named_parameters())
+        for n, p in model32.named_parameters():
+            p.copy_(src[n].float())
     dispatch._FORCE_REFERENCE = True
     try:
-        loss_r, grads_r = _run(model, batch)
+        loss_r, grads_r = _run(model32, batch)
     finally:
         dispatch._FORCE_REFERENCE = False
     assert abs(loss_k - loss_r) < 3e-2, (loss_k, loss_r)
@@ -37,6 +43,8 @@ def test_model_matches_reference_math(name):
         denom = b.abs().max().item() + 1e-6
         rel = (a - b).abs().max().item() / denom
         assert rel < 0.08, f"{n}: rel err {rel}"
+        cos = torch.nn.functional.cosine_similarity(a.flatten(), b.flatten(), dim=0).item()
+        assert cos > 0.995, f"{n}: cosine {cos}"
 
 
 def test_training_reduces_loss():
