@@ -86,8 +86,7 @@ class PeerComm(TorchComm):
         self.rs_blocks = int(os.environ.get("B200TRAIN_RS_BLOCKS", "64"))
         # reduce-scatter transport. "ce": the copy engines pull the peers' slices into local staging and one
         # local kernel reduces (+ AdamW) -- nothing resident beside the GEMMs but an HBM-bound kernel; "nvls":
-        # in-switch reduction by a thin kernel; "peer": SM loads from the peers. auto = ce at 2 ranks (measured
-        # 200 vs 208-216 ms per Llama-8B step against the SM kernels), nvls from 4 ranks when the fabric has it
+        # in-switch reduction by a thin kernel; "peer": SM loads from the peers. auto: see _transport
         self.rs_transport = os.environ.get("B200TRAIN_RS_TRANSPORT", "auto")
         self._ce_staging = {}
         self.debug = os.environ.get("B200TRAIN_COMM_DEBUG", "0") == "1"
@@ -204,12 +203,19 @@ class PeerComm(TorchComm):
                     self._stream())
 
     # ---- copy-engine reduce-scatter ---------------------------------------------------------------------
-    def _transport(self, nvls: Optional[bool], mc_available: bool) -> str:
+    def _transport(self, nvls: Optional[bool], mc_available: bool, fused: bool = False) -> str:
         if nvls is not None:
             return "nvls" if (nvls and mc_available) else "peer"
         t = self.rs_transport
         if t == "auto":
-            t = "ce" if self.world == 2 else ("nvls" if (self.nvls and mc_available) else "ce")
+            # fused with AdamW: copy-engine pull + local reduce-update at every world size (Llama-8B step on 4
+            # GPUs: 198.4 ms, against 209.2 ms with the in-switch load feeding AdamW in one thin kernel and
+            # 198.6 ms with in-switch reduce-scatter then a separate AdamW launch). Plain reduce-scatter: in-switch
+            # from 4 ranks, copy engine at 2.
+            if fused:
+                t = "ce"
+            else:
+                t = "ce" if self.world == 2 else ("nvls" if (self.nvls and mc_available) else "ce")
         if t == "nvls" and not mc_available:
             t = "ce"
         return t
@@ -266,7 +272,7 @@ class PeerComm(TorchComm):
         if fulls is None or p.dtype != torch.bfloat16:
             return False
         mc = self._mc_ptr(full_grad) if (self.nvls if nvls is None else nvls) else 0
-        if self._transport(nvls, bool(self._mc_ptr(full_grad))) == "ce":
+        if self._transport(nvls, bool(self._mc_ptr(full_grad)), fused=True) == "ce":
             n = p.numel()
             local = full_grad[self.rank * n:(self.rank + 1) * n]
             scale = (1.0 / self.world) if average else 1.0
