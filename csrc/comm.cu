@@ -556,7 +556,10 @@ struct StagedPtrs {
   const V4* p[kMaxStaged];
 };
 
-template <bool kAdam>
+// NST staged slices known at compile time (0 = runtime count): every load of a vector -- optimizer state,
+// own slice, all staged slices -- is issued before the first use, one memory round trip per vector
+// instead of one per pair of slices.
+template <bool kAdam, int NST>
 __global__ void __launch_bounds__(kCommThreads, 3)
 reduce_local_kernel(V4* __restrict__ out, const V4* __restrict__ g_local, StagedPtrs staged, int nstaged,
                     size_t n16, float scale, AdamArgs adam) {
@@ -569,16 +572,49 @@ reduce_local_kernel(V4* __restrict__ out, const V4* __restrict__ g_local, Staged
       vv = ld_local(reinterpret_cast<const V4*>(adam.v) + i);
     }
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    acc_bf16x8(acc, ld_local(g_local + i));
-    int k = 0;
-    for (; k + 1 < nstaged; k += 2) {  // two staged slices per trip: independent loads in flight
-      const V4 a = ld_local(staged.p[k] + i), b = ld_local(staged.p[k + 1] + i);
-      acc_bf16x8(acc, a);
-      acc_bf16x8(acc, b);
+    const V4 gl = ld_local(g_local + i);
+    if constexpr (NST > 0) {
+      V4 st[NST];
+#pragma unroll
+      for (int k = 0; k < NST; ++k) st[k] = ld_local(staged.p[k] + i);
+      acc_bf16x8(acc, gl);
+#pragma unroll
+      for (int k = 0; k < NST; ++k) acc_bf16x8(acc, st[k]);
+    } else {
+      acc_bf16x8(acc, gl);
+      int k = 0;
+      for (; k + 1 < nstaged; k += 2) {
+        const V4 a = ld_local(staged.p[k] + i), b = ld_local(staged.p[k + 1] + i);
+        acc_bf16x8(acc, a);
+        acc_bf16x8(acc, b);
+      }
+      if (k < nstaged) acc_bf16x8(acc, ld_local(staged.p[k] + i));
     }
-    if (k < nstaged) acc_bf16x8(acc, ld_local(staged.p[k] + i));
     rs_finish<kAdam>(acc, i, scale, out, adam, pv, mv, vv);
   }
+}
+
+template <bool kAdam>
+static int launch_reduce_local(int blocks, cudaStream_t stream, V4* out, const V4* g_local, StagedPtrs sp,
+                               int nstaged, size_t n16, float scale, const AdamArgs& a) {
+#define B2_RL_CASE(N)                                                                                  \
+  case N:                                                                                              \
+    B2_SIDE_KERNEL((reduce_local_kernel<kAdam, N>));                                                   \
+    reduce_local_kernel<kAdam, N><<<blocks, kCommThreads, 0, stream>>>(out, g_local, sp, nstaged, n16, \
+                                                                        scale, a);                     \
+    break;
+  switch (nstaged) {
+    B2_RL_CASE(1)
+    B2_RL_CASE(3)
+    B2_RL_CASE(7)
+    default:
+      B2_SIDE_KERNEL((reduce_local_kernel<kAdam, 0>));
+      reduce_local_kernel<kAdam, 0><<<blocks, kCommThreads, 0, stream>>>(out, g_local, sp, nstaged, n16,
+                                                                         scale, a);
+  }
+#undef B2_RL_CASE
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
 }
 
 static bool rs_pipe_enabled() {
@@ -736,12 +772,9 @@ int b2_reduce_slices(void* out, const void* g_local, const void* staging, int ns
   const size_t n16 = shard_elems / 8;
   if (n16 == 0) return 0;
   AdamArgs none = {};
-  B2_SIDE_KERNEL((reduce_local_kernel<false>));
-  reduce_local_kernel<false><<<clamp_blocks(n16, max_blocks > 0 ? max_blocks : 296), kCommThreads, 0, stream>>>(
-      static_cast<V4*>(out), static_cast<const V4*>(g_local), staged_ptrs(staging, n16, nstaged), nstaged, n16,
-      scale, none);
-  B2_CUDA_CHECK(cudaGetLastError());
-  return 0;
+  return launch_reduce_local<false>(clamp_blocks(n16, max_blocks > 0 ? max_blocks : 296), stream,
+                                    static_cast<V4*>(out), static_cast<const V4*>(g_local),
+                                    staged_ptrs(staging, n16, nstaged), nstaged, n16, scale, none);
 }
 
 // AdamW on the owned shard with the gradient scale * (g_local + sum_k staging[k]) formed in registers.
@@ -762,11 +795,9 @@ int b2_reduce_adamw(void* p, void* m, void* v, const void* g_local, const void* 
   a.eps = eps;
   a.step_size = lr / (1.f - powf(beta1, (float)step));
   a.inv_bc2_sqrt = 1.f / sqrtf(1.f - powf(beta2, (float)step));
-  B2_SIDE_KERNEL((reduce_local_kernel<true>));
-  reduce_local_kernel<true><<<clamp_blocks(n16, max_blocks > 0 ? max_blocks : 296), kCommThreads, 0, stream>>>(
-      nullptr, static_cast<const V4*>(g_local), staged_ptrs(staging, n16, nstaged), nstaged, n16, grad_scale, a);
-  B2_CUDA_CHECK(cudaGetLastError());
-  return 0;
+  return launch_reduce_local<true>(clamp_blocks(n16, max_blocks > 0 ? max_blocks : 296), stream, nullptr,
+                                   static_cast<const V4*>(g_local), staged_ptrs(staging, n16, nstaged), nstaged,
+                                   n16, grad_scale, a);
 }
 
 // Spin bound of every cross-rank wait in this file (milliseconds; applies to the current device).

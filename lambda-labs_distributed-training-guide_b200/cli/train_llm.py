@@ -83,10 +83,11 @@ def get_parser(chapter: str = "generic") -> argparse.ArgumentParser:
     p.add_argument("--activation-checkpointing", default=None, choices=["on", "off"])
     p.add_argument("--grad-accum-steps", default=1, type=int)
     p.add_argument("--zero1", default=None, choices=["on", "off"], help="shard optimizer state (DDP)")
-    p.add_argument("--fuse-optimizer", default="kernel", choices=["kernel", "stream", "off"],
+    p.add_argument("--fuse-optimizer", default="auto", choices=["auto", "kernel", "stream", "off"],
                    help="FSDP: 'kernel' reduces a unit's gradient and applies AdamW to the owned shard in one kernel "
                         "inside backward (the 'update' phase then only steps the schedule); 'stream' queues a separate "
-                        "AdamW launch behind the reduce-scatter; 'off' updates after backward like the reference")
+                        "AdamW launch behind the reduce-scatter; 'off' updates after backward like the reference; 'auto' picks "
+                        "'kernel' up to 4 ranks and 'stream' from 8")
     p.add_argument("--deterministic", action="store_true")
     p.add_argument("--packed", action="store_true", help="packed rows: derive position ids per document")
     p.add_argument("--max-steps", default=None, type=int, help="stop after this many optimizer steps")

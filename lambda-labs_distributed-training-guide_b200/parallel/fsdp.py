@@ -93,8 +93,14 @@ class FSDP(Strategy):
         self.W, self.R = self.comm.world, self.comm.rank
         self.cpu_offload = cpu_offload
         self.act_ckpt = activation_checkpointing
-        # fuse_optimizer: False | True / "kernel" (reduce-scatter + AdamW in one peer-memory kernel when the
-        # communicator provides it) | "stream" (AdamW kernel queued right behind the reduce-scatter)
+        # fuse_optimizer: False | True / "kernel" (gradient reduce-scatter + AdamW on the owned shard as one
+        # fused operation when the communicator provides it: copy-engine pull of the peers' slices, one local
+        # kernel that reduces and updates) | "stream" (AdamW kernel queued right behind the reduce-scatter) |
+        # "auto": "kernel" up to 4 ranks, "stream" from 8 (measured per Llama-8B step, kernel / stream:
+        # 2 GPUs 197.8-199.6 / 202.7 ms, 4 GPUs 198.4 / 198.6 ms, 8 GPUs 201.0 / 196.9 ms: with 7 staged
+        # slices per unit the in-switch reduction that feeds a separate AdamW moves fewer HBM bytes)
+        if fuse_optimizer == "auto":
+            fuse_optimizer = "stream" if self.W >= 8 else "kernel"
         self.fuse_optimizer = fuse_optimizer and not cpu_offload
         self.fuse_in_kernel = fuse_optimizer in (True, "kernel")
         self.is_cuda = self.device.type == "cuda"
