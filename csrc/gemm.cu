@@ -29,12 +29,22 @@ constexpr int kEpiStageBytes = BM * kEpiChunk * 2;  // 16 KB
 constexpr int kNumEpiStages = 2;
 constexpr int kSmemBudget = 232448 - 1024;  // max dynamic smem minus alignment slack
 
-enum Epilogue { EPI_NONE = 0, EPI_BIAS = 1, EPI_BIAS_GELU = 2, EPI_ACCUM = 3 };
+// EPI_DSWIGLU: C is d(gate|up) [M, 2I] of a SwiGLU whose output gradient dh [M, I] is THIS GEMM's
+//   result (down-projection dgrad): each dh tile is combined in registers with the saved gate / up
+//   pre-activations and stored as dgate (columns j) and dup (columns I + j); dh is never written.
+// EPI_ROPE: rotary embedding applied to the first `rope_heads` 128-wide heads of each output row
+//   (q and k heads of a fused QKV projection) before the store; the remaining heads (v) pass through.
+enum Epilogue { EPI_NONE = 0, EPI_BIAS = 1, EPI_BIAS_GELU = 2, EPI_ACCUM = 3, EPI_DSWIGLU = 4, EPI_ROPE = 5 };
 
 struct EpiArgs {
   const __nv_bfloat16* bias;  // [N] (EPI_BIAS*)
   const __nv_bfloat16* c_old; // [M, ldc] (EPI_ACCUM)
   int ldc;
+  const __nv_bfloat16* gu;    // [M, ld_gu] saved gate | up (EPI_DSWIGLU)
+  int ld_gu, inter;           // row stride of gu, I
+  const __nv_bfloat16 *cosT, *sinT;  // [max_pos, 128] (EPI_ROPE)
+  const int* pos;             // [M] positions or nullptr (row % seq_len)
+  int rope_heads, seq_len;
 };
 
 // ---- fused compute + collective variants (tensor parallel, see b2_gemm_ag / b2_gemm_rs) ----------
@@ -56,14 +66,15 @@ struct FuseScatterC {
   CUtensorMap cm[kMaxTP];  // cm[r]: rank r's slot `rank`, shape [rows_per_rank, N]
   int rows_per_rank, rank, W;
 };
-// kFuse = 3 (FSDP parameter all-gather -> GEMM): the weight (B operand) is a slice of a flat unit buffer
-//   that the copy engines are still filling from the peers' shards, chunk by chunk, while the kernel
-//   runs; chunk c is present once flags[c] >= epoch (the gathering stream writes the flag after the
-//   chunk's copy). The TMA producer waits for the chunks that hold a tile's weight rows before the
-//   tile's first load, and the n-blocks are visited starting with the rows that arrive first (the
-//   rank's own shard, then the peers in the order they are pulled). All loads are from local memory.
-struct FuseBWait {
-  const uint32_t* flags;
+// FSDP parameter all-gather -> GEMM (every variant of the kernel, switched on at run time by
+//   gw.flags != nullptr): the weight (B operand) is a slice of a flat unit buffer that the copy engines are
+//   still filling from the peers' shards, chunk by chunk, while the kernel runs; chunk c is present once
+//   flags[c] >= epoch (the gathering stream writes the flag after the chunk's copy). The TMA producer waits
+//   for the chunks that hold a tile's weight rows before the tile's first load, and the n-blocks are
+//   visited starting with the rows that arrive first (the rank's own shard, then the peers in the order
+//   they are pulled). All loads are from local memory.
+struct GatherWaitArgs {
+  const uint32_t* flags;  // nullptr: B is complete, no waiting
   uint32_t epoch;
   long long b_off;        // element offset of B[0][0] in the flat buffer the flags describe
   long long chunk_elems;  // elements per flag
@@ -72,8 +83,17 @@ struct FuseBWait {
   int ldb;
   unsigned long long timeout_ns;
 };
+// kFuse = 4 (gate/up projection + SwiGLU): B is the stacked [2I, K] weight. The two CTAs of a pair load
+//   DIFFERENT row blocks of it -- CTA 0 the gate rows [j, j+128), CTA 1 the up rows [I+j, I+j+128) -- so
+//   the 256-column accumulator of a tile holds gate in columns 0..127 and up in 128..255 for the same 128
+//   outputs; the epilogue stores both pre-activations (backward needs them) into C [M, 2I] and
+//   h = silu(gate) * up into H [M, I] through the tensor map `th`.
+struct FuseSwiglu {
+  CUtensorMap th;
+  int inter;
+};
 template <class F> struct FuseKind { static constexpr int v = 0; };
-template <> struct FuseKind<FuseBWait> { static constexpr int v = 3; };
+template <> struct FuseKind<FuseSwiglu> { static constexpr int v = 4; };
 template <> struct FuseKind<FuseAWait> { static constexpr int v = 1; };
 template <> struct FuseKind<FuseScatterC> { static constexpr int v = 2; };
 
@@ -98,11 +118,11 @@ __device__ __forceinline__ float gelu_new(float x) {
 }
 
 template <int kCta, bool kAK, bool kBK, int kEpi, int BN, class Fuse = NoFuse>
-__global__ void __launch_bounds__(256, 1)
+__global__ void __maxnreg__(168)   // 256 threads x 168 registers leave room for one 256 x 80 side-stream block
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmC, int M, int N, int K, EpiArgs epi,
                  const __grid_constant__ Fuse fuse, const __grid_constant__ CUtensorMap tmBh,
-                 int split_from) {
+                 int split_from, const __grid_constant__ GatherWaitArgs gw) {
   using Cfg = GemmCfg<kCta, BN>;
   constexpr int kFuse = FuseKind<Fuse>::v;
   constexpr int kStages = Cfg::kStages;
@@ -150,7 +170,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   // ---- persistent tile schedule (identical in every role) ----
   const int tile_m = BM * kCta;
   const int num_m = (M + tile_m - 1) / tile_m;
-  const int num_n = (N + BN - 1) / BN;
+  int num_n_ = (N + BN - 1) / BN;
+  if constexpr (kFuse == 4) num_n_ = fuse.inter / (BN / 2);   // one tile = 128 gate + 128 up columns
+  const int num_n = num_n_;
   const int num_tiles = num_m * num_n;
   const int num_k = (K + BK - 1) / BK;
   const int num_workers = gridDim.x / kCta;
@@ -181,10 +203,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int blocks_per_rank = fuse.rows_per_rank / (BM * kCta);
       mb = (mb + fuse.rank * blocks_per_rank) % num_m;
     }
-    if constexpr (kFuse == 3) {
-      nb += fuse.nb_start;
-      if (nb >= num_n) nb -= num_n;
-    }
+    nb += gw.nb_start;   // 0 unless the weight is still being gathered
+    if (nb >= num_n) nb -= num_n;
   };
 
   if (warp == 0) {
@@ -198,7 +218,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         unit_tile(u, t, n_off, bn_cur);
         tile_coord(t, mb, nb);
         const int m0 = mb * tile_m + (int)cta_rank * BM;
-        const int n0 = nb * BN + n_off + (int)cta_rank * (bn_cur / kCta);
+        int n0 = nb * BN + n_off + (int)cta_rank * (bn_cur / kCta);
+        if constexpr (kFuse == 4) n0 = nb * (BN / 2) + (int)cta_rank * fuse.inter;
         const CUtensorMap* tb = bn_cur == BN ? &tmB : &tmBh;
         const uint32_t stage_tx = (uint32_t)(Cfg::kABytes + (bn_cur / kCta) * BK * 2) * kCta;
         if constexpr (kFuse == 1) {
@@ -210,24 +231,24 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             asm volatile("fence.proxy.async.global;" ::: "memory");
           }
         }
-        if constexpr (kFuse == 3) {
+        if (gw.flags != nullptr) {
           // flat range of the weight rows this CTA loads for the tile (K-major: rows n0.. of length
           // ldb; MN-major: the tile's columns run through every row, i.e. the whole matrix)
           long long lo, hi;
           if constexpr (kBK) {
-            lo = fuse.b_off + (long long)n0 * fuse.ldb;
-            hi = fuse.b_off + (long long)(min(n0 + bn_cur / kCta, N) - 1) * fuse.ldb + K;
+            lo = gw.b_off + (long long)n0 * gw.ldb;
+            hi = gw.b_off + (long long)(min(n0 + bn_cur / kCta, kFuse == 4 ? 2 * N : N) - 1) * gw.ldb + K;
           } else {
-            lo = fuse.b_off;
-            hi = fuse.b_off + (long long)(K - 1) * fuse.ldb + N;
+            lo = gw.b_off;
+            hi = gw.b_off + (long long)(K - 1) * gw.ldb + N;
           }
-          int c_lo = (int)(lo / fuse.chunk_elems);
-          int c_hi = (int)((hi - 1) / fuse.chunk_elems);
-          if (c_hi > fuse.n_chunks - 1) c_hi = fuse.n_chunks - 1;
+          int c_lo = (int)(lo / gw.chunk_elems);
+          int c_hi = (int)((hi - 1) / gw.chunk_elems);
+          if (c_hi > gw.n_chunks - 1) c_hi = gw.n_chunks - 1;
           bool waited = false;
           for (int c = c_lo; c <= c_hi; ++c) {
             if (!((known >> c) & 1ull)) {
-              wait_flag_geq(fuse.flags + c, fuse.epoch, fuse.timeout_ns);
+              wait_flag_geq(gw.flags + c, gw.epoch, gw.timeout_ns);
               known |= 1ull << c;
               waited = true;
             }
@@ -307,21 +328,173 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + acc * BN;
+      // hand the drained TMEM stage back to the MMA warp
+      auto release_tmem = [&]() {
+        tc_fence_before();
+        __syncwarp();
+        if (lane_id() == 0) {
+          if constexpr (kCta == 2) mbar_arrive_cluster(&tempty_bar[acc], 0);
+          else mbar_arrive(&tempty_bar[acc]);
+        }
+      };
+      // one 64-column chunk (32 packed bf16x2 per row) -> 128B-swizzled staging -> TMA store
+      auto emit = [&](const uint32_t (&packed)[32], const CUtensorMap* map, int col, int row0, bool valid) {
+        // staging buffer reuse: the TMA store issued two chunks ago must have finished reading
+        uint8_t* sc = smem_c + (chunk_ctr & 1) * kEpiStageBytes;
+        if (epi_leader) tma_store_wait_read<kNumEpiStages - 1>();
+        named_bar_sync(1, 128);
+        const uint32_t row_addr = smem_u32(sc) + row * 128;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint32_t addr = row_addr + ((j ^ (row & 7)) << 4);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(packed[4 * j]),
+                       "r"(packed[4 * j + 1]), "r"(packed[4 * j + 2]), "r"(packed[4 * j + 3])
+                       : "memory");
+        }
+        fence_proxy_async_smem();
+        named_bar_sync(1, 128);
+        if (epi_leader) {
+          if (valid) tma_store_2d(map, sc, col, row0);
+          tma_store_commit();
+        }
+        ++chunk_ctr;
+      };
+
+      if constexpr (kFuse == 4) {
+        // ---- gate | up accumulator -> gate, up, silu(gate) * up ----
+        const int j0 = nb * (BN / 2);
+#pragma unroll 1
+        for (int c = 0; c < 2; ++c) {
+          uint32_t pg[32], pu[32], ph[32];
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+            uint32_t rg[32], ru[32];
+            tmem_ld_32x32b_x32(taddr + c * kEpiChunk + half * 32, rg);
+            tmem_ld_32x32b_x32(taddr + BN / 2 + c * kEpiChunk + half * 32, ru);
+            tmem_ld_wait();
+            if (c == 1 && half == 1) release_tmem();
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const uint32_t gb = pack_bf16(__uint_as_float(rg[2 * j]), __uint_as_float(rg[2 * j + 1]));
+              const uint32_t ub = pack_bf16(__uint_as_float(ru[2 * j]), __uint_as_float(ru[2 * j + 1]));
+              const float2 g = unpack_bf16(gb), u = unpack_bf16(ub);
+              // the standalone kernel's arithmetic on the bf16-rounded pre-activations: silu rounded to
+              // bf16 (as HF's act_fn output is), then the product
+              const float s0 = unpack_bf16(pack_bf16(__fdividef(g.x, 1.f + __expf(-g.x)), 0.f)).x;
+              const float s1 = unpack_bf16(pack_bf16(__fdividef(g.y, 1.f + __expf(-g.y)), 0.f)).x;
+              pg[half * 16 + j] = gb;
+              pu[half * 16 + j] = ub;
+              ph[half * 16 + j] = pack_bf16(s0 * u.x, s1 * u.y);
+            }
+          }
+          const bool valid = m0 < M;
+          emit(pg, &tmC, j0 + c * kEpiChunk, m0, valid);
+          emit(pu, &tmC, fuse.inter + j0 + c * kEpiChunk, m0, valid);
+          emit(ph, &fuse.th, j0 + c * kEpiChunk, m0, valid);
+        }
+      } else if constexpr (kEpi == EPI_DSWIGLU) {
+        // ---- dh tile (+ saved gate / up) -> dgate, dup ----
+        const int grow = m0 + row;
+#pragma unroll 1
+        for (int c = 0; c < n_chunks; ++c) {
+          const int col0 = n0 + c * kEpiChunk;
+          uint32_t pdg[32], pdu[32];
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+            uint32_t gq[16], uq[16];   // 32 saved gate / up values each, packed bf16x2
+            const int colh = col0 + half * 32;
+            if (grow < M && colh + 32 <= epi.inter) {
+              const uint4* gp = reinterpret_cast<const uint4*>(epi.gu + (size_t)grow * epi.ld_gu + colh);
+              const uint4* up = reinterpret_cast<const uint4*>(epi.gu + (size_t)grow * epi.ld_gu + epi.inter + colh);
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const uint4 a = gp[q], bq = up[q];
+                gq[4 * q] = a.x; gq[4 * q + 1] = a.y; gq[4 * q + 2] = a.z; gq[4 * q + 3] = a.w;
+                uq[4 * q] = bq.x; uq[4 * q + 1] = bq.y; uq[4 * q + 2] = bq.z; uq[4 * q + 3] = bq.w;
+              }
+            } else {
+#pragma unroll
+              for (int q = 0; q < 16; ++q) { gq[q] = 0u; uq[q] = 0u; }
+            }
+            uint32_t rd[32];
+            tmem_ld_32x32b_x32(taddr + c * kEpiChunk + half * 32, rd);
+            tmem_ld_wait();
+            if (c == n_chunks - 1 && half == 1) release_tmem();
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const float2 g = unpack_bf16(gq[j]), u = unpack_bf16(uq[j]);
+              const float d0 = __uint_as_float(rd[2 * j]), d1 = __uint_as_float(rd[2 * j + 1]);
+              const float sg0 = __fdividef(1.f, 1.f + __expf(-g.x)), sg1 = __fdividef(1.f, 1.f + __expf(-g.y));
+              pdu[half * 16 + j] = pack_bf16(d0 * (g.x * sg0), d1 * (g.y * sg1));
+              pdg[half * 16 + j] = pack_bf16(d0 * u.x * (sg0 * (1.f + g.x * (1.f - sg0))),
+                                             d1 * u.y * (sg1 * (1.f + g.y * (1.f - sg1))));
+            }
+          }
+          const bool valid = col0 < N && m0 < M;
+          emit(pdg, &tmC, col0, m0, valid);
+          emit(pdu, &tmC, epi.inter + col0, m0, valid);
+        }
+      } else if constexpr (kEpi == EPI_ROPE) {
+        // ---- rotary embedding on 128-wide heads (two 64-column chunks: low and high half of a head) ----
+        const int grow = m0 + row;
+        int p = 0;
+        if (grow < M) p = epi.pos ? epi.pos[grow] : grow % epi.seq_len;
+        const __nv_bfloat16* crow = epi.cosT + (size_t)p * 128;
+        const __nv_bfloat16* srow = epi.sinT + (size_t)p * 128;
+        const int n_heads_tile = n_chunks / 2;
+#pragma unroll 1
+        for (int h = 0; h < n_heads_tile; ++h) {
+          const int col0 = n0 + h * 128;
+          const bool rot = (col0 >> 7) < epi.rope_heads;
+          uint32_t plo[32], phi[32];
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+            uint32_t rl[32], rh[32];
+            tmem_ld_32x32b_x32(taddr + h * 128 + half * 32, rl);
+            tmem_ld_32x32b_x32(taddr + h * 128 + 64 + half * 32, rh);
+            tmem_ld_wait();
+            if (h == n_heads_tile - 1 && half == 1) release_tmem();
+            if (rot) {
+              const uint4* c0 = reinterpret_cast<const uint4*>(crow + half * 32);
+              const uint4* c1 = reinterpret_cast<const uint4*>(crow + 64 + half * 32);
+              const uint4* s0 = reinterpret_cast<const uint4*>(srow + half * 32);
+              const uint4* s1 = reinterpret_cast<const uint4*>(srow + 64 + half * 32);
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const uint4 vc0 = c0[q], vc1 = c1[q], vs0 = s0[q], vs1 = s1[q];
+                const uint32_t ac0[4] = {vc0.x, vc0.y, vc0.z, vc0.w}, ac1[4] = {vc1.x, vc1.y, vc1.z, vc1.w};
+                const uint32_t as0[4] = {vs0.x, vs0.y, vs0.z, vs0.w}, as1[4] = {vs1.x, vs1.y, vs1.z, vs1.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  const int j = 4 * q + e;
+                  // the standalone kernel rotates the bf16-rounded projection output
+                  const float2 a = unpack_bf16(pack_bf16(__uint_as_float(rl[2 * j]), __uint_as_float(rl[2 * j + 1])));
+                  const float2 b = unpack_bf16(pack_bf16(__uint_as_float(rh[2 * j]), __uint_as_float(rh[2 * j + 1])));
+                  const float2 cl = unpack_bf16(ac0[e]), ch = unpack_bf16(ac1[e]);
+                  const float2 sl = unpack_bf16(as0[e]), sh = unpack_bf16(as1[e]);
+                  plo[half * 16 + j] = pack_bf16(a.x * cl.x - b.x * sl.x, a.y * cl.y - b.y * sl.y);
+                  phi[half * 16 + j] = pack_bf16(b.x * ch.x + a.x * sh.x, b.y * ch.y + a.y * sh.y);
+                }
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                plo[half * 16 + j] = pack_bf16(__uint_as_float(rl[2 * j]), __uint_as_float(rl[2 * j + 1]));
+                phi[half * 16 + j] = pack_bf16(__uint_as_float(rh[2 * j]), __uint_as_float(rh[2 * j + 1]));
+              }
+            }
+          }
+          emit(plo, &tmC, col0, m0, col0 < N && m0 < M);
+          emit(phi, &tmC, col0 + 64, m0, col0 + 64 < N && m0 < M);
+        }
+      } else {
 #pragma unroll 1
       for (int c = 0; c < n_chunks; ++c) {
         uint32_t r0[32], r1[32];
         tmem_ld_32x32b_x32(taddr + c * kEpiChunk, r0);
         tmem_ld_32x32b_x32(taddr + c * kEpiChunk + 32, r1);
         tmem_ld_wait();
-        if (c == n_chunks - 1) {
-          // accumulator fully drained to registers: hand the TMEM stage back to the MMA warp
-          tc_fence_before();
-          __syncwarp();
-          if (lane_id() == 0) {
-            if constexpr (kCta == 2) mbar_arrive_cluster(&tempty_bar[acc], 0);
-            else mbar_arrive(&tempty_bar[acc]);
-          }
-        }
+        if (c == n_chunks - 1) release_tmem();   // accumulator fully drained to registers
         const int col0 = n0 + c * kEpiChunk;
         uint32_t packed[32];
         if constexpr (kEpi == EPI_NONE) {
@@ -360,32 +533,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             packed[j] = pack_bf16(v0, v1);
           }
         }
-        // staging buffer reuse: the TMA store issued two chunks ago must have finished reading
-        uint8_t* sc = smem_c + (chunk_ctr & 1) * kEpiStageBytes;
-        if (epi_leader) tma_store_wait_read<kNumEpiStages - 1>();
-        named_bar_sync(1, 128);
-        const uint32_t row_addr = smem_u32(sc) + row * 128;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const uint32_t addr = row_addr + ((j ^ (row & 7)) << 4);
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(packed[4 * j]),
-                       "r"(packed[4 * j + 1]), "r"(packed[4 * j + 2]), "r"(packed[4 * j + 3])
-                       : "memory");
+        if constexpr (kFuse == 2) {
+          const int owner = min(m0 / fuse.rows_per_rank, fuse.W - 1);
+          emit(packed, &fuse.cm[owner], col0, m0 - owner * fuse.rows_per_rank, col0 < N && m0 < M);
+        } else {
+          emit(packed, &tmC, col0, m0, col0 < N && m0 < M);
         }
-        fence_proxy_async_smem();
-        named_bar_sync(1, 128);
-        if (epi_leader) {
-          if (col0 < N && m0 < M) {
-            if constexpr (kFuse == 2) {
-              const int owner = min(m0 / fuse.rows_per_rank, fuse.W - 1);
-              tma_store_2d(&fuse.cm[owner], sc, col0, m0 - owner * fuse.rows_per_rank);
-            } else {
-              tma_store_2d(&tmC, sc, col0, m0);
-            }
-          }
-          tma_store_commit();
-        }
-        ++chunk_ctr;
+      }
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
@@ -557,7 +711,8 @@ static bool tail_split_enabled() {
 template <int kCta, bool kAK, bool kBK, int kEpi, int BN, class Fuse = NoFuse>
 static int launch_gemm(void* C, const void* A, const void* B, int M, int N, int K, int lda, int ldb,
                        int ldc, const EpiArgs& epi, int max_ctas, cudaStream_t stream,
-                       const Fuse& fuse = Fuse(), bool allow_split = true) {
+                       const Fuse& fuse = Fuse(), bool allow_split = true,
+                       const GatherWaitArgs& gw = GatherWaitArgs()) {
   using Cfg = GemmCfg<kCta, BN>;
   CUtensorMap tmA, tmB, tmC;
   int rc;
@@ -569,6 +724,9 @@ static int launch_gemm(void* C, const void* A, const void* B, int M, int N, int 
   if (rc) return rc;
   if constexpr (FuseKind<Fuse>::v == 2) {
     tmC = fuse.cm[0];  // unused by the scatter variant; keep the parameter well formed
+  } else if constexpr (FuseKind<Fuse>::v == 4) {
+    rc = make_tmap_2d_bf16(&tmC, C, M, 2 * N, ldc, BM, kEpiChunk);
+    if (rc) return rc;
   } else {
     rc = make_tmap_2d_bf16(&tmC, C, M, N, ldc, BM, kEpiChunk);
     if (rc) return rc;
@@ -585,7 +743,8 @@ static int launch_gemm(void* C, const void* A, const void* B, int M, int N, int 
     attr_set[dev] = true;
   }
   const int tile_m = BM * kCta;
-  const int num_tiles = ((M + tile_m - 1) / tile_m) * ((N + BN - 1) / BN);
+  const int num_n_host = FuseKind<Fuse>::v == 4 ? N / (BN / 2) : (N + BN - 1) / BN;
+  const int num_tiles = ((M + tile_m - 1) / tile_m) * num_n_host;
   int sms = sm_count();
   if (max_ctas > 0 && max_ctas < sms) sms = max_ctas;
   int workers = sms / kCta;
@@ -596,8 +755,7 @@ static int launch_gemm(void* C, const void* A, const void* B, int M, int N, int 
   // more round; the fused variants order their tiles by chunk arrival and keep whole tiles
   int split_from = num_tiles;
   CUtensorMap tmBh = tmB;
-  if (allow_split && tail_split_enabled() && BN == 256 && (FuseKind<Fuse>::v == 0 || FuseKind<Fuse>::v == 3) &&
-      num_tiles > workers) {
+  if (allow_split && tail_split_enabled() && BN == 256 && FuseKind<Fuse>::v == 0 && num_tiles > workers) {
     const int rem = num_tiles % workers;
     if (rem > 0 && 2 * rem <= workers) {
       if constexpr (kBK) rc = make_tmap_2d_bf16(&tmBh, B, N, K, ldb, BN / 2 / kCta, BK);
@@ -619,7 +777,7 @@ static int launch_gemm(void* C, const void* A, const void* B, int M, int N, int 
   attrs[0].val.clusterDim.z = 1;
   cfg.attrs = attrs;
   cfg.numAttrs = 1;
-  B2_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, M, N, K, epi, fuse, tmBh, split_from));
+  B2_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, M, N, K, epi, fuse, tmBh, split_from, gw));
   return 0;
 }
 
@@ -697,6 +855,34 @@ static unsigned long long flag_wait_timeout_ns() {
     return ms * 1000000ull;
   }();
   return ns;
+}
+
+// Describe a weight that is still being gathered (flags == nullptr: none). num_n_blocks / rows_per_block:
+// the K-major n-block structure used to pick the first block to visit (0 blocks: MN-major, no rotation).
+static int make_gather_wait(GatherWaitArgs* gw, const unsigned int* flags, unsigned int epoch, long long b_off,
+                            long long chunk_elems, int n_chunks, int chunks_per_rank, int rank, int W, int ldb,
+                            int num_n_blocks, int rows_per_block) {
+  *gw = GatherWaitArgs();
+  if (flags == nullptr) return 0;
+  B2_REQUIRE(n_chunks >= 1 && n_chunks <= 64 && chunk_elems > 0 && chunks_per_rank >= 1 && W >= 1,
+             "gather wait: %d chunks (at most 64) of %lld elements", n_chunks, chunk_elems);
+  gw->flags = flags;
+  gw->epoch = epoch;
+  gw->b_off = b_off;
+  gw->chunk_elems = chunk_elems;
+  gw->n_chunks = n_chunks;
+  gw->ldb = ldb;
+  gw->timeout_ns = flag_wait_timeout_ns();
+  gw->nb_start = 0;
+  int best = W + 1;  // visit first the n-blocks whose rows arrive first: own shard, then the peers in pull order
+  for (int nb = 0; nb < num_n_blocks; ++nb) {
+    long long c = (b_off + (long long)nb * rows_per_block * ldb) / chunk_elems;
+    if (c > n_chunks - 1) c = n_chunks - 1;
+    const int owner = (int)(c / chunks_per_rank) % W;
+    const int dist = (owner - rank + W) % W;
+    if (dist < best) { best = dist; gw->nb_start = nb; }
+  }
+  return 0;
 }
 
 // out[i] = sum_w slots[w * n + i]   (bf16, fp32 accumulate): the local half of a scattered reduction
@@ -797,39 +983,87 @@ int b2_gemm_bf16_bwait(void* C, const void* A, const void* B, int M, int N, int 
                        int chunks_per_rank, int rank, int W, cudaStream_t stream) {
   using namespace b2;
   B2_REQUIRE(M > BM, "gemm_bwait: M=%d must exceed %d (2-CTA tiles)", M, BM);
-  B2_REQUIRE(n_chunks >= 1 && n_chunks <= 64 && chunk_elems > 0 && chunks_per_rank >= 1,
-             "gemm_bwait: %d chunks (at most 64) of %lld elements", n_chunks, chunk_elems);
   B2_REQUIRE(epilogue == EPI_NONE || epilogue == EPI_BIAS, "gemm_bwait: unsupported epilogue %d", epilogue);
-  FuseBWait f;
-  f.flags = flags;
-  f.epoch = epoch;
-  f.b_off = b_off;
-  f.chunk_elems = chunk_elems;
-  f.n_chunks = n_chunks;
-  f.ldb = ldb;
-  f.timeout_ns = flag_wait_timeout_ns();
-  f.nb_start = 0;
-  if (!b_mn) {  // visit first the n-blocks whose rows arrive first: own shard, then the peers in pull order
-    const int num_n = (N + 255) / 256;
-    int best = W + 1;
-    for (int nb = 0; nb < num_n; ++nb) {
-      long long c = (b_off + (long long)nb * 256 * ldb) / chunk_elems;
-      if (c > n_chunks - 1) c = n_chunks - 1;
-      const int owner = (int)(c / chunks_per_rank) % W;
-      const int dist = (owner - rank + W) % W;
-      if (dist < best) { best = dist; f.nb_start = nb; }
-    }
-  }
+  GatherWaitArgs gw;
+  if (int rc = make_gather_wait(&gw, flags, epoch, b_off, chunk_elems, n_chunks, chunks_per_rank, rank, W, ldb,
+                                b_mn ? 0 : (N + 255) / 256, 256))
+    return rc;
   EpiArgs epi = {};
   epi.bias = static_cast<const __nv_bfloat16*>(bias);
   if (b_mn) {
     if (epilogue == EPI_BIAS)
-      return launch_gemm<2, true, false, EPI_BIAS, 256, FuseBWait>(C, A, B, M, N, K, lda, ldb, ldc, epi, 0, stream, f);
-    return launch_gemm<2, true, false, EPI_NONE, 256, FuseBWait>(C, A, B, M, N, K, lda, ldb, ldc, epi, 0, stream, f);
+      return launch_gemm<2, true, false, EPI_BIAS, 256>(C, A, B, M, N, K, lda, ldb, ldc, epi, 0, stream, NoFuse(), true, gw);
+    return launch_gemm<2, true, false, EPI_NONE, 256>(C, A, B, M, N, K, lda, ldb, ldc, epi, 0, stream, NoFuse(), true, gw);
   }
   if (epilogue == EPI_BIAS)
-    return launch_gemm<2, true, true, EPI_BIAS, 256, FuseBWait>(C, A, B, M, N, K, lda, ldb, ldc, epi, 0, stream, f);
-  return launch_gemm<2, true, true, EPI_NONE, 256, FuseBWait>(C, A, B, M, N, K, lda, ldb, ldc, epi, 0, stream, f);
+    return launch_gemm<2, true, true, EPI_BIAS, 256>(C, A, B, M, N, K, lda, ldb, ldc, epi, 0, stream, NoFuse(), true, gw);
+  return launch_gemm<2, true, true, EPI_NONE, 256>(C, A, B, M, N, K, lda, ldb, ldc, epi, 0, stream, NoFuse(), true, gw);
+}
+
+// ---- GEMMs with fused elementwise neighbours -------------------------------------------------------
+// Every function below takes the optional gather-wait description of its weight (flags == nullptr: none).
+//
+// gate/up projection + SwiGLU: GU[M, 2I] = x W^T (gate | up pre-activations, kept for backward) and
+// H[M, I] = silu(gate) * up, W stacked [2I, K]. Requires I % 128 == 0 and M > 128.
+int b2_gemm_swiglu(void* GU, void* H, const void* A, const void* B, int M, int I, int K, int lda, int ldb,
+                   int ld_gu, int ld_h, const unsigned int* flags, unsigned int epoch, long long b_off,
+                   long long chunk_elems, int n_chunks, int chunks_per_rank, int rank, int W,
+                   cudaStream_t stream) {
+  using namespace b2;
+  B2_REQUIRE(M > BM && I % 128 == 0, "gemm_swiglu: M=%d (> %d) I=%d (%% 128)", M, BM, I);
+  GatherWaitArgs gw;
+  if (int rc = make_gather_wait(&gw, flags, epoch, b_off, chunk_elems, n_chunks, chunks_per_rank, rank, W, ldb,
+                                I / 128, 128))
+    return rc;
+  FuseSwiglu f;
+  if (int rc = make_tmap_2d_bf16(&f.th, H, M, I, ld_h, BM, kEpiChunk)) return rc;
+  f.inter = I;
+  EpiArgs epi = {};
+  return launch_gemm<2, true, true, EPI_NONE, 256, FuseSwiglu>(GU, A, B, M, I, K, lda, ldb, ld_gu, epi, 0, stream,
+                                                               f, false, gw);
+}
+
+// down-projection dgrad + SwiGLU backward: dGU[M, 2I] = dswiglu(dY W_down, GU) with W_down stored [H, I]
+// (the dgrad operand layout); dh = dY W_down never leaves the chip.
+int b2_gemm_dswiglu(void* dGU, const void* dY, const void* Wd, const void* GU, int M, int I, int Hdim, int lda,
+                    int ldb, int ld_dgu, int ld_gu, const unsigned int* flags, unsigned int epoch,
+                    long long b_off, long long chunk_elems, int n_chunks, int chunks_per_rank, int rank,
+                    int W, cudaStream_t stream) {
+  using namespace b2;
+  B2_REQUIRE(M > BM && I % 64 == 0, "gemm_dswiglu: M=%d (> %d) I=%d (%% 64)", M, BM, I);
+  GatherWaitArgs gw;
+  if (int rc = make_gather_wait(&gw, flags, epoch, b_off, chunk_elems, n_chunks, chunks_per_rank, rank, W, ldb,
+                                0, 256))
+    return rc;
+  EpiArgs epi = {};
+  epi.gu = static_cast<const __nv_bfloat16*>(GU);
+  epi.ld_gu = ld_gu;
+  epi.inter = I;
+  // C's tensor map spans [M, 2I]; the GEMM's N is I
+  return launch_gemm<2, true, false, EPI_DSWIGLU, 256>(dGU, dY, Wd, M, I, Hdim, lda, ldb, ld_dgu, epi, 0, stream,
+                                                       NoFuse(), true, gw);
+}
+
+// QKV projection + rotary embedding: C[M, N] = x W^T with the first rope_heads 128-wide heads of every
+// row rotated by the row's position (pos[row], or row % seq_len when pos is null); cos / sin [max_pos, 128].
+int b2_gemm_rope(void* C, const void* A, const void* B, int M, int N, int K, int lda, int ldb, int ldc,
+                 const void* cosT, const void* sinT, const int* pos, int rope_heads, int seq_len,
+                 const unsigned int* flags, unsigned int epoch, long long b_off, long long chunk_elems,
+                 int n_chunks, int chunks_per_rank, int rank, int W, cudaStream_t stream) {
+  using namespace b2;
+  B2_REQUIRE(M > BM && N % 128 == 0, "gemm_rope: M=%d (> %d) N=%d (%% 128)", M, BM, N);
+  GatherWaitArgs gw;
+  if (int rc = make_gather_wait(&gw, flags, epoch, b_off, chunk_elems, n_chunks, chunks_per_rank, rank, W, ldb,
+                                (N + 255) / 256, 256))
+    return rc;
+  EpiArgs epi = {};
+  epi.cosT = static_cast<const __nv_bfloat16*>(cosT);
+  epi.sinT = static_cast<const __nv_bfloat16*>(sinT);
+  epi.pos = pos;
+  epi.rope_heads = rope_heads;
+  epi.seq_len = seq_len;
+  return launch_gemm<2, true, true, EPI_ROPE, 256>(C, A, B, M, N, K, lda, ldb, ldc, epi, 0, stream, NoFuse(), true,
+                                                   gw);
 }
 
 int b2_sum_slots(void* out, const void* slots, size_t n_elems, int W, cudaStream_t stream) {

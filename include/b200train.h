@@ -124,6 +124,28 @@ int b2_colsum(void* out, float* partial, const void* x, int T, int N, int ld, in
 int b2_cpu_adamw_bf16(void* p, void* m, void* v, const void* g, size_t n, float lr, float beta1,
                       float beta2, float eps, float wd, int step, float grad_scale);
 
+/* ---- GEMMs with fused elementwise neighbours ----------------------------------------------------------
+ * b2_gemm_swiglu : GU[M, 2I] = x W^T (gate | up, kept for backward) and H[M, I] = silu(gate) * up in one GEMM
+ *                  on the stacked weight W [2I, K] (I % 128 == 0, M > 128).
+ * b2_gemm_dswiglu: dGU[M, 2I] = SwiGLU backward of dh = dY W_down (W_down stored [H, I]) and the saved GU; dh is
+ *                  formed in tensor memory and never written.
+ * b2_gemm_rope   : C = x W^T with the first rope_heads 128-wide heads of each row rotated (cos / sin
+ *                  [max_pos, 128], position = pos[row] or row % seq_len).
+ * The trailing (flags .. W) arguments describe an in-flight all-gather of the weight (see below); flags == NULL
+ * means the weight is complete. Reference: HF LlamaMLP.forward / apply_rotary_pos_emb behind
+ * 01-single-gpu/train_llm.py:140 (Liger-patched in 00-rime/train_llm_01-single-gpu.py:51-54). */
+int b2_gemm_swiglu(void* GU, void* H, const void* A, const void* B, int M, int I, int K, int lda, int ldb,
+                   int ld_gu, int ld_h, const unsigned int* flags, unsigned int epoch, long long b_off,
+                   long long chunk_elems, int n_chunks, int chunks_per_rank, int rank, int W, b2_stream_t stream);
+int b2_gemm_dswiglu(void* dGU, const void* dY, const void* Wd, const void* GU, int M, int I, int Hdim, int lda,
+                    int ldb, int ld_dgu, int ld_gu, const unsigned int* flags, unsigned int epoch,
+                    long long b_off, long long chunk_elems, int n_chunks, int chunks_per_rank, int rank,
+                    int W, b2_stream_t stream);
+int b2_gemm_rope(void* C, const void* A, const void* B, int M, int N, int K, int lda, int ldb, int ldc,
+                 const void* cosT, const void* sinT, const int* pos, int rope_heads, int seq_len,
+                 const unsigned int* flags, unsigned int epoch, long long b_off, long long chunk_elems,
+                 int n_chunks, int chunks_per_rank, int rank, int W, b2_stream_t stream);
+
 /* ---- FSDP parameter all-gather fused into the consuming GEMM ---------------------------------------
  * b2_peer_all_gather_flagged pulls the peers' shards of a flat unit into the local full buffer with the
  * copy engines, `sub` chunks per shard, and writes flags[r * sub + j] = epoch after chunk (r, j) with a

@@ -59,6 +59,12 @@ def _declare(lib):
         "b2_sum_slots": [P, P, Z, I, P],
         "b2_gemm_bf16_bwait": [P, P, P, I, I, I, I, I, I, I, I, P, P, ctypes.c_uint, ctypes.c_longlong,
                                ctypes.c_longlong, I, I, I, I, P],
+        "b2_gemm_swiglu": [P, P, P, P, I, I, I, I, I, I, I, P, ctypes.c_uint, ctypes.c_longlong, ctypes.c_longlong,
+                           I, I, I, I, P],
+        "b2_gemm_dswiglu": [P, P, P, P, I, I, I, I, I, I, I, P, ctypes.c_uint, ctypes.c_longlong, ctypes.c_longlong,
+                            I, I, I, I, P],
+        "b2_gemm_rope": [P, P, P, I, I, I, I, I, I, P, P, P, I, I, P, ctypes.c_uint, ctypes.c_longlong,
+                         ctypes.c_longlong, I, I, I, I, P],
         "b2_peer_all_gather_flagged": [P, P, Z, I, I, I, I, I, P, ctypes.c_uint, P],
         "b2_stream_wait_flags": [P, I, I, ctypes.c_uint, P],
         "b2_local_copy": [P, P, Z, I, P],

@@ -64,8 +64,9 @@ class LlamaAttention(nn.Module):
         self.o_proj = FusedLinearWeight(cfg.q_size, cfg.hidden_size, dtype, device)
 
     def forward(self, x, ctx):
-        qkv = self.qkv_proj(x)
-        qkv = ops.rope_qk(qkv, ctx.cos, ctx.sin, ctx.pos, self.n_q + self.n_kv, self.D, ctx.seq_len)
+        # QKV projection with the rotary embedding of the q / k heads in the GEMM epilogue
+        qkv = ops.linear_rope(x, self.qkv_proj.weight, ctx.cos, ctx.sin, ctx.pos, self.n_q + self.n_kv, self.D,
+                              ctx.seq_len)
         o = ops.attention(qkv, ctx.cu_seqlens, ctx.max_seqlen, self.n_q, self.n_kv, self.D)
         return self.o_proj(o)
 
@@ -79,7 +80,8 @@ class LlamaMLP(nn.Module):
         self.down_proj = FusedLinearWeight(I, cfg.hidden_size, dtype, device)
 
     def forward(self, x):
-        return self.down_proj(ops.swiglu(self.gate_up_proj(x)))
+        # gate/up GEMM with SwiGLU in its epilogue, down projection, and the mirrored fused backward
+        return ops.mlp_swiglu(x, self.gate_up_proj.weight, self.down_proj.weight)
 
 
 class LlamaDecoderLayer(nn.Module):
