@@ -568,7 +568,19 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+// cuTensorMapEncodeTiled is a driver call and needs a current context on the calling thread. A thread whose
+// first CUDA work is one of our launches (an autograd worker whose first backward node is one of these ops)
+// has had no runtime call yet, so bind the primary context once per thread.
+static void ensure_context() {
+  static thread_local bool ready = false;
+  if (!ready) {
+    cudaFree(nullptr);
+    ready = true;
+  }
+}
+
 static EncodeTiledFn get_encode() {
+  ensure_context();
   static EncodeTiledFn fn = nullptr;
   static std::once_flag once;
   std::call_once(once, [] {
@@ -719,12 +731,14 @@ static int launch_gemm(void* C, const void* A, const void* B, int M, int N, int 
   if constexpr (kAK) rc = make_tmap_2d_bf16(&tmA, A, M, K, lda, BM, BK);
   else rc = make_tmap_mn_bf16(&tmA, A, K, M, lda, BK, BM / 64);
   if (rc) return rc;
-  if constexpr (kBK) rc = make_tmap_2d_bf16(&tmB, B, N, K, ldb, BN / kCta, BK);
+  // SwiGLU: B is the stacked [2I, K] weight while the GEMM's N is I
+  if constexpr (kBK) rc = make_tmap_2d_bf16(&tmB, B, FuseKind<Fuse>::v == 4 ? 2 * N : N, K, ldb, BN / kCta, BK);
   else rc = make_tmap_mn_bf16(&tmB, B, K, N, ldb, BK, BN / kCta / 64);
   if (rc) return rc;
   if constexpr (FuseKind<Fuse>::v == 2) {
     tmC = fuse.cm[0];  // unused by the scatter variant; keep the parameter well formed
-  } else if constexpr (FuseKind<Fuse>::v == 4) {
+  } else if constexpr (FuseKind<Fuse>::v == 4 || kEpi == EPI_DSWIGLU) {
+    // C is the [M, 2I] gate | up (or d gate | d up) tensor while the GEMM's N is I
     rc = make_tmap_2d_bf16(&tmC, C, M, 2 * N, ldc, BM, kEpiChunk);
     if (rc) return rc;
   } else {

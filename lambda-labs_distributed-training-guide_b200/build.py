@@ -49,7 +49,9 @@ def _digest(paths) -> str:
     for p in sorted(paths):
         h.update(p.name.encode())
         h.update(p.read_bytes())
-    h.update(" ".join(NVCC_FLAGS).encode())
+    # the flags without the include directories: those are absolute paths of this checkout, and a tree copied to
+    # another machine (gpurun) must still recognise its own up-to-date objects
+    h.update(" ".join(f for f in NVCC_FLAGS if not f.startswith("/")).encode())
     return h.hexdigest()
 
 
