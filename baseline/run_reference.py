@@ -50,9 +50,14 @@ def _load_module(path: Path, name: str):
 
 
 def run_reference(chapter: str, hf_config: dict, batch_size: int, seq_len: int, steps: int, warmup: int,
-                  extra_args=(), dp_size=None) -> dict:
+                  extra_args=(), dp_size=None, init_weights_dir=None, capture_losses=False) -> dict:
     """Run ``warmup + steps`` optimizer steps of the reference chapter; returns timing of the last
-    ``steps`` (CUDA events, max over ranks) plus the end-to-end host-clock figure."""
+    ``steps`` (CUDA events, max over ranks) plus the end-to-end host-clock figure.
+
+    Parity mode (``tests/test_parity_reference_gpu.py``): ``init_weights_dir`` is a directory of HF-named
+    safetensors that replaces the random initialisation right after the script's own ``from_config`` call,
+    ``capture_losses`` logs every step (``--log-freq 1``) and returns the per-step losses the script reports,
+    with the loader's shuffling switched off so both sides see the same batches in the same order."""
     import torch
     import torch.distributed as dist
 
@@ -127,9 +132,47 @@ def run_reference(chapter: str, hf_config: dict, batch_size: int, seq_len: int, 
 
     mod.LocalTimer = EventTimer
 
+    losses = []
+    if init_weights_dir is not None:
+        from safetensors.torch import load_file
+
+        orig_from_config = mod.AutoModelForCausalLM.from_config
+
+        def from_config_with_weights(*a, **kw):
+            model = orig_from_config(*a, **kw)
+            sd = {}
+            for f in sorted(Path(init_weights_dir).glob("*.safetensors")):
+                sd.update(load_file(str(f)))
+            missing, unexpected = model.load_state_dict(sd, strict=False)
+            missing = [k for k in missing if "rotary" not in k and "inv_freq" not in k]
+            assert not missing and not unexpected, (missing[:4], unexpected[:4])
+            return model
+
+        class _Auto:
+            from_config = staticmethod(from_config_with_weights)
+            from_pretrained = staticmethod(mod.AutoModelForCausalLM.from_pretrained)
+
+        mod.AutoModelForCausalLM = _Auto
+    if capture_losses:
+        orig_loader = mod.DataLoader
+
+        def loader_in_order(*a, **kw):
+            kw["shuffle"] = False
+            return orig_loader(*a, **kw)
+
+        mod.DataLoader = loader_in_order
+        orig_info = mod.LOGGER.info
+
+        def info(msg, *a, **kw):
+            if isinstance(msg, dict) and "running_loss" in msg:
+                losses.append(float(msg["running_loss"]))
+            return orig_info(msg, *a, **kw)
+
+        mod.LOGGER.info = info
+
     argv = ["train_llm.py", "-e", "bench", "-d", "synthetic", "-m", str(model_dir), "--save-dir",
             str(work / "out"), "-b", str(batch_size), "-s", str(seq_len), "--num-epochs", "1",
-            "--log-freq", str(10 ** 9), "--ckpt-freq", str(10 ** 9), *extra_args]
+            "--log-freq", "1" if capture_losses else str(10 ** 9), "--ckpt-freq", str(10 ** 9), *extra_args]
     old_argv = sys.argv
     sys.argv = argv
     try:
@@ -157,4 +200,5 @@ def run_reference(chapter: str, hf_config: dict, batch_size: int, seq_len: int, 
         "world": world,
         "setup_s": records["host_start"][0] - t0,
         "peak_alloc_gb": torch.cuda.max_memory_allocated() / 1e9,
+        "losses": losses,
     }

@@ -28,5 +28,19 @@ if which in ("attn", "all"):
     for _ in range(3):
         o, lse = attn_fwd_raw(q, k, v, cu, T, nq, nkv, D, D ** -0.5)
         attn_bwd_raw(torch.randn_like(o), q, k, v, o, lse, dq, dk, dv, cu, T, nq, nkv, D, D ** -0.5)
+if which in ("gemm_fused", "all"):
+    # the fused-epilogue GEMMs on one Llama-3.1-8B layer: gate/up + SwiGLU, down dgrad + SwiGLU backward, QKV + RoPE
+    from b200train import ops
+
+    H, I = 4096, 14336
+    x = (torch.randn(T, H, device="cuda") * 0.5).to(torch.bfloat16).requires_grad_()
+    w_gu = (torch.randn(2 * I, H, device="cuda") * H ** -0.5).to(torch.bfloat16).requires_grad_()
+    w_d = (torch.randn(H, I, device="cuda") * I ** -0.5).to(torch.bfloat16).requires_grad_()
+    w_qkv = (torch.randn(6144, H, device="cuda") * H ** -0.5).to(torch.bfloat16)
+    cos, sin = ops.rope_tables(128, 8192, 500000.0, None, device="cuda")
+    for _ in range(3):
+        y = ops.mlp_swiglu(x, w_gu, w_d)
+        y.backward(torch.ones_like(y))
+        ops.linear_rope(x.detach(), w_qkv, cos, sin, None, 40, 128, T)
 torch.cuda.synchronize()
 print("ok")

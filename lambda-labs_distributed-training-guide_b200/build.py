@@ -41,7 +41,11 @@ def _nvcc() -> str:
 
 
 def _sources() -> list[Path]:
-    return sorted(CSRC.glob("*.cu"))
+    # *.cu: device + host code through nvcc; *.cpp: host-only code (CPU optimizer) straight through g++
+    return sorted(CSRC.glob("*.cu")) + sorted(CSRC.glob("*.cpp"))
+
+
+CXX_FLAGS = ["-O3", "-std=c++17", "-fPIC", "-fopenmp"]
 
 
 def _digest(paths) -> str:
@@ -89,12 +93,16 @@ def _build_locked(force: bool, verbose: bool) -> Path:
 
     def compile_one(item):
         src, obj, stamp, dig = item
-        cmd = [nvcc, *NVCC_FLAGS, "-c", str(src), "-o", str(obj)]
-        if verbose:
-            cmd.insert(1, "-Xptxas=-v")
+        if src.suffix == ".cpp":
+            cmd = [shutil.which("g++") or "g++", *CXX_FLAGS, "-I", str(INCLUDE), "-I", str(CSRC), "-c", str(src),
+                   "-o", str(obj)]
+        else:
+            cmd = [nvcc, *NVCC_FLAGS, "-c", str(src), "-o", str(obj)]
+            if verbose:
+                cmd.insert(1, "-Xptxas=-v")
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
-            raise RuntimeError(f"nvcc failed for {src.name}:\n{r.stdout}\n{r.stderr}")
+            raise RuntimeError(f"compiler failed for {src.name}:\n{r.stdout}\n{r.stderr}")
         if verbose:
             print(r.stderr)
         stamp.write_text(dig)

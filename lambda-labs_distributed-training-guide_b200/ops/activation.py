@@ -68,7 +68,8 @@ class _GeluNew(torch.autograd.Function):
 
 
 def gelu_new_ref(x):
-    return 0.5 * x * (1.0 + torch.tanh(math.sqrt(2.0 / math.pi) * (x + 0.044715 * torch.pow(x, 3.0))))
+    # HF "gelu_new" is the tanh approximation; ATen implements exactly that formula as one fused kernel
+    return torch.nn.functional.gelu(x, approximate="tanh")
 
 
 def gelu_new(x: torch.Tensor) -> torch.Tensor:

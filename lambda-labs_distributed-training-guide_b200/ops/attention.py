@@ -95,6 +95,16 @@ def attention_ref(qkv, cu_seqlens, max_seqlen, n_q, n_kv, D, scale=None, causal=
     bounds = cu_seqlens.tolist()
     g = n_q // n_kv
     for s, e in zip(bounds[:-1], bounds[1:]):
+        if qkv.device.type == "cpu" and qkv.dtype in (torch.float32, torch.bfloat16) and torch.is_grad_enabled():
+            # the CPU plumbing path (chapter 01 on CPU): ATen's fused attention, no S x S tensor
+            qi = q[s:e].transpose(0, 1).unsqueeze(0)
+            ki = k[s:e].transpose(0, 1).unsqueeze(0)
+            vi = v[s:e].transpose(0, 1).unsqueeze(0)
+            if g > 1:
+                ki, vi = ki.repeat_interleave(g, dim=1), vi.repeat_interleave(g, dim=1)
+            oi = torch.nn.functional.scaled_dot_product_attention(qi, ki, vi, is_causal=causal, scale=scale)
+            outs.append(oi[0].transpose(0, 1).reshape(e - s, n_q * D))
+            continue
         qi = q[s:e].transpose(0, 1).float()
         ki = k[s:e].transpose(0, 1).repeat_interleave(g, dim=0).float()
         vi = v[s:e].transpose(0, 1).repeat_interleave(g, dim=0).float()

@@ -174,6 +174,8 @@ class _Linear(torch.autograd.Function):
 
 def linear_ref(x, w, bias=None, w_is_kn=False):
     if w_is_kn:
+        if bias is not None and x.dim() >= 2:
+            return torch.addmm(bias, x.reshape(-1, x.shape[-1]), w).view(*x.shape[:-1], w.shape[1])
         y = x @ w
         return y + bias if bias is not None else y
     return torch.nn.functional.linear(x, w, bias)

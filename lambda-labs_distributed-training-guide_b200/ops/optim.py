@@ -37,6 +37,13 @@ def adamw_step(p, g, m, v, lr, beta1=0.9, beta2=0.999, eps=1e-8, wd=0.01, step=1
         # offloaded shards: native OpenMP loop over the (pinned) host buffers
         _C.call("b2_cpu_adamw_bf16", p.data_ptr(), m.data_ptr(), v.data_ptr(), g.data_ptr(), p.numel(), lr, beta1,
                 beta2, eps, wd, step, grad_scale)
+    elif (p.device.type == "cpu" and p.dtype == torch.float32 and grad_scale == 1.0
+          and hasattr(torch, "_fused_adamw_")):
+        # fp32 on the host (the chapter-01 CPU configuration): ATen's fused CPU AdamW, as the reference's
+        # AdamW(fused=True) (01-single-gpu/train_llm.py:65) -- one pass, no temporaries
+        with torch.no_grad():
+            torch._fused_adamw_([p], [g], [m], [v], [], [torch.tensor(float(step))], lr=lr, beta1=beta1,
+                                beta2=beta2, weight_decay=wd, eps=eps, amsgrad=False, maximize=False)
     else:
         with torch.no_grad():
             adamw_step_ref(p, g, m, v, lr, beta1, beta2, eps, wd, step, grad_scale)
