@@ -617,6 +617,37 @@ static int launch_reduce_local(int blocks, cudaStream_t stream, V4* out, const V
   return 0;
 }
 
+
+// ---- vocabulary-parallel cross entropy: statistics exchange through peer memory -------------------------
+// Every rank has written its per-row shard statistics -- row max, sum exp(x - max), target logit -- as fp32
+// [3][T] into a symmetric buffer. After a barrier each rank combines the W shards itself, reading the
+// peers' buffers directly: global max, rescaled sum, log-sum-exp and the row loss. This replaces the
+// all-reduce(MAX) + all-reduce(SUM) pair of the reference's loss_parallel (N10).
+__global__ void __launch_bounds__(256)
+ce_combine_peer_kernel(float* __restrict__ lse, float* __restrict__ loss_row, PeerPtrs stats,
+                       const long long* __restrict__ labels, int T, int W, int ignore_index) {
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < T; t += gridDim.x * blockDim.x) {
+    float mx[kMaxPeers], sm[kMaxPeers];
+    float gmax = -INFINITY, tgt = 0.f;
+    for (int r = 0; r < W; ++r) {
+      const float* st = static_cast<const float*>(stats.p[r]);
+      float a, b, c;
+      asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(a) : "l"(st + t) : "memory");
+      asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(b) : "l"(st + T + t) : "memory");
+      asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(c) : "l"(st + 2 * (size_t)T + t) : "memory");
+      mx[r] = a;
+      sm[r] = b;
+      tgt += c;
+      gmax = fmaxf(gmax, a);
+    }
+    float total = 0.f;
+    for (int r = 0; r < W; ++r) total += sm[r] * __expf(mx[r] - gmax);
+    const float l = gmax + __logf(total);
+    lse[t] = l;
+    loss_row[t] = labels[t] == ignore_index ? 0.f : l - tgt;
+  }
+}
+
 static bool rs_pipe_enabled() {
   static const bool on = [] {
     const char* e = getenv("B200TRAIN_RS_PIPE");
@@ -798,6 +829,35 @@ int b2_reduce_adamw(void* p, void* m, void* v, const void* g_local, const void* 
   return launch_reduce_local<true>(clamp_blocks(n16, max_blocks > 0 ? max_blocks : 296), stream, nullptr,
                                    static_cast<const V4*>(g_local), staged_ptrs(staging, n16, nstaged), nstaged,
                                    n16, grad_scale, a);
+}
+
+// lse[T], loss_row[T] from the W ranks' shard statistics (stats[r]: fp32 [3][T] in rank r's symmetric
+// memory, complete on every rank -- issue b2_peer_barrier first).
+int b2_ce_combine_peer(float* lse, float* loss_row, void* const* stats, const long long* labels, int T, int W,
+                       int ignore_index, cudaStream_t stream) {
+  B2_REQUIRE(W >= 1 && W <= kMaxPeers, "peer collectives support up to %d ranks (got %d)", kMaxPeers, W);
+  if (T == 0) return 0;
+  int blocks = (T + 255) / 256;
+  if (blocks > 296) blocks = 296;
+  ce_combine_peer_kernel<<<blocks, 256, 0, stream>>>(lse, loss_row, to_ptrs(stats, W), labels, T, W,
+                                                     ignore_index);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// Copy-engine strided pulls from the peers: for every rank j, `rows` rows of `width_bytes` from
+// srcs[j] + src_offset_bytes (pitch src_pitch) to dst + j * dst_step_bytes (pitch dst_pitch). Used for the
+// hidden-sharded -> sequence-sharded exchange of the tensor-parallel embedding output and its transpose.
+int b2_peer_pull_2d(void* dst, size_t dst_pitch, size_t dst_step_bytes, void* const* srcs, size_t src_offset_bytes,
+                    size_t src_pitch, size_t width_bytes, size_t rows, int rank, int W, cudaStream_t stream) {
+  B2_REQUIRE(W >= 1 && W <= kMaxPeers, "peer collectives support up to %d ranks (got %d)", kMaxPeers, W);
+  for (int k = 0; k < W; ++k) {
+    const int j = (rank + k) % W;
+    B2_CUDA_CHECK(cudaMemcpy2DAsync(static_cast<char*>(dst) + (size_t)j * dst_step_bytes, dst_pitch,
+                                    static_cast<const char*>(srcs[j]) + src_offset_bytes, src_pitch, width_bytes,
+                                    rows, cudaMemcpyDeviceToDevice, stream));
+  }
+  return 0;
 }
 
 // Spin bound of every cross-rank wait in this file (milliseconds; applies to the current device).

@@ -196,6 +196,16 @@ int b2_reduce_slices(void* out, const void* g_local, const void* staging, int ns
 int b2_reduce_adamw(void* p, void* m, void* v, const void* g_local, const void* staging, int nstaged,
                     size_t shard_elems, float grad_scale, float lr, float beta1, float beta2, float eps,
                     float wd, int step, int max_blocks, b2_stream_t stream);
+/* Tensor-parallel plan, small collectives in device code / on the copy engines.
+ * b2_ce_combine_peer: vocabulary-parallel cross entropy -- each rank combines the W shard statistics
+ * (fp32 [3][T]: row max, sum exp(x - max), target logit) by reading the peers' symmetric buffers, instead of
+ * the all-reduce(MAX) + all-reduce(SUM) of tp.loss_parallel (06-tensor-parallel/train_llm.py:239-243).
+ * b2_peer_pull_2d: strided copy-engine pulls from every peer, the hidden-sharded -> sequence-sharded
+ * exchange behind ColwiseParallel(output_layouts=Shard(1)) on embed_tokens (06-.../train_llm.py:84-88). */
+int b2_ce_combine_peer(float* lse, float* loss_row, void* const* stats, const long long* labels, int T, int W,
+                       int ignore_index, b2_stream_t stream);
+int b2_peer_pull_2d(void* dst, size_t dst_pitch, size_t dst_step_bytes, void* const* srcs, size_t src_offset_bytes,
+                    size_t src_pitch, size_t width_bytes, size_t rows, int rank, int W, b2_stream_t stream);
 /* bound (ms) of every cross-rank spin wait on the current device; past it the waiting kernel reports the
  * rank / channel / epoch it is stuck on and traps (a dead peer becomes a launch failure, not a hang) */
 int b2_comm_set_timeout_ms(unsigned long long ms);

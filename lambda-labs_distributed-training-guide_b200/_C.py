@@ -74,6 +74,8 @@ def _declare(lib):
         "b2_peer_all_gather": [P, P, Z, I, I, I, I, P],
         "b2_peer_all_gather_ce": [P, P, Z, I, I, I, I, P],
         "b2_comm_set_timeout_ms": [ctypes.c_ulonglong],
+        "b2_ce_combine_peer": [P, P, P, P, I, I, I, P],
+        "b2_peer_pull_2d": [P, Z, Z, P, Z, Z, Z, Z, I, I, P],
         "b2_signal_peers": [P, I, I, I, ctypes.c_uint, P],
         "b2_stream_wait_pad": [P, I, I, I, ctypes.c_uint, P],
         "b2_ce_pull_slices": [P, P, Z, I, I, P],

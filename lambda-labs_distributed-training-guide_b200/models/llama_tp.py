@@ -97,7 +97,8 @@ class TPLlamaForCausalLM(LlamaForCausalLM):
             logits = colwise(x, self.lm_head.weight, tp)                        # [T, V/tp]
             if shifted is None:
                 return logits
-            return ops.vocab_parallel_cross_entropy(logits, shifted, self.vocab_start, tp.group)
+            return ops.vocab_parallel_cross_entropy(logits, shifted, self.vocab_start, tp.group,
+                                                    peer=getattr(tp, "fused", None))
 
         out = self._run(L + 1, head, h, delta) if delta is not None else self._run(L + 1, head, h)
         if labels is None:

@@ -104,8 +104,10 @@ def linear_cross_entropy(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor)
 # ------------------------------------------------------------------------------------------------
 class _VocabParallelCE(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, logits, labels, vocab_start, group):
-        """logits [T, Vlocal] (this rank's vocabulary shard), labels [T] global ids (shifted)."""
+    def forward(ctx, logits, labels, vocab_start, group, peer=None):
+        """logits [T, Vlocal] (this rank's vocabulary shard), labels [T] global ids (shifted). ``peer``: the
+        tp group's peer-memory handle (``parallel/tp_fused.FusedTP``); with it the shard statistics are
+        combined by a kernel that reads the peers' memory instead of two NCCL all-reduces."""
         T, Vl = logits.shape
         labels = labels.contiguous()
         if use_kernels(logits):
@@ -122,14 +124,18 @@ class _VocabParallelCE(torch.autograd.Function):
             local = labels - vocab_start
             mine = (labels != IGNORE) & (local >= 0) & (local < Vl)
             ltgt = torch.where(mine, lf.gather(1, local.clamp(0, Vl - 1)[:, None])[:, 0], torch.zeros_like(lmax))
-        gmax = lmax.clone()
-        dist.all_reduce(gmax, op=dist.ReduceOp.MAX, group=group)
-        packed = torch.stack((lsum * torch.exp(lmax - gmax), ltgt))
-        dist.all_reduce(packed, op=dist.ReduceOp.SUM, group=group)
-        lse = gmax + torch.log(packed[0])
         valid = labels != IGNORE
         n_valid = valid.sum().clamp_(min=1)
-        loss = torch.where(valid, lse - packed[1], torch.zeros_like(lse)).sum() / n_valid
+        if peer is not None and use_kernels(logits):
+            lse, loss_rows = peer.ce_combine(stats, labels)
+            loss = loss_rows.sum() / n_valid
+        else:
+            gmax = lmax.clone()
+            dist.all_reduce(gmax, op=dist.ReduceOp.MAX, group=group)
+            packed = torch.stack((lsum * torch.exp(lmax - gmax), ltgt))
+            dist.all_reduce(packed, op=dist.ReduceOp.SUM, group=group)
+            lse = gmax + torch.log(packed[0])
+            loss = torch.where(valid, lse - packed[1], torch.zeros_like(lse)).sum() / n_valid
         ctx.save_for_backward(logits, labels, lse, n_valid)
         ctx.vocab_start = vocab_start
         return loss
@@ -150,9 +156,9 @@ class _VocabParallelCE(torch.autograd.Function):
             p[mine, local[mine]] -= 1.0
             p[labels == IGNORE] = 0
             dl = (p * scale_t).to(logits.dtype)
-        return dl, None, None, None
+        return dl, None, None, None, None
 
 
-def vocab_parallel_cross_entropy(logits, labels, vocab_start: int, group=None):
+def vocab_parallel_cross_entropy(logits, labels, vocab_start: int, group=None, peer=None):
     """Mean CE over vocabulary-sharded ``logits`` [T, V/tp]; ``labels`` are global, already shifted."""
-    return _VocabParallelCE.apply(logits, labels.reshape(-1), vocab_start, group)
+    return _VocabParallelCE.apply(logits, labels.reshape(-1), vocab_start, group, peer)

@@ -33,7 +33,7 @@ from .comm import TorchComm
 
 _ARENA_MIN_BYTES = 256 << 20
 _ALIGN = 256
-CHAN_RS, CHAN_AR, CHAN_BARRIER, CHAN_CE_IN, CHAN_CE_OUT = 0, 2, 4, 6, 7
+CHAN_RS, CHAN_AR, CHAN_BARRIER, CHAN_CE_IN, CHAN_CE_OUT = 0, 2, 4, 8, 9   # 6, 7: tp_fused barriers
 
 
 class _Arena:

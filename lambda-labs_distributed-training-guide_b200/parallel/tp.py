@@ -63,20 +63,33 @@ class Mesh2D:
             h.fused = FusedTP(self.tp_group, self.tp_rank, self.tp, device)
         return h
 
-    def dp_comm(self) -> Comm:
+    def dp_comm(self, device=None) -> Comm:
+        """Communicator of this rank's dp group: the peer-memory / NVLS kernels (their own symmetric arenas
+        and signal pad per mesh dimension) when the group lives on one node, NCCL otherwise."""
         if self.world == 1 or self.dp == 1:
             c = Comm()
             return c
-        return TorchComm(self.dp_group)
+        from .comm import make_comm
+
+        return make_comm(self.dp_group, True, device)
 
 
-def _reduce_replicated_grads(unit, tp: TPGroup):
-    """Sum the partial gradients of tp-replicated parameters (sequence-parallel norm weights) [N11]."""
+def _reduce_replicated_grads(units, tp: TPGroup):
+    """Sum the partial gradients of tp-replicated parameters (sequence-parallel norm weights) [N11]: every
+    such gradient of ``units`` (one unit, or the whole model) goes through ONE peer-memory all-reduce when the
+    tp group has a peer handle, else one NCCL call per parameter."""
     if tp.size == 1:
         return
-    for p in unit.params:
-        if getattr(p, "_b2_tp_replicated", False) and p.grad is not None:
-            tp.all_reduce_(p.grad)
+    grads = [p.grad for u in units for p in u.params
+             if getattr(p, "_b2_tp_replicated", False) and p.grad is not None]
+    if not grads:
+        return
+    fz = getattr(tp, "fused", None)
+    if fz is not None and grads[0].is_cuda and grads[0].dtype == torch.bfloat16:
+        fz.all_reduce_sum_(grads)
+        return
+    for g in grads:
+        tp.all_reduce_(g)
 
 
 def _init_tp_model(model: TPLlamaForCausalLM, cfg, device, dtype, seed):
@@ -98,12 +111,18 @@ class TensorParallel(Strategy):
         world = dist.get_world_size() if dist.is_initialized() else 1
         self.mesh = Mesh2D(tp or world)
         self.tpg = self.mesh.tp_handle(self.device)
-        self.dp_comm = self.mesh.dp_comm()
+        self.dp_comm = self.mesh.dp_comm(self.device)
         self.act_ckpt = activation_checkpointing
         self.model = TPLlamaForCausalLM(cfg, self.tpg, dtype=dtype, device=self.device)
         _init_tp_model(self.model, cfg, self.device, dtype, seed)
         self.model.train()
-        self.units = [FlatUnit(name, params) for name, params in self.model.units()]
+        if self.mesh.dp > 1:
+            # gradients are all-reduced over dp: place the flat buffers in the dp communicator's (symmetric) memory
+            self.units = [FlatUnit(name, params, pad_to=8 * self.mesh.dp,
+                                   alloc=lambda k: self.dp_comm.empty(k, dtype, self.device))
+                          for name, params in self.model.units()]
+        else:
+            self.units = [FlatUnit(name, params) for name, params in self.model.units()]
         self.optimizer = FlatAdamW(self.units, lr=lr)
         self.lr_scheduler = make_lr_scheduler(self.optimizer, lr)
         self.model.unit_runner = self._runner
@@ -124,13 +143,17 @@ class TensorParallel(Strategy):
     def post_backward(self, i):
         u = self.units[i]
         u.finalize_grads()
-        _reduce_replicated_grads(u, self.tpg)
         if self.mesh.dp > 1:
+            # replicas over dp consume the gradient unit by unit: sum the tp-partial norm gradients first
+            _reduce_replicated_grads([u], self.tpg)
             self.dp_comm.all_reduce(u.flat_grad, average=True)
 
     def backward(self, loss):
         loss.backward()
         self.post_backward(0)
+        if self.mesh.dp == 1:
+            # every sequence-parallel norm-weight gradient of the model in one all-reduce (65 tensors at 8B)
+            _reduce_replicated_grads(self.units, self.tpg)
 
     @property
     def rank(self):
@@ -162,7 +185,7 @@ class TwoD(FSDP):
         self.mesh = Mesh2D(tp)
         self.tpg = self.mesh.tp_handle(device)
         kw.pop("comm", None)
-        super().__init__(cfg, device, lr=lr, seed=seed, dtype=dtype, comm=self.mesh.dp_comm(), **kw)
+        super().__init__(cfg, device, lr=lr, seed=seed, dtype=dtype, comm=self.mesh.dp_comm(device), **kw)
 
     def _build_meta_model(self, cfg, dtype):
         return TPLlamaForCausalLM(cfg, self.tpg, dtype=dtype, device="meta")
@@ -171,7 +194,7 @@ class TwoD(FSDP):
         return seed * 7919 + self.mesh.tp_rank  # distinct shards per tp rank
 
     def pre_reduce(self, i):
-        _reduce_replicated_grads(self.units[i], self.tpg)
+        _reduce_replicated_grads([self.units[i]], self.tpg)
 
     @property
     def rank(self):

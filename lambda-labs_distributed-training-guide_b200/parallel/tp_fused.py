@@ -23,7 +23,7 @@ from ..ops.dispatch import keep_params, real_param
 from ..ops.linear import EPI_ACCUM, EPI_NONE, _direct_grad, gemm
 from .peer import PeerComm
 
-CHAN_AG_BARRIER, CHAN_RS_BARRIER = 6, 7
+CHAN_AG_BARRIER, CHAN_RS_BARRIER, CHAN_SMALL_BARRIER = 6, 7, 10
 
 
 class FusedTP:
@@ -39,7 +39,9 @@ class FusedTP:
         self._slot_bufs = {}  # (rows_per_rank, cols) -> [buf0, buf1]
         self._ag_i = 0
         self._rs_i = 0
-        self._bar_epochs = {CHAN_AG_BARRIER: 0, CHAN_RS_BARRIER: 0}
+        self._bar_epochs = {CHAN_AG_BARRIER: 0, CHAN_RS_BARRIER: 0, CHAN_SMALL_BARRIER: 0}
+        self._small = {}      # name -> [symmetric buf0, buf1] (double buffered: a rank may run one call ahead)
+        self._small_i = {}
 
     # ---- buffers (symmetric, two alternating copies; see module docstring of csrc/gemm.cu) ----------
     def ag_buffer(self, rows: int, cols: int) -> torch.Tensor:
@@ -61,6 +63,82 @@ class FusedTP:
         self._bar_epochs[chan] += 1
         _C.call("b2_peer_barrier", self.comm._pad_ptrs, self.rank, self.W, chan, self._bar_epochs[chan] & 0xFFFFFFFF,
                 torch.cuda.current_stream(self.device).cuda_stream)
+
+    # ---- the plan's small collectives, in device code / on the copy engines (N9, N10, N11) -------------------
+    def _small_buf(self, name: str, numel: int, dtype) -> torch.Tensor:
+        """Symmetric staging buffer ``name`` of at least ``numel`` elements; alternates between two copies so
+        a rank that is one call ahead never overwrites what a slower peer is still reading (the barrier in
+        every call bounds the lead to one)."""
+        nbytes = numel * torch.empty((), dtype=dtype).element_size()
+        pair = self._small.get(name)
+        if pair is None or pair[0].numel() < nbytes:
+            # every rank reaches this with the same sizes in the same order (symmetric allocation)
+            pair = [self.comm.empty(nbytes, torch.uint8) for _ in range(2)]
+            self._small[name] = pair
+            self._small_i[name] = 0
+        self._small_i[name] ^= 1
+        return pair[self._small_i[name]][:nbytes].view(dtype)
+
+    def _stream(self):
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def all_reduce_sum_(self, tensors):
+        """Sum a list of small bf16 tensors over the tp group in ONE in-switch (or peer) all-reduce: they are
+        packed into a symmetric buffer, reduced, and copied back (N11: the sequence-parallel norm-weight
+        gradients of a unit, or of the whole model)."""
+        sizes = [t.numel() for t in tensors]
+        total = sum(sizes)
+        q = 8 * self.W
+        padded = (total + q - 1) // q * q
+        buf = self._small_buf("ar", padded, torch.bfloat16)
+        if padded != total:
+            buf[total:].zero_()
+        views = list(buf[:total].split(sizes))
+        torch._foreach_copy_(views, [t.reshape(-1) for t in tensors])
+        self.comm.all_reduce(buf, average=False)
+        for t, v in zip(tensors, views):
+            t.copy_(v.view(t.shape))
+
+    def ce_combine(self, stats: torch.Tensor, labels: torch.Tensor):
+        """``stats`` fp32 [3, T] (row max, sum exp(x - max), target logit of this rank's vocabulary shard) ->
+        (lse [T], loss_row [T]) over the whole vocabulary, each rank reading the peers' statistics from peer
+        memory inside one kernel (N10)."""
+        T = stats.shape[1]
+        buf = self._small_buf("ce", 3 * T, torch.float32)
+        buf.copy_(stats.reshape(-1))
+        self._barrier(CHAN_SMALL_BARRIER)
+        lse = torch.empty(T, dtype=torch.float32, device=self.device)
+        loss_row = torch.empty(T, dtype=torch.float32, device=self.device)
+        _C.call("b2_ce_combine_peer", lse.data_ptr(), loss_row.data_ptr(), self.comm._peer_array(buf),
+                labels.data_ptr(), T, self.W, -100, self._stream())
+        return lse, loss_row
+
+    def hidden_to_seq(self, x: torch.Tensor) -> torch.Tensor:
+        """[T, H/tp] (all tokens, local hidden slice) -> [T/tp, H] (local tokens, full hidden): every rank
+        pulls its token rows of every peer's slice with strided copy-engine copies (N9)."""
+        T, Hl = x.shape
+        n = T // self.W
+        buf = self._small_buf("h2s", T * Hl, x.dtype)
+        buf.copy_(x.reshape(-1))
+        self._barrier(CHAN_SMALL_BARRIER)
+        out = torch.empty((n, self.W * Hl), dtype=x.dtype, device=self.device)
+        es = x.element_size()
+        _C.call("b2_peer_pull_2d", out.data_ptr(), self.W * Hl * es, Hl * es, self.comm._peer_array(buf),
+                self.rank * n * Hl * es, Hl * es, Hl * es, n, self.rank, self.W, self._stream())
+        return out
+
+    def seq_to_hidden(self, g: torch.Tensor) -> torch.Tensor:
+        """Transpose of :meth:`hidden_to_seq` (its backward): [T/tp, H] -> [T, H/tp]."""
+        n, H = g.shape
+        Hl = H // self.W
+        buf = self._small_buf("s2h", n * H, g.dtype)
+        buf.copy_(g.reshape(-1))
+        self._barrier(CHAN_SMALL_BARRIER)
+        out = torch.empty((self.W * n, Hl), dtype=g.dtype, device=self.device)
+        es = g.element_size()
+        _C.call("b2_peer_pull_2d", out.data_ptr(), Hl * es, n * Hl * es, self.comm._peer_array(buf),
+                self.rank * Hl * es, H * es, Hl * es, n, self.rank, self.W, self._stream())
+        return out
 
     # ---- all-gather of row chunks with per-chunk flags ------------------------------------------------
     def gather_rows(self, x_local: torch.Tensor):

@@ -104,6 +104,9 @@ class _HiddenToSeq(torch.autograd.Function):
     def forward(ctx, x, tp):
         ctx.tp = tp
         T, Hl = x.shape
+        fz = getattr(tp, "fused", None)
+        if fz is not None and x.is_cuda:                   # strided copy-engine pulls from peer memory
+            return fz.hidden_to_seq(x.contiguous())
         recv = tp.all_to_all_rows(x)                       # block j: my tokens' hidden slice j
         n = T // tp.size
         return recv.view(tp.size, n, Hl).transpose(0, 1).reshape(n, tp.size * Hl)
@@ -113,6 +116,9 @@ class _HiddenToSeq(torch.autograd.Function):
         tp = ctx.tp
         n, H = g.shape
         Hl = H // tp.size
+        fz = getattr(tp, "fused", None)
+        if fz is not None and g.is_cuda:
+            return fz.seq_to_hidden(g.contiguous()), None
         send = g.view(n, tp.size, Hl).transpose(0, 1).contiguous().view(tp.size * n, Hl)
         return tp.all_to_all_rows(send), None
 
