@@ -52,7 +52,15 @@ struct AttnBwdParams {
   int T, Hq, Hkv, ndocs;
   float scale, scale_log2;
   int causal;
+  AttnDropout drop;   // attention-probability dropout of the forward (thr == 0: none)
 };
+
+__global__ void attn_dropout_mask_kernel(unsigned char* keep, int S, int doc, AttnDropout d) {
+  const int g = blockIdx.x, q = blockIdx.y, h = blockIdx.z, i = threadIdx.x;
+  const uint4 bits = attn_dropout_bits(d, q, g, h, doc);
+  const int k = g * 16 + i;
+  if (k < S) keep[((size_t)h * S + q) * S + k] = dropout_keep(bits, i, d.thr) ? 1 : 0;
+}
 
 // delta[h, t] = sum_d dO[t, h, d] * O[t, h, d]
 // D / 8 lanes per (t, h) row, one 16-byte load of each tensor per lane, four rows in flight per lane
@@ -131,7 +139,7 @@ __device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* m, const vo
       : "memory");
 }
 
-template <int D>
+template <int D, bool kDrop = false>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
@@ -337,6 +345,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           if (lane_id() == 0) mbar_arrive(&sdp_free[s]);
         }
         uint32_t pp[16], dd[16];
+        uint4 bits0, bits1;
+        if constexpr (kDrop) {  // the forward's keep decisions for key positions kv0 + 32 hf + [0, 16), + [16, 32)
+          const int g = (kv0 + hf * 32) >> 4;
+          bits0 = attn_dropout_bits(p.drop, q_idx, g, head, doc);
+          bits1 = attn_dropout_bits(p.drop, q_idx, g + 1, head, doc);
+        }
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
           float pv[2], dv[2];
@@ -345,8 +359,15 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             const int c = 2 * i + e;
             const bool on = (kv0 + hf * 32 + c) <= lim;
             const float pe = on ? fast_exp2(__uint_as_float(sr[c]) * p.scale_log2 - lse2) : 0.f;
-            pv[e] = pe;
-            dv[e] = pe * (__uint_as_float(dr[c]) - delta) * p.scale;
+            if constexpr (kDrop) {
+              // O = (P o M / (1 - p)) V: dV sees the dropped, rescaled P; dS = P o (dP o M / (1 - p) - delta)
+              const bool keep = dropout_keep(c < 16 ? bits0 : bits1, c & 15, p.drop.thr);
+              pv[e] = keep ? pe * p.drop.scale : 0.f;
+              dv[e] = pe * ((keep ? __uint_as_float(dr[c]) * p.drop.scale : 0.f) - delta) * p.scale;
+            } else {
+              pv[e] = pe;
+              dv[e] = pe * (__uint_as_float(dr[c]) - delta) * p.scale;
+            }
           }
           pp[i] = pack_bf16(pv[0], pv[1]);
           dd[i] = pack_bf16(dv[0], dv[1]);
@@ -887,13 +908,13 @@ static int launch_attn_bwd2(const CUtensorMap& tmQ, const CUtensorMap& tmK, cons
   return 0;
 }
 
-template <int D>
+template <int D, bool kDrop = false>
 static int launch_attn_bwd(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
                            const CUtensorMap& tmDO, const CUtensorMap& tmDQ,
                            const AttnBwdParams& prm, int max_kblocks, int ndocs,
                            cudaStream_t stream) {
   using SM = AttnBwdSmem<D>;
-  auto kern = attn_bwd_kernel<D>;
+  auto kern = attn_bwd_kernel<D, kDrop>;
   static bool attr_set = false;
   if (!attr_set) {
     B2_CUDA_CHECK(
@@ -913,12 +934,12 @@ extern "C" {
 // Gradients of b2_attn_fwd. dq/dk/dv are strided [T, heads*D] bf16 views (e.g. slices of one fused
 // dQKV buffer). Scratch supplied by the caller: dq_accum fp32 [T, Hq*D] (zeroed here, contiguous),
 // delta fp32 [Hq, T].
-int b2_attn_bwd(void* dq, void* dk, void* dv, float* dq_accum, float* delta, const void* dout,
+static int attn_bwd_impl(void* dq, void* dk, void* dv, float* dq_accum, float* delta, const void* dout,
                 const void* q, const void* k, const void* v, const void* o, const float* lse,
                 const int* cu_seqlens, int ndocs, int max_seqlen, int T, int Hq, int Hkv, int D,
                 int q_stride, int k_stride, int v_stride, int o_stride, int do_stride,
                 int dq_stride, int dk_stride, int dv_stride, float softmax_scale, int causal,
-                cudaStream_t stream) {
+                const b2::AttnDropout& drop, cudaStream_t stream) {
   using namespace b2;
   B2_REQUIRE(D == 64 || D == 128, "attn bwd: head_dim %d unsupported (64 or 128)", D);
   B2_REQUIRE(Hq % Hkv == 0, "attn bwd: Hq=%d not a multiple of Hkv=%d", Hq, Hkv);
@@ -950,7 +971,7 @@ int b2_attn_bwd(void* dq, void* dk, void* dv, float* dq_accum, float* delta, con
     const char* e = getenv("B200TRAIN_ATTN_BWD_GEN");
     return !(e && e[0] == '1');
   }();
-  const bool v2 = want_v2 && D == 128 && dk_stride % 8 == 0 && dv_stride % 8 == 0 &&
+  const bool v2 = want_v2 && drop.thr == 0 && D == 128 && dk_stride % 8 == 0 && dv_stride % 8 == 0 &&
                   (reinterpret_cast<uintptr_t>(dk) & 15) == 0 && (reinterpret_cast<uintptr_t>(dv) & 15) == 0;
   const int qb = v2 ? QB2 : QB, kb = v2 ? KB2 : KB;
   CUtensorMap tmQ, tmK, tmV, tmDO, tmDQ;
@@ -976,8 +997,11 @@ int b2_attn_bwd(void* dq, void* dk, void* dv, float* dq_accum, float* delta, con
   prm.scale = softmax_scale;
   prm.scale_log2 = softmax_scale * 1.4426950408889634f;
   prm.causal = causal;
+  prm.drop = drop;
   const int max_kb = (max_seqlen + kb - 1) / kb;
   if (v2) rc = launch_attn_bwd2(tmQ, tmK, tmV, tmDO, tmDQ, prm, max_kb, ndocs, stream);
+  else if (drop.thr != 0 && D == 64) rc = launch_attn_bwd<64, true>(tmQ, tmK, tmV, tmDO, tmDQ, prm, max_kb, ndocs, stream);
+  else if (drop.thr != 0) rc = launch_attn_bwd<128, true>(tmQ, tmK, tmV, tmDO, tmDQ, prm, max_kb, ndocs, stream);
   else if (D == 64) rc = launch_attn_bwd<64>(tmQ, tmK, tmV, tmDO, tmDQ, prm, max_kb, ndocs, stream);
   else rc = launch_attn_bwd<128>(tmQ, tmK, tmV, tmDO, tmDQ, prm, max_kb, ndocs, stream);
   if (rc) return rc;
@@ -993,6 +1017,41 @@ int b2_attn_bwd(void* dq, void* dk, void* dv, float* dq_accum, float* delta, con
                                                            T, cols, dq_stride, v2 ? softmax_scale : 1.f);
     B2_CUDA_CHECK(cudaGetLastError());
   }
+  return 0;
+}
+
+int b2_attn_bwd(void* dq, void* dk, void* dv, float* dq_accum, float* delta, const void* dout,
+                const void* q, const void* k, const void* v, const void* o, const float* lse,
+                const int* cu_seqlens, int ndocs, int max_seqlen, int T, int Hq, int Hkv, int D,
+                int q_stride, int k_stride, int v_stride, int o_stride, int do_stride,
+                int dq_stride, int dk_stride, int dv_stride, float softmax_scale, int causal,
+                cudaStream_t stream) {
+  b2::AttnDropout none = {};
+  return attn_bwd_impl(dq, dk, dv, dq_accum, delta, dout, q, k, v, o, lse, cu_seqlens, ndocs, max_seqlen, T, Hq,
+                       Hkv, D, q_stride, k_stride, v_stride, o_stride, do_stride, dq_stride, dk_stride, dv_stride,
+                       softmax_scale, causal, none, stream);
+}
+
+// Gradients of b2_attn_fwd_dropout: the same (drop_p, seed, offset) regenerate the forward's mask.
+int b2_attn_bwd_dropout(void* dq, void* dk, void* dv, float* dq_accum, float* delta, const void* dout,
+                        const void* q, const void* k, const void* v, const void* o, const float* lse,
+                        const int* cu_seqlens, int ndocs, int max_seqlen, int T, int Hq, int Hkv, int D,
+                        int q_stride, int k_stride, int v_stride, int o_stride, int do_stride,
+                        int dq_stride, int dk_stride, int dv_stride, float softmax_scale, int causal,
+                        float drop_p, unsigned long long seed, unsigned long long offset,
+                        cudaStream_t stream) {
+  return attn_bwd_impl(dq, dk, dv, dq_accum, delta, dout, q, k, v, o, lse, cu_seqlens, ndocs, max_seqlen, T, Hq,
+                       Hkv, D, q_stride, k_stride, v_stride, o_stride, do_stride, dq_stride, dk_stride, dv_stride,
+                       softmax_scale, causal, b2::make_attn_dropout(drop_p, seed, offset), stream);
+}
+
+// Test helper: keep[h][q][k] (1 byte each) of one document of length S -- the mask b2_attn_fwd_dropout applies.
+int b2_attn_dropout_mask(unsigned char* keep, int Hq, int S, int doc, float drop_p, unsigned long long seed,
+                         unsigned long long offset, cudaStream_t stream) {
+  b2::AttnDropout d = b2::make_attn_dropout(drop_p, seed, offset);
+  dim3 grid((S + 15) / 16, S, Hq);
+  b2::attn_dropout_mask_kernel<<<grid, 16, 0, stream>>>(keep, S, doc, d);
+  B2_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
 

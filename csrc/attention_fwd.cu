@@ -48,6 +48,7 @@ struct AttnFwdParams {
   int q_col0, k_col0, v_col0;  // element offsets of head 0 inside the q/k/v row
   float scale_log2;            // softmax_scale * log2(e)
   int causal;
+  AttnDropout drop;            // attention-probability dropout (thr == 0: none)
 };
 
 template <int D>
@@ -380,7 +381,7 @@ struct AttnFwd1Smem {
   static constexpr int kTotal = kQ + kK + kV + 256 + 1024;
 };
 
-template <int D>
+template <int D, bool kDrop = false>
 __global__ void __launch_bounds__(kAttn1Threads, 2)
 attn_fwd1_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                  const __grid_constant__ CUtensorMap tmV, AttnFwdParams p) {
@@ -558,12 +559,23 @@ attn_fwd1_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
         uint32_t pk[16];
+        uint4 bits0, bits1;
+        if constexpr (kDrop) {  // keep decisions of key positions kv0 + 32 c + [0, 16) and + [16, 32)
+          const int g = (kv0 + c * 32) >> 4;
+          bits0 = attn_dropout_bits(p.drop, q_idx, g, head, doc);
+          bits1 = attn_dropout_bits(p.drop, q_idx, g + 1, head, doc);
+        }
 #pragma unroll
         for (int e = 0; e < 16; ++e) {
           const int i = c * 32 + e * 2;
-          const float p0 = fast_exp2(fmaf(sv[i], p.scale_log2, -base));
-          const float p1 = fast_exp2(fmaf(sv[i + 1], p.scale_log2, -base));
-          ps4[e & 3] += p0 + p1;
+          float p0 = fast_exp2(fmaf(sv[i], p.scale_log2, -base));
+          float p1 = fast_exp2(fmaf(sv[i + 1], p.scale_log2, -base));
+          ps4[e & 3] += p0 + p1;   // the normaliser is the sum of the un-dropped probabilities
+          if constexpr (kDrop) {
+            const uint4& b = e < 8 ? bits0 : bits1;
+            if (!dropout_keep(b, (2 * e) & 15, p.drop.thr)) p0 = 0.f;
+            if (!dropout_keep(b, (2 * e + 1) & 15, p.drop.thr)) p1 = 0.f;
+          }
           pk[e] = pack_bf16(p0, p1);
         }
         tmem_st_32x32b_x16(tmem_S + lane_off + c * 16, pk);  // P_j over the first 64 columns of S_j
@@ -580,7 +592,8 @@ attn_fwd1_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       tc_fence_after();
     }
     const bool valid = q_idx < doc_len;
-    const float inv_l = l > 0.f ? 1.f / l : 0.f;
+    float inv_l = l > 0.f ? 1.f / l : 0.f;
+    if constexpr (kDrop) inv_l *= p.drop.scale;   // kept probabilities are scaled by 1 / (1 - p)
     __nv_bfloat16* orow = p.o + (size_t)(doc_start + q_idx) * p.o_stride + (size_t)head * D;
 #pragma unroll
     for (int c = 0; c < D / 32; ++c) {
@@ -618,12 +631,12 @@ attn_fwd1_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   }
 }
 
-template <int D>
+template <int D, bool kDrop = false>
 static int launch_attn_fwd1(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
                             const AttnFwdParams& prm, int max_qblocks, int ndocs,
                             cudaStream_t stream) {
   using SM = AttnFwd1Smem<D>;
-  auto kern = attn_fwd1_kernel<D>;
+  auto kern = attn_fwd1_kernel<D, kDrop>;
   static bool attr_set = false;
   if (!attr_set) {
     B2_CUDA_CHECK(
@@ -661,10 +674,10 @@ extern "C" {
 // q/k/v are row-major [T, *_stride] bf16 views whose head h starts at column h * D (q: Hq heads,
 // k/v: Hkv heads); they may alias one fused QKV buffer. o: [T, o_stride], lse: [Hq, T] fp32.
 // cu_seqlens: device int32 [ndocs+1] document boundaries; max_seqlen bounds the longest document.
-int b2_attn_fwd(void* o, float* lse, const void* q, const void* k, const void* v,
-                const int* cu_seqlens, int ndocs, int max_seqlen, int T, int Hq, int Hkv, int D,
-                int q_stride, int k_stride, int v_stride, int o_stride, float softmax_scale,
-                int causal, cudaStream_t stream) {
+static int attn_fwd_impl(void* o, float* lse, const void* q, const void* k, const void* v,
+                         const int* cu_seqlens, int ndocs, int max_seqlen, int T, int Hq, int Hkv, int D,
+                         int q_stride, int k_stride, int v_stride, int o_stride, float softmax_scale,
+                         int causal, const b2::AttnDropout& drop, cudaStream_t stream) {
   using namespace b2;
   B2_REQUIRE(D == 64 || D == 128, "attn: head_dim %d unsupported (64 or 128)", D);
   B2_REQUIRE(Hq % Hkv == 0, "attn: Hq=%d not a multiple of Hkv=%d", Hq, Hkv);
@@ -687,7 +700,12 @@ int b2_attn_fwd(void* o, float* lse, const void* q, const void* k, const void* v
   prm.q_col0 = prm.k_col0 = prm.v_col0 = 0;
   prm.scale_log2 = softmax_scale * 1.4426950408889634f;
   prm.causal = causal;
+  prm.drop = drop;
   const int max_qb = (max_seqlen + ABM - 1) / ABM;
+  if (drop.thr != 0) {
+    if (D == 64) return launch_attn_fwd1<64, true>(tmQ, tmK, tmV, prm, max_qb, ndocs, stream);
+    return launch_attn_fwd1<128, true>(tmQ, tmK, tmV, prm, max_qb, ndocs, stream);
+  }
   // default: one warpgroup per CTA, two CTAs per SM; B200TRAIN_ATTN_FWD_PINGPONG=1 selects the ping-pong kernel
   static const bool pingpong = [] {
     const char* e = getenv("B200TRAIN_ATTN_FWD_PINGPONG");
@@ -699,6 +717,28 @@ int b2_attn_fwd(void* o, float* lse, const void* q, const void* k, const void* v
   }
   if (D == 64) return launch_attn_fwd1<64>(tmQ, tmK, tmV, prm, max_qb, ndocs, stream);
   return launch_attn_fwd1<128>(tmQ, tmK, tmV, prm, max_qb, ndocs, stream);
+}
+
+int b2_attn_fwd(void* o, float* lse, const void* q, const void* k, const void* v,
+                const int* cu_seqlens, int ndocs, int max_seqlen, int T, int Hq, int Hkv, int D,
+                int q_stride, int k_stride, int v_stride, int o_stride, float softmax_scale,
+                int causal, cudaStream_t stream) {
+  b2::AttnDropout none = {};
+  return attn_fwd_impl(o, lse, q, k, v, cu_seqlens, ndocs, max_seqlen, T, Hq, Hkv, D, q_stride, k_stride,
+                       v_stride, o_stride, softmax_scale, causal, none, stream);
+}
+
+// The same forward with dropout on the attention probabilities (GPT-2's attn_pdrop): a probability is kept
+// when its Philox byte is >= round(256 p), so the effective rate is round(256 p) / 256 and the kept ones are
+// scaled by its reciprocal complement. b2_attn_bwd_dropout regenerates the mask from (seed, offset).
+int b2_attn_fwd_dropout(void* o, float* lse, const void* q, const void* k, const void* v,
+                        const int* cu_seqlens, int ndocs, int max_seqlen, int T, int Hq, int Hkv, int D,
+                        int q_stride, int k_stride, int v_stride, int o_stride, float softmax_scale,
+                        int causal, float drop_p, unsigned long long seed, unsigned long long offset,
+                        cudaStream_t stream) {
+  b2::AttnDropout d = b2::make_attn_dropout(drop_p, seed, offset);
+  return attn_fwd_impl(o, lse, q, k, v, cu_seqlens, ndocs, max_seqlen, T, Hq, Hkv, D, q_stride, k_stride,
+                       v_stride, o_stride, softmax_scale, causal, d, stream);
 }
 
 }  // extern "C"

@@ -109,6 +109,50 @@ __device__ __forceinline__ void wait_flag_geq(const uint32_t* flag, uint32_t epo
 }
 
 // ----------------------------------------------------------------------------------------------
+// counter-based random numbers for dropout (Philox4x32-10): the mask is a pure function of
+// (seed, offset, element coordinates), so backward regenerates it instead of storing it
+// ----------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+    c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+    k.x += 0x9E3779B9u;
+    k.y += 0xBB67AE85u;
+  }
+  return c;
+}
+// Attention-probability dropout: 16 keep decisions (one byte each, keep iff byte >= thr) for the 16 key
+// positions [16 g, 16 g + 16) of query row q of (head, document). Forward and backward call this with the
+// same arguments.
+struct AttnDropout {
+  unsigned long long seed, offset;
+  uint32_t thr;   // 0: no dropout; drop probability = thr / 256
+  float scale;    // 1 / (1 - thr / 256)
+};
+inline AttnDropout make_attn_dropout(float p, unsigned long long seed, unsigned long long offset) {
+  AttnDropout d = {};
+  int thr = (int)(p * 256.f + 0.5f);
+  if (thr < 0) thr = 0;
+  if (thr > 255) thr = 255;
+  d.seed = seed;
+  d.offset = offset;
+  d.thr = (uint32_t)thr;
+  d.scale = 256.f / (256.f - (float)thr);
+  return d;
+}
+__device__ __forceinline__ uint4 attn_dropout_bits(const AttnDropout& d, int q, int g, int head, int doc) {
+  const uint2 key = make_uint2((uint32_t)d.seed ^ (uint32_t)d.offset,
+                               (uint32_t)(d.seed >> 32) ^ (uint32_t)(d.offset >> 32) ^ 0x85EBCA6Bu);
+  return philox4x32_10(make_uint4((uint32_t)q, (uint32_t)g, (uint32_t)head, (uint32_t)doc), key);
+}
+__device__ __forceinline__ bool dropout_keep(const uint4& bits, int i, uint32_t thr) {  // i in [0, 16)
+  const uint32_t w = i < 4 ? bits.x : (i < 8 ? bits.y : (i < 12 ? bits.z : bits.w));
+  return ((w >> ((i & 3) * 8)) & 0xffu) >= thr;
+}
+
+// ----------------------------------------------------------------------------------------------
 // mbarrier
 // ----------------------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {

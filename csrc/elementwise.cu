@@ -981,6 +981,26 @@ adamw_kernel(__nv_bfloat16* __restrict__ p, __nv_bfloat16* __restrict__ m,
   }
 }
 
+// Elementwise dropout: out = keep ? x / (1 - p) : 0 with the keep mask a pure function of (seed, offset,
+// element index) -- backward calls the same kernel on the gradient. Eight elements per thread from two
+// Philox4x32-10 blocks; an element is kept when its 32-bit draw is >= p * 2^32 (exact drop rate).
+__global__ void __launch_bounds__(256)
+dropout_kernel(__nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ x, size_t nvec, uint32_t thr,
+               float scale, unsigned long long seed, unsigned long long offset) {
+  const uint2 key = make_uint2((uint32_t)seed ^ (uint32_t)offset,
+                               (uint32_t)(seed >> 32) ^ (uint32_t)(offset >> 32) ^ 0x27D4EB2Fu);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x) {
+    const uint4 r0 = philox4x32_10(make_uint4((uint32_t)i, (uint32_t)(i >> 32), 0u, 0u), key);
+    const uint4 r1 = philox4x32_10(make_uint4((uint32_t)i, (uint32_t)(i >> 32), 1u, 0u), key);
+    const uint32_t r[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+    float v[8];
+    bf8_to_f(ld_stream(reinterpret_cast<const BF8*>(x) + i), v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = r[j] >= thr ? v[j] * scale : 0.f;
+    st_stream(reinterpret_cast<BF8*>(out) + i, f_to_bf8(v));
+  }
+}
+
 // out = a + b (bf16), used for gradient accumulation into flat buffers and residual joins
 __global__ void add_kernel(__nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ a,
                            const __nv_bfloat16* __restrict__ b, size_t nvec) {
@@ -1254,6 +1274,20 @@ int b2_adamw(void* p, void* m, void* v, const void* g, size_t n, float lr, float
   B2_SIDE_KERNEL((adamw_kernel));   // runs beside the GEMMs of backward on the optimizer stream
   adamw_kernel<<<grid, 256, 0, stream>>>((bf16*)p, (bf16*)m, (bf16*)v, (const bf16*)g, n, lr,
                                          beta1, beta2, eps, wd, bc1, sqrtf(bc2), grad_scale);
+  B2_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// out[n] = dropout(x) with drop probability p (n % 8 == 0); out may alias x. Same (seed, offset) -> same mask.
+int b2_dropout(void* out, const void* x, size_t n, float p, unsigned long long seed, unsigned long long offset,
+               cudaStream_t stream) {
+  B2_REQUIRE(n % 8 == 0, "dropout: n not a multiple of 8");
+  B2_REQUIRE(p >= 0.f && p < 1.f, "dropout: p=%f out of range", p);
+  if (n == 0) return 0;
+  const double t = (double)p * 4294967296.0;
+  const uint32_t thr = t >= 4294967295.0 ? 4294967295u : (uint32_t)t;
+  dropout_kernel<<<ew_grid(n / 8, 256), 256, 0, stream>>>((bf16*)out, (const bf16*)x, n / 8, thr, 1.f / (1.f - p),
+                                                          seed, offset);
   B2_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

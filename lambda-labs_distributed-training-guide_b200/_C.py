@@ -16,7 +16,7 @@ import torch
 _LIB = None
 _LAUNCHES = 0
 # kernels launched per library call (for the bench's launch count)
-_LAUNCH_MULT = {"b2_rmsnorm_bwd": 2, "b2_layernorm_bwd": 2, "b2_attn_bwd": 3, "b2_rmsnorm_bwd_partial_rows": 0,
+_LAUNCH_MULT = {"b2_rmsnorm_bwd": 2, "b2_layernorm_bwd": 2, "b2_attn_bwd": 3, "b2_attn_bwd_dropout": 3, "b2_rmsnorm_bwd_partial_rows": 0,
                 "b2_colsum": 2, "b2_colsum_partial_rows": 0}
 _LIB_PATH = Path(__file__).resolve().parent / "_lib" / "libb200train.so"
 
@@ -52,6 +52,12 @@ def _declare(lib):
         "b2_ce_bwd": [P, P, P, P, I, I, I, I, I, F, P, P],
         "b2_adamw": [P, P, P, P, Z, F, F, F, F, F, I, F, I, P],
         "b2_add": [P, P, P, Z, P],
+        "b2_dropout": [P, P, Z, F, ctypes.c_ulonglong, ctypes.c_ulonglong, P],
+        "b2_attn_fwd_dropout": [P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, F, I, F, ctypes.c_ulonglong,
+                                ctypes.c_ulonglong, P],
+        "b2_attn_bwd_dropout": [P, P, P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, I, I, I, I, F, I,
+                                F, ctypes.c_ulonglong, ctypes.c_ulonglong, P],
+        "b2_attn_dropout_mask": [P, I, I, I, F, ctypes.c_ulonglong, ctypes.c_ulonglong, P],
         "b2_colsum_partial_rows": [I, I],
         "b2_colsum": [P, P, P, I, I, I, I, P],
         "b2_gemm_ag": [P, P, P, I, I, I, I, I, I, I, P, ctypes.c_uint, I, I, I, P],

@@ -30,7 +30,7 @@ class ModelConfig:
     rope_scaling: Optional[dict] = None
     tie_word_embeddings: bool = False
     initializer_range: float = 0.02
-    # GPT-2 dropout (HF default 0.1 x3). The kernels implement p=0; see DESIGN.md.
+    # GPT-2 dropout, one rate for HF's embd_pdrop / attn_pdrop / resid_pdrop (all 0.1 in GPT2Config's defaults)
     dropout: float = 0.0
     name: str = ""
 
@@ -75,7 +75,7 @@ _LLAMA3_SCALING = {"factor": 8.0, "low_freq_factor": 1.0, "high_freq_factor": 4.
 PRESETS = {
     "gpt2": dict(model_type="gpt2", vocab_size=50257, hidden_size=768, intermediate_size=3072,
                  num_hidden_layers=12, num_attention_heads=12, num_key_value_heads=12,
-                 max_position_embeddings=1024, tie_word_embeddings=True),
+                 max_position_embeddings=1024, tie_word_embeddings=True, dropout=0.1),
     "llama-2-7b": dict(vocab_size=32000, hidden_size=4096, intermediate_size=11008, num_hidden_layers=32,
                        num_attention_heads=32, num_key_value_heads=32, max_position_embeddings=4096,
                        rope_theta=10000.0),
@@ -125,6 +125,7 @@ def _from_hf_dict(d: dict, name: str) -> ModelConfig:
                            max_position_embeddings=d.get("n_positions", 1024),
                            layer_norm_epsilon=d.get("layer_norm_epsilon", 1e-5),
                            tie_word_embeddings=d.get("tie_word_embeddings", True),
+                           dropout=float(d.get("resid_pdrop", 0.1)),   # GPT2Config default (one rate for the 3 sites)
                            initializer_range=d.get("initializer_range", 0.02), name=name)
     rope_scaling = d.get("rope_scaling")
     rope_theta = d.get("rope_theta", 10000.0)

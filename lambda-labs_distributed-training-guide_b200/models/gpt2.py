@@ -2,8 +2,10 @@
 ``python train_llm.py -m openai-community/gpt2``, ``01-single-gpu/README.md:9-15``).
 
 HF parameter names are kept (``transformer.h.N.attn.c_attn.weight`` ..., Conv1D weights stored [in, out],
-``lm_head`` tied to ``wte``). HF's GPT-2 config defaults to dropout 0.1 in three places; these kernels
-implement p = 0 (documented in DESIGN.md) and the reference arm is configured identically.
+``lm_head`` tied to ``wte``). HF's GPT-2 config defaults to dropout 0.1 at three sites and ``from_config``
+leaves the module in training mode (``02-distributed-data-parallel/train_llm.py:60-62``): ``cfg.dropout`` is
+applied to the embedding sum (embd_pdrop), to the attention probabilities inside the attention kernels
+(attn_pdrop) and to both residual branches (resid_pdrop), with Philox masks regenerated in backward.
 """
 from __future__ import annotations
 
@@ -48,11 +50,13 @@ class GPT2Attention(nn.Module):
         self.n_head, self.D = cfg.num_attention_heads, cfg.head_dim
         self.c_attn = Conv1D(3 * H, H, dtype, device)
         self.c_proj = Conv1D(H, H, dtype, device)
+        self.pdrop = cfg.dropout
 
     def forward(self, x, ctx):
         qkv = self.c_attn(x)
-        o = ops.attention(qkv, ctx.cu_seqlens, ctx.max_seqlen, self.n_head, self.n_head, self.D)
-        return self.c_proj(o)
+        p = self.pdrop if self.training else 0.0
+        o = ops.attention(qkv, ctx.cu_seqlens, ctx.max_seqlen, self.n_head, self.n_head, self.D, dropout_p=p)
+        return ops.dropout(self.c_proj(o), self.pdrop, self.training)      # attn_pdrop inside, resid_pdrop after
 
 
 class GPT2MLP(nn.Module):
@@ -60,9 +64,10 @@ class GPT2MLP(nn.Module):
         super().__init__()
         self.c_fc = Conv1D(cfg.intermediate_size, cfg.hidden_size, dtype, device)
         self.c_proj = Conv1D(cfg.hidden_size, cfg.intermediate_size, dtype, device)
+        self.pdrop = cfg.dropout
 
     def forward(self, x):
-        return self.c_proj(ops.gelu_new(self.c_fc(x)))
+        return ops.dropout(self.c_proj(ops.gelu_new(self.c_fc(x))), self.pdrop, self.training)   # resid_pdrop
 
 
 class GPT2Block(nn.Module):
@@ -155,7 +160,9 @@ class GPT2LMHeadModel(nn.Module):
         if position_ids is None:
             position_ids = torch.arange(S, device=input_ids.device).repeat(B)
         flat_ids, flat_pos = input_ids.reshape(-1), position_ids.reshape(-1)
-        h = self._run(0, lambda: ops.embedding(flat_ids, t.wte.weight) + ops.embedding(flat_pos, t.wpe.weight))
+        pdrop, training = self.config.dropout, self.training
+        h = self._run(0, lambda: ops.dropout(ops.embedding(flat_ids, t.wte.weight)
+                                             + ops.embedding(flat_pos, t.wpe.weight), pdrop, training))   # embd_pdrop
         delta = None
         groups = self._groups()
         for gi, g in enumerate(groups):

@@ -2,6 +2,7 @@
 from .activation import gelu_new, swiglu
 from .attention import attention
 from .cross_entropy import (IGNORE, linear_cross_entropy, shift_labels, vocab_parallel_cross_entropy)
+from .dropout import dropout
 from .embedding import embedding
 from .fused import linear_rope, mlp_swiglu
 from .linear import gemm, linear
@@ -12,5 +13,5 @@ from .rope import rope_qk, rope_tables
 __all__ = [
     "gelu_new", "swiglu", "attention", "IGNORE", "linear_cross_entropy", "shift_labels",
     "vocab_parallel_cross_entropy", "embedding", "gemm", "linear", "layernorm", "rmsnorm", "adamw_step",
-    "rope_qk", "rope_tables", "linear_rope", "mlp_swiglu",
+    "rope_qk", "rope_tables", "linear_rope", "mlp_swiglu", "dropout",
 ]

@@ -29,19 +29,35 @@ def _split(qkv, n_q, n_kv, D):
     return q, k, v
 
 
-def attn_fwd_raw(q, k, v, cu_seqlens, max_seqlen, n_q, n_kv, D, scale, causal=True):
-    """Forward on strided [T, heads*D] views; returns (o [T, Hq*D], lse [Hq, T])."""
+def attn_fwd_raw(q, k, v, cu_seqlens, max_seqlen, n_q, n_kv, D, scale, causal=True, dropout=None):
+    """Forward on strided [T, heads*D] views; returns (o [T, Hq*D], lse [Hq, T]). ``dropout``: None or
+    ``(p, seed, offset)`` for dropout on the attention probabilities."""
     T = q.shape[0]
     o = torch.empty((T, n_q * D), dtype=torch.bfloat16, device=q.device)
     lse = torch.empty((n_q, T), dtype=torch.float32, device=q.device)
+    if dropout is not None:
+        _C.call("b2_attn_fwd_dropout", o.data_ptr(), lse.data_ptr(), q.data_ptr(), k.data_ptr(), v.data_ptr(),
+                cu_seqlens.data_ptr(), cu_seqlens.numel() - 1, max_seqlen, T, n_q, n_kv, D, q.stride(0),
+                k.stride(0), v.stride(0), o.stride(0), scale, int(causal), *dropout, stream(q))
+        return o, lse
     _C.call("b2_attn_fwd", o.data_ptr(), lse.data_ptr(), q.data_ptr(), k.data_ptr(), v.data_ptr(),
             cu_seqlens.data_ptr(), cu_seqlens.numel() - 1, max_seqlen, T, n_q, n_kv, D, q.stride(0),
             k.stride(0), v.stride(0), o.stride(0), scale, int(causal), stream(q))
     return o, lse
 
 
-def attn_bwd_raw(do, q, k, v, o, lse, dq, dk, dv, cu_seqlens, max_seqlen, n_q, n_kv, D, scale, causal=True):
+def attn_bwd_raw(do, q, k, v, o, lse, dq, dk, dv, cu_seqlens, max_seqlen, n_q, n_kv, D, scale, causal=True,
+                 dropout=None):
     T = q.shape[0]
+    if dropout is not None:
+        dq_accum = torch.empty((T, n_q * D), dtype=torch.float32, device=q.device)
+        delta = torch.empty((n_q, T), dtype=torch.float32, device=q.device)
+        _C.call("b2_attn_bwd_dropout", dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), dq_accum.data_ptr(),
+                delta.data_ptr(), do.data_ptr(), q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(),
+                lse.data_ptr(), cu_seqlens.data_ptr(), cu_seqlens.numel() - 1, max_seqlen, T, n_q, n_kv, D,
+                q.stride(0), k.stride(0), v.stride(0), o.stride(0), do.stride(0), dq.stride(0), dk.stride(0),
+                dv.stride(0), scale, int(causal), *dropout, stream(q))
+        return
     if BWD_IMPL == "flash_attn":
         from flash_attn.flash_attn_interface import _flash_attn_varlen_backward
 
@@ -62,29 +78,29 @@ def attn_bwd_raw(do, q, k, v, o, lse, dq, dk, dv, cu_seqlens, max_seqlen, n_q, n
 
 class _Attention(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, qkv, cu_seqlens, max_seqlen, n_q, n_kv, D, scale, causal):
+    def forward(ctx, qkv, cu_seqlens, max_seqlen, n_q, n_kv, D, scale, causal, dropout=None):
         check_bf16(qkv)
         assert qkv.dim() == 2 and qkv.is_contiguous()
         q, k, v = _split(qkv, n_q, n_kv, D)
-        o, lse = attn_fwd_raw(q, k, v, cu_seqlens, max_seqlen, n_q, n_kv, D, scale, causal)
+        o, lse = attn_fwd_raw(q, k, v, cu_seqlens, max_seqlen, n_q, n_kv, D, scale, causal, dropout)
         ctx.save_for_backward(qkv, o, lse, cu_seqlens)
-        ctx.args = (max_seqlen, n_q, n_kv, D, scale, causal)
+        ctx.args = (max_seqlen, n_q, n_kv, D, scale, causal, dropout)
         return o
 
     @staticmethod
     def backward(ctx, do):
         qkv, o, lse, cu_seqlens = ctx.saved_tensors
-        max_seqlen, n_q, n_kv, D, scale, causal = ctx.args
+        max_seqlen, n_q, n_kv, D, scale, causal, dropout = ctx.args
         do = do.contiguous()
         dqkv = torch.empty_like(qkv)
         q, k, v = _split(qkv, n_q, n_kv, D)
         dq, dk, dv = _split(dqkv, n_q, n_kv, D)
-        attn_bwd_raw(do, q, k, v, o, lse, dq, dk, dv, cu_seqlens, max_seqlen, n_q, n_kv, D, scale, causal)
-        return dqkv, None, None, None, None, None, None, None
+        attn_bwd_raw(do, q, k, v, o, lse, dq, dk, dv, cu_seqlens, max_seqlen, n_q, n_kv, D, scale, causal, dropout)
+        return dqkv, None, None, None, None, None, None, None, None
 
 
-def attention_ref(qkv, cu_seqlens, max_seqlen, n_q, n_kv, D, scale=None, causal=True):
-    """fp32 PyTorch reference over each document separately."""
+def attention_ref(qkv, cu_seqlens, max_seqlen, n_q, n_kv, D, scale=None, causal=True, dropout_p=0.0):
+    """fp32 PyTorch reference over each document separately (``dropout_p``: torch's own mask)."""
     scale = scale if scale is not None else 1.0 / math.sqrt(D)
     T = qkv.shape[0]
     q, k, v = _split(qkv, n_q, n_kv, D)
@@ -102,7 +118,8 @@ def attention_ref(qkv, cu_seqlens, max_seqlen, n_q, n_kv, D, scale=None, causal=
             vi = v[s:e].transpose(0, 1).unsqueeze(0)
             if g > 1:
                 ki, vi = ki.repeat_interleave(g, dim=1), vi.repeat_interleave(g, dim=1)
-            oi = torch.nn.functional.scaled_dot_product_attention(qi, ki, vi, is_causal=causal, scale=scale)
+            oi = torch.nn.functional.scaled_dot_product_attention(qi, ki, vi, is_causal=causal, scale=scale,
+                                                                  dropout_p=dropout_p)
             outs.append(oi[0].transpose(0, 1).reshape(e - s, n_q * D))
             continue
         qi = q[s:e].transpose(0, 1).float()
@@ -113,14 +130,27 @@ def attention_ref(qkv, cu_seqlens, max_seqlen, n_q, n_kv, D, scale=None, causal=
             L = e - s
             mask = torch.ones(L, L, dtype=torch.bool, device=qkv.device).tril()
             att = att.masked_fill(~mask, float("-inf"))
-        oi = torch.softmax(att, dim=-1) @ vi
+        pi = torch.softmax(att, dim=-1)
+        if dropout_p > 0.0:
+            pi = torch.nn.functional.dropout(pi, dropout_p)
+        oi = pi @ vi
         outs.append(oi.transpose(0, 1).reshape(e - s, n_q * D))
     return torch.cat(outs, 0).to(qkv.dtype)
 
 
 def attention(qkv: torch.Tensor, cu_seqlens: torch.Tensor, max_seqlen: int, n_q: int, n_kv: int,
-              head_dim: int, scale: float | None = None, causal: bool = True) -> torch.Tensor:
+              head_dim: int, scale: float | None = None, causal: bool = True, dropout_p: float = 0.0,
+              philox=None) -> torch.Tensor:
+    """``dropout_p`` > 0: dropout on the attention probabilities inside the kernels (forward applies a Philox
+    mask keyed on (seed, offset, head, query, key); backward regenerates it). ``philox``: explicit
+    ``(seed, offset)``, else drawn from the default CPU generator."""
     scale = scale if scale is not None else 1.0 / math.sqrt(head_dim)
     if use_kernels(qkv):
-        return _Attention.apply(qkv, cu_seqlens, max_seqlen, n_q, n_kv, head_dim, scale, causal)
-    return attention_ref(qkv, cu_seqlens, max_seqlen, n_q, n_kv, head_dim, scale, causal)
+        drop = None
+        if dropout_p > 0.0:
+            from .dropout import next_philox
+
+            seed, offset = philox if philox is not None else next_philox()
+            drop = (float(dropout_p), seed, offset)
+        return _Attention.apply(qkv, cu_seqlens, max_seqlen, n_q, n_kv, head_dim, scale, causal, drop)
+    return attention_ref(qkv, cu_seqlens, max_seqlen, n_q, n_kv, head_dim, scale, causal, dropout_p)
