@@ -927,11 +927,24 @@ __device__ __forceinline__ void adamw_vec(float (&pf)[8], float (&mf)[8], float 
   }
 }
 
+// store of an updated parameter vector: plain, or (ZeRO-1) one multimem.st on the multicast mapping of the
+// replicated flat parameter buffer, which lands the owner's update in every rank's copy at once -- the
+// "broadcast of updated params" of ZeroRedundancyOptimizer (N3) without a separate all-gather
+__device__ __forceinline__ void st_param(BF8* p, BF8* p_mc, size_t i, const BF8& v) {
+  if (p_mc == nullptr) {
+    st_stream(p + i, v);
+  } else {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p_mc + i), "r"(v.u[0]),
+                 "r"(v.u[1]), "r"(v.u[2]), "r"(v.u[3])
+                 : "memory");
+  }
+}
+
 __global__ void __launch_bounds__(256)
 adamw_kernel(__nv_bfloat16* __restrict__ p, __nv_bfloat16* __restrict__ m,
              __nv_bfloat16* __restrict__ v, const __nv_bfloat16* __restrict__ g, size_t n, float lr,
              float beta1, float beta2, float eps, float wd, float bc1, float bc2_sqrt,
-             float grad_scale) {
+             float grad_scale, __nv_bfloat16* p_mc) {
   const size_t nvec = n >> 3;
   const float decay = 1.f - lr * wd, step_size = lr / bc1, inv_bc2_sqrt = 1.f / bc2_sqrt;
   const size_t stride = (size_t)gridDim.x * blockDim.x;
@@ -946,12 +959,12 @@ adamw_kernel(__nv_bfloat16* __restrict__ p, __nv_bfloat16* __restrict__ m,
     float pf[8], mf[8], vf[8], gf[8];
     bf8_to_f(p0, pf); bf8_to_f(m0, mf); bf8_to_f(v0, vf); bf8_to_f(g0, gf);
     adamw_vec(pf, mf, vf, gf, decay, beta1, beta2, eps, step_size, inv_bc2_sqrt, grad_scale);
-    st_stream(reinterpret_cast<BF8*>(p) + i, f_to_bf8(pf));
+    st_param(reinterpret_cast<BF8*>(p), reinterpret_cast<BF8*>(p_mc), i, f_to_bf8(pf));
     st_stream(reinterpret_cast<BF8*>(m) + i, f_to_bf8(mf));
     st_stream(reinterpret_cast<BF8*>(v) + i, f_to_bf8(vf));
     bf8_to_f(p1, pf); bf8_to_f(m1, mf); bf8_to_f(v1, vf); bf8_to_f(g1, gf);
     adamw_vec(pf, mf, vf, gf, decay, beta1, beta2, eps, step_size, inv_bc2_sqrt, grad_scale);
-    st_stream(reinterpret_cast<BF8*>(p) + i1, f_to_bf8(pf));
+    st_param(reinterpret_cast<BF8*>(p), reinterpret_cast<BF8*>(p_mc), i1, f_to_bf8(pf));
     st_stream(reinterpret_cast<BF8*>(m) + i1, f_to_bf8(mf));
     st_stream(reinterpret_cast<BF8*>(v) + i1, f_to_bf8(vf));
   }
@@ -962,7 +975,7 @@ adamw_kernel(__nv_bfloat16* __restrict__ p, __nv_bfloat16* __restrict__ m,
     bf8_to_f(reinterpret_cast<const BF8*>(v)[i], vf);
     bf8_to_f(reinterpret_cast<const BF8*>(g)[i], gf);
     adamw_vec(pf, mf, vf, gf, decay, beta1, beta2, eps, step_size, inv_bc2_sqrt, grad_scale);
-    reinterpret_cast<BF8*>(p)[i] = f_to_bf8(pf);
+    st_param(reinterpret_cast<BF8*>(p), reinterpret_cast<BF8*>(p_mc), i, f_to_bf8(pf));
     reinterpret_cast<BF8*>(m)[i] = f_to_bf8(mf);
     reinterpret_cast<BF8*>(v)[i] = f_to_bf8(vf);
   }
@@ -1261,10 +1274,12 @@ int b2_ce_bwd(void* dlogits, const void* logits, const float* lse, const long lo
   return 0;
 }
 
-int b2_adamw(void* p, void* m, void* v, const void* g, size_t n, float lr, float beta1,
-             float beta2, float eps, float wd, int step, float grad_scale, int max_blocks,
-             cudaStream_t stream) {
+static int adamw_impl(void* p, void* m, void* v, const void* g, size_t n, float lr, float beta1,
+                      float beta2, float eps, float wd, int step, float grad_scale, int max_blocks, void* p_mc,
+                      cudaStream_t stream) {
   if (n == 0) return 0;
+  B2_REQUIRE(p_mc == nullptr || (n % 8 == 0 && (uintptr_t)p_mc % 16 == 0),
+             "adamw: a multicast parameter store needs n %% 8 == 0 (n=%zu) and a 16B aligned address", n);
   B2_REQUIRE(((uintptr_t)p | (uintptr_t)m | (uintptr_t)v | (uintptr_t)g) % 16 == 0,
              "adamw: buffers must be 16B aligned");
   const float bc1 = 1.f - powf(beta1, (float)step);
@@ -1273,9 +1288,25 @@ int b2_adamw(void* p, void* m, void* v, const void* g, size_t n, float lr, float
   if (max_blocks > 0 && grid > max_blocks) grid = max_blocks;
   B2_SIDE_KERNEL((adamw_kernel));   // runs beside the GEMMs of backward on the optimizer stream
   adamw_kernel<<<grid, 256, 0, stream>>>((bf16*)p, (bf16*)m, (bf16*)v, (const bf16*)g, n, lr,
-                                         beta1, beta2, eps, wd, bc1, sqrtf(bc2), grad_scale);
+                                         beta1, beta2, eps, wd, bc1, sqrtf(bc2), grad_scale, (bf16*)p_mc);
   B2_CUDA_CHECK(cudaGetLastError());
   return 0;
+}
+
+int b2_adamw(void* p, void* m, void* v, const void* g, size_t n, float lr, float beta1,
+             float beta2, float eps, float wd, int step, float grad_scale, int max_blocks,
+             cudaStream_t stream) {
+  return adamw_impl(p, m, v, g, n, lr, beta1, beta2, eps, wd, step, grad_scale, max_blocks, nullptr, stream);
+}
+
+// ZeRO-1: p is this rank's slice of a flat parameter buffer that every rank replicates in symmetric memory and
+// p_mc the multicast address of the same slice: the updated parameters are written with multimem.st, i.e.
+// into every rank's copy (including this one's). Follow with b2_peer_barrier before anyone reads them.
+int b2_adamw_multicast(void* p, void* p_mc, void* m, void* v, const void* g, size_t n, float lr, float beta1,
+                       float beta2, float eps, float wd, int step, float grad_scale, int max_blocks,
+                       cudaStream_t stream) {
+  B2_REQUIRE(p_mc != nullptr, "adamw_multicast: no multicast mapping%s", "");
+  return adamw_impl(p, m, v, g, n, lr, beta1, beta2, eps, wd, step, grad_scale, max_blocks, p_mc, stream);
 }
 
 // out[n] = dropout(x) with drop probability p (n % 8 == 0); out may alias x. Same (seed, offset) -> same mask.

@@ -166,6 +166,14 @@ int b2_stream_wait_flags(const unsigned int* flags, int first, int count, unsign
                          b2_stream_t stream);
 int b2_local_copy(void* dst, const void* src, size_t bytes, int blocks, b2_stream_t stream);
 
+/* ZeRO-1 parameter re-assembly inside the optimizer kernel: b2_adamw on this rank's slice, the updated
+ * parameters stored through the multicast address p_mc of the same slice (multimem.st), so every rank's
+ * replica is updated by the owner -- the broadcast of ZeroRedundancyOptimizer.step()
+ * (02-distributed-data-parallel/train_llm.py:81-83,163). Follow with b2_peer_barrier. */
+int b2_adamw_multicast(void* p, void* p_mc, void* m, void* v, const void* g, size_t n, float lr, float beta1,
+                       float beta2, float eps, float wd, int step, float grad_scale, int max_blocks,
+                       b2_stream_t stream);
+
 /* ---- NVLink / NVSwitch peer-memory collectives (one process per GPU, one node) -------------------
  * Pointer arrays hold W peer-mapped addresses of the same symmetric buffer, index = rank. `pads` is the
  * symmetric signal pad (uint32 [channel][16]); `epoch` increases by one per call and channel pair;

@@ -51,6 +51,7 @@ def _declare(lib):
         "b2_ce_shard_stats": [P, P, P, P, P, I, I, I, I, I, P],
         "b2_ce_bwd": [P, P, P, P, I, I, I, I, I, F, P, P],
         "b2_adamw": [P, P, P, P, Z, F, F, F, F, F, I, F, I, P],
+        "b2_adamw_multicast": [P, P, P, P, P, Z, F, F, F, F, F, I, F, I, P],
         "b2_add": [P, P, P, Z, P],
         "b2_dropout": [P, P, Z, F, ctypes.c_ulonglong, ctypes.c_ulonglong, P],
         "b2_attn_fwd_dropout": [P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, F, I, F, ctypes.c_ulonglong,

@@ -26,10 +26,15 @@ def adamw_step_ref(p, g, m, v, lr, beta1, beta2, eps, wd, step, grad_scale=1.0):
 
 
 def adamw_step(p, g, m, v, lr, beta1=0.9, beta2=0.999, eps=1e-8, wd=0.01, step=1, grad_scale=1.0,
-               max_blocks=0):
-    """In-place AdamW update of the flat tensors ``p, m, v`` from ``g`` (all same numel/dtype)."""
+               max_blocks=0, p_mc: int = 0):
+    """In-place AdamW update of the flat tensors ``p, m, v`` from ``g`` (all same numel/dtype). ``p_mc``: the
+    multicast address of ``p`` (ZeRO-1 over symmetric memory): the updated parameters are then stored into
+    every rank's replica with ``multimem.st`` instead of being gathered afterwards."""
     assert p.numel() == g.numel() == m.numel() == v.numel()
-    if use_kernels(p) and p.dtype == torch.bfloat16:
+    if p_mc and use_kernels(p) and p.dtype == torch.bfloat16:
+        _C.call("b2_adamw_multicast", p.data_ptr(), p_mc, m.data_ptr(), v.data_ptr(), g.data_ptr(), p.numel(), lr,
+                beta1, beta2, eps, wd, step, grad_scale, max_blocks, stream(p))
+    elif use_kernels(p) and p.dtype == torch.bfloat16:
         _C.call("b2_adamw", p.data_ptr(), m.data_ptr(), v.data_ptr(), g.data_ptr(), p.numel(), lr, beta1,
                 beta2, eps, wd, step, grad_scale, max_blocks, stream(p))
     elif (p.device.type == "cpu" and p.dtype == torch.bfloat16 and _cpu_kernel_ok()

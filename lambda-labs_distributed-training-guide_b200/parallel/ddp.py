@@ -16,6 +16,7 @@ Reference: ``DistributedDataParallel(model, device_ids=[local_rank])`` + ``ZeroR
 from __future__ import annotations
 
 import contextlib
+import os
 from typing import Optional
 
 import torch
@@ -38,6 +39,7 @@ class DDP(Strategy):
         self.comm = comm if comm is not None else make_comm(group, prefer_peer, self.device)
         self.W, self.R = self.comm.world, self.comm.rank
         self.zero1 = zero1 and self.W > 1
+        self._zero1_mc = os.environ.get("B200TRAIN_ZERO1_MULTICAST", "1") != "0"
         self.fuse_optimizer = fuse_optimizer
         self.is_cuda = self.device.type == "cuda"
         self.sync_grads = True
@@ -127,17 +129,31 @@ class DDP(Strategy):
         self._stepped.add(i)
         with self._on_comm():
             self._wait(after, self.comm_stream)
-            self.optimizer.step_unit(i, max_blocks=96 if self.is_cuda else 0)
+            self.optimizer.step_unit(i, max_blocks=96 if self.is_cuda else 0, p_mc=self._param_mc(i))
             self._reassemble(i)
             self._param_events[i] = self._record(self.comm_stream)
 
+    def _param_mc(self, i) -> int:
+        """ZeRO-1 over symmetric memory with an NVSwitch: multicast address of this rank's slice of unit ``i``'s
+        flat parameters (0: none -- the slices are gathered after the update instead)."""
+        if not (self.zero1 and self.is_cuda and self._zero1_mc):
+            return 0
+        mc = self.comm._mc_ptr(self.units[i].flat_param) if hasattr(self.comm, "_mc_ptr") else 0
+        if not mc:
+            return 0
+        u = self.units[i]
+        return mc + self.R * (u.numel // self.W) * u.flat_param.element_size()
+
     def _reassemble(self, i):
-        """ZeRO-1: gather the updated parameter slices back into every replica (N3)."""
+        """ZeRO-1: make every replica hold the updated parameter slices (N3). With a multicast mapping the
+        AdamW kernel has already stored its slice into every rank's copy (``multimem.st``) and a device-side
+        barrier is all that is left; otherwise the slices are gathered by the copy engines."""
         if not self.zero1:
             return
         u = self.units[i]
         self.comm.stream_barrier()  # every owner finished updating its slice
-        self.comm.all_gather_inplace(u.flat_param)
+        if not self._param_mc(i):
+            self.comm.all_gather_inplace(u.flat_param)
 
     # ---- phases ---------------------------------------------------------------------------------------
     def backward(self, loss):
@@ -160,7 +176,7 @@ class DDP(Strategy):
             self.optimizer.begin_step()
         for i in range(len(self.units)):
             if i not in self._stepped:
-                self.optimizer.step_unit(i)
+                self.optimizer.step_unit(i, p_mc=self._param_mc(i))
                 self._reassemble(i)
         self._stepped.clear()
         self._param_events.clear()

@@ -53,7 +53,7 @@ class FlatAdamW(torch.optim.Optimizer):
         self._opt_called = True  # lets torch LR schedulers see that an optimizer step happened
 
     def step_unit(self, i: int, max_blocks: int = 0, grad: Optional[torch.Tensor] = None,
-                  param: Optional[torch.Tensor] = None):
+                  param: Optional[torch.Tensor] = None, p_mc: int = 0):
         """Update unit ``i``. ``grad`` / ``param`` override the flat buffers (sharded strategies pass
         their reduced gradient shard and their owned parameter shard)."""
         u = self.units[i]
@@ -62,7 +62,7 @@ class FlatAdamW(torch.optim.Optimizer):
         p = param if param is not None else u.flat_param[lo:hi]
         gr = grad if grad is not None else u.flat_grad[lo:hi]
         adamw_step(p, gr, self.exp_avg[i], self.exp_avg_sq[i], g["lr"], g["betas"][0], g["betas"][1], g["eps"],
-                   g["weight_decay"], self._step, self.grad_scale, max_blocks)
+                   g["weight_decay"], self._step, self.grad_scale, max_blocks, p_mc=p_mc)
 
     @torch.no_grad()
     def step(self, closure=None):
