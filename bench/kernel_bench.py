@@ -193,10 +193,57 @@ def bench_elementwise(results):
         print(k, {a: round(b, 3) for a, b in r.items()}, flush=True)
 
 
+def bench_fused(results):
+    """GEMMs with fused epilogues against the kernel sequences they replace (one Llama-3.1-8B layer)."""
+    from b200train import _C
+    from b200train.ops.dispatch import stream
+
+    T, H, I = 4096, 4096, 14336
+    n_rot = 2
+    xs = [rnd(T, H) for _ in range(n_rot)]
+    w_gu, w_d, w_qkv = rnd(2 * I, H), rnd(H, I), rnd(6144, H)
+    gu = torch.empty(T, 2 * I, device="cuda", dtype=torch.bfloat16)
+    h = torch.empty(T, I, device="cuda", dtype=torch.bfloat16)
+    nul = (None, 0, 0, 0, 0, 0, 0, 0)
+    st = stream(gu)
+    r = results["fused"]
+    flops = 2.0 * T * 2 * I * H
+    ms = timeit(lambda i: _C.call("b2_gemm_swiglu", gu.data_ptr(), h.data_ptr(), xs[i].data_ptr(), w_gu.data_ptr(), T, I,
+                                  H, H, H, 2 * I, I, *nul, st), n_rot)
+    r["gateup_swiglu_fused"] = {"ms": ms, "tflops": flops / ms / 1e9}
+    ms = timeit(lambda i: ops.swiglu(gemm(xs[i], w_gu, out=gu)), n_rot)
+    r["gateup_then_swiglu"] = {"ms": ms, "tflops": flops / ms / 1e9}
+    dys = [rnd(T, H) for _ in range(n_rot)]
+    dgu = torch.empty_like(gu)
+    flops = 2.0 * T * I * H
+    ms = timeit(lambda i: _C.call("b2_gemm_dswiglu", dgu.data_ptr(), dys[i].data_ptr(), w_d.data_ptr(), gu.data_ptr(), T,
+                                  I, H, H, I, 2 * I, 2 * I, *nul, st), n_rot)
+    r["down_dgrad_dswiglu_fused"] = {"ms": ms, "tflops": flops / ms / 1e9}
+    dh = torch.empty(T, I, device="cuda", dtype=torch.bfloat16)
+
+    def unfused_bwd(i):
+        gemm(dys[i], w_d, b_mn=True, out=dh)
+        _C.call("b2_swiglu_bwd", dgu.data_ptr(), dh.data_ptr(), gu.data_ptr(), T, I, st)
+
+    ms = timeit(unfused_bwd, n_rot)
+    r["down_dgrad_then_swiglu_bwd"] = {"ms": ms, "tflops": flops / ms / 1e9}
+    cos, sin = ops.rope_tables(128, 8192, 500000.0, None, device="cuda")
+    qkv = torch.empty(T, 6144, device="cuda", dtype=torch.bfloat16)
+    flops = 2.0 * T * 6144 * H
+    ms = timeit(lambda i: _C.call("b2_gemm_rope", qkv.data_ptr(), xs[i].data_ptr(), w_qkv.data_ptr(), T, 6144, H, H, H,
+                                  6144, cos.data_ptr(), sin.data_ptr(), None, 40, T, *nul, st), n_rot)
+    r["qkv_rope_fused"] = {"ms": ms, "tflops": flops / ms / 1e9}
+    ms = timeit(lambda i: ops.rope_qk(gemm(xs[i], w_qkv, out=qkv), cos, sin, None, 40, 128, T), n_rot)
+    r["qkv_then_rope"] = {"ms": ms, "tflops": flops / ms / 1e9}
+    for k, v in r.items():
+        v["frac_of_measured_peak"] = v["tflops"] / PEAKS["bf16_tflops"]
+        print(k, {a: round(b, 3) for a, b in v.items()}, flush=True)
+
+
 if __name__ == "__main__":
     quick = "--quick" in sys.argv
-    results = {"peaks": PEAKS, "gemm": {}, "attention": {}, "elementwise": {}}
-    fns = (bench_gemm, bench_attention, bench_elementwise)
+    results = {"peaks": PEAKS, "gemm": {}, "attention": {}, "elementwise": {}, "fused": {}}
+    fns = (bench_gemm, bench_attention, bench_elementwise, bench_fused)
     if "--no-gemm" in sys.argv:
         fns = fns[1:]
     if "--only-gemm" in sys.argv:

@@ -940,6 +940,10 @@ __device__ __forceinline__ void st_param(BF8* p, BF8* p_mc, size_t i, const BF8&
   }
 }
 
+// kSide only makes two distinct functions: the one launched beside the GEMMs of backward asks for the GEMM's
+// shared-memory carveout (see B2_SIDE_KERNEL); the stand-alone one keeps the default, because with 28 KB of
+// L1 left a streaming kernel cannot keep enough loads in flight (0.61 vs 0.50 ms per 218 M parameters)
+template <bool kSide>
 __global__ void __launch_bounds__(256)
 adamw_kernel(__nv_bfloat16* __restrict__ p, __nv_bfloat16* __restrict__ m,
              __nv_bfloat16* __restrict__ v, const __nv_bfloat16* __restrict__ g, size_t n, float lr,
@@ -1286,9 +1290,14 @@ static int adamw_impl(void* p, void* m, void* v, const void* g, size_t n, float 
   const float bc2 = 1.f - powf(beta2, (float)step);
   int grid = ew_grid(n / 8 + 1, 256);
   if (max_blocks > 0 && grid > max_blocks) grid = max_blocks;
-  B2_SIDE_KERNEL((adamw_kernel));   // runs beside the GEMMs of backward on the optimizer stream
-  adamw_kernel<<<grid, 256, 0, stream>>>((bf16*)p, (bf16*)m, (bf16*)v, (const bf16*)g, n, lr,
-                                         beta1, beta2, eps, wd, bc1, sqrtf(bc2), grad_scale, (bf16*)p_mc);
+  if (max_blocks > 0) {  // capped grid = launched beside the GEMMs of backward on the optimizer stream
+    B2_SIDE_KERNEL((adamw_kernel<true>));
+    adamw_kernel<true><<<grid, 256, 0, stream>>>((bf16*)p, (bf16*)m, (bf16*)v, (const bf16*)g, n, lr, beta1,
+                                                 beta2, eps, wd, bc1, sqrtf(bc2), grad_scale, (bf16*)p_mc);
+  } else {
+    adamw_kernel<false><<<grid, 256, 0, stream>>>((bf16*)p, (bf16*)m, (bf16*)v, (const bf16*)g, n, lr, beta1,
+                                                  beta2, eps, wd, bc1, sqrtf(bc2), grad_scale, (bf16*)p_mc);
+  }
   B2_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
