@@ -85,6 +85,26 @@ def run_reference(chapter: str, hf_config: dict, batch_size: int, seq_len: int, 
             if p.exists():
                 p.unlink()
 
+    if chapter == "fsdp405":
+        # chapter 05 loads the model on rank 0 with from_pretrained(--model-name) and reads HF_HOME: give it a
+        # local checkpoint directory -- random-init weights of the named architecture written once as safetensors
+        # (there is no network for the real checkpoint)
+        os.environ.setdefault("HF_HOME", str(work / "hf_home"))
+        marker = model_dir / "weights.done"
+        if rank == 0 and not marker.exists():
+            from transformers import AutoConfig, AutoModelForCausalLM
+
+            nthreads = torch.get_num_threads()
+            torch.set_num_threads(max(nthreads, min(32, os.cpu_count() or 1)))
+            cfg_obj = AutoConfig.from_pretrained(str(model_dir))
+            m = AutoModelForCausalLM.from_config(cfg_obj, torch_dtype=torch.bfloat16)
+            m.save_pretrained(str(model_dir), safe_serialization=True)
+            del m
+            torch.set_num_threads(nthreads)
+            marker.write_text("ok")
+        while not marker.exists():
+            time.sleep(1.0)
+
     vocab = hf_config["vocab_size"]
     dp = dp_size or world            # chapters 06/07 sample over the dp coordinate only
     n_items = (warmup + steps) * batch_size * dp

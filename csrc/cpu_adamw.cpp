@@ -85,6 +85,21 @@ static bool has_avx512() {
 }
 #endif
 
+#if defined(_OPENMP)
+#include <omp.h>
+#endif
+// Threads of the host optimizer. torchrun exports OMP_NUM_THREADS=1 to every rank, which would leave the
+// offloaded AdamW on one core; the FSDP strategy calls this with cores / local ranks when it offloads
+// (the reference sets OMP_NUM_THREADS=26 by hand: 05-training-llama-405b/launch.sh:18).
+extern "C" int b2_cpu_set_threads(int n) {
+#if defined(_OPENMP)
+  if (n > 0) omp_set_num_threads(n);
+  return omp_get_max_threads();
+#else
+  return 1;
+#endif
+}
+
 extern "C" int b2_cpu_adamw_bf16(void* p_, void* m_, void* v_, const void* g_, size_t n, float lr,
                                  float beta1, float beta2, float eps, float wd, int step,
                                  float grad_scale) {

@@ -124,8 +124,10 @@ class FSDP(Strategy):
         else:
             # transient full buffers: current + prefetched (+ the tied embedding kept resident);
             # without resharding every unit keeps its gathered copy for the whole step
-            self.param_pool = _BufferPool((3 + int(tied)) if self.reshard else n_units, max_numel, dtype,
-                                          self.device, dedicated_first=tied and self.reshard)
+            # offload: gathers start with a PCIe copy of the shard, so they are prefetched two units ahead
+            self.prefetch = 2 if cpu_offload else 1
+            self.param_pool = _BufferPool((2 + self.prefetch + int(tied)) if self.reshard else n_units, max_numel,
+                                          dtype, self.device, dedicated_first=tied and self.reshard)
             # gradient buffers are read by the peers' reduce-scatter: allocate them through the comm
             self.grad_pool = _BufferPool(2 + int(tied), max_numel, dtype, self.device, dedicated_first=tied,
                                          alloc=(None if cpu_offload else
@@ -187,7 +189,19 @@ class FSDP(Strategy):
         if cpu_offload and self.is_cuda:
             from concurrent.futures import ThreadPoolExecutor
 
-            self._cpu_worker = ThreadPoolExecutor(max_workers=1)
+            # two workers: one can sit in the event wait of the next unit's gradient copy while the other updates
+            self._cpu_worker = ThreadPoolExecutor(max_workers=2)
+            # torchrun pins every rank to OMP_NUM_THREADS=1: give the host AdamW its share of the cores instead
+            local = int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("WORLD_SIZE", "1")))
+            want = int(os.environ.get("B200TRAIN_CPU_ADAMW_THREADS", "0")) or max(1, (os.cpu_count() or 8) // local - 2)
+            try:
+                from .. import _C
+
+                lib = _C.load()
+                if hasattr(lib, "b2_cpu_set_threads"):
+                    lib.b2_cpu_set_threads(want)
+            except Exception:
+                pass
         self.model.unit_runner = self._runner
         self.model.train()
 
@@ -330,7 +344,8 @@ class FSDP(Strategy):
         self._ensure(i)
         if self._tied_head(i):
             self._ensure(0)
-        self._gather(i + 1)
+        for k in range(1, getattr(self, "prefetch", 1) + 1):
+            self._gather(i + k)
 
     def post_forward(self, i):
         last = i == len(self.units) - 1
@@ -353,7 +368,8 @@ class FSDP(Strategy):
         if self._tied_head(i):
             self._ensure(0)
             self._assign_grad_buffer(0)
-        self._gather(i - 1)
+        for k in range(1, getattr(self, "prefetch", 1) + 1):
+            self._gather(i - k)
 
     def post_backward(self, i):
         u = self.units[i]
