@@ -86,14 +86,22 @@ def main():
         ids = torch.randint(0, cfg.vocab_size, (B, S), generator=g)
         return {"input_ids": ids.pin_memory(), "labels": ids.clone().pin_memory()}
 
+    sys.path.insert(0, ROOT)
+    from bench import ClockSampler, PEAK_BF16_TFLOPS, _physical_gpu_index   # the headline bench's sampler / peaks
+
     batches = [batch(i) for i in range(args.warmup + args.steps)]
     for i in range(args.warmup):
         loss = eng.train_step(batches[i])
     float(loss)
+    sampler = ClockSampler(_physical_gpu_index(local_rank))
+    sampler.start()
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
+    # the timed region is end to end through the public API: every step copies its pinned host batch to the
+    # device and reads the loss back (4 bytes)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
     e0.record()
     for i in range(args.steps):
         loss = eng.train_step(batches[args.warmup + i])
@@ -102,13 +110,20 @@ def main():
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
-    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    sampler.stop()
+    sampler.join(timeout=2)
+    t = torch.tensor([e0.elapsed_time(e1), wall_ms], dtype=torch.float64, device=device)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = t.item() / args.steps
+    ms = t[0].item() / args.steps
     tokens = dp * B * S
+    h2d = sum(x.numel() * x.element_size() for x in batches[0].values())
     out.update(tokens_per_s=round(tokens / ms * 1e3, 1), ms_per_step=round(ms, 2), final_loss=round(lv, 4),
-               mfu_vs_measured_burst=round(tokens / ms * 1e3 * cfg.flops_per_token(S) / (world * 1637.5e12), 4),
+               mfu_vs_measured_burst=round(tokens / ms * 1e3 * cfg.flops_per_token(S) / (world * PEAK_BF16_TFLOPS * 1e12), 4),
+               e2e={"value": round(tokens * args.steps / max(t[0].item(), t[1].item()) * 1e3, 1), "unit": "tokens/s",
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
+               clocks=sampler.summary(),
                peak_alloc_gb=round(torch.cuda.max_memory_allocated() / 1e9, 1))
     if rank == 0:
         print(json.dumps(out), flush=True)

@@ -133,6 +133,28 @@ def test_group_texts_and_seq_length_clamp():
     assert resolve_seq_length(8192, 2048, 512) == 512
 
 
+def test_host_adamw_kernel_matches_reference_math():
+    """The vectorised host AdamW (csrc/cpu_adamw.cpp: AVX-512 where available, scalar otherwise) against the
+    plain PyTorch expression on bf16 buffers, including a length that is not a multiple of the vector width."""
+    from b200train.ops.optim import _cpu_kernel_ok, adamw_step, adamw_step_ref
+
+    if not _cpu_kernel_ok():
+        pytest.skip("native library unavailable")
+    torch.manual_seed(0)
+    n = 100_003
+    p = (torch.randn(n) * 0.02).bfloat16()
+    g = (torch.randn(n) * 0.01).bfloat16()
+    m, v = torch.zeros(n).bfloat16(), torch.zeros(n).bfloat16()
+    p2, m2, v2 = p.clone(), m.clone(), v.clone()
+    for step in (1, 2, 3):
+        adamw_step(p, g, m, v, 1e-3, step=step)
+        adamw_step_ref(p2, g, m2, v2, 1e-3, 0.9, 0.999, 1e-8, 0.01, step)
+    # fused multiply-adds round differently from separate operations: at most one bf16 ulp apart
+    assert (p.float() - p2.float()).abs().max().item() <= 2 ** -7 * 0.1
+    assert (m.float() - m2.float()).abs().max().item() <= 1e-4
+    assert (v.float() - v2.float()).abs().max().item() <= 1e-6
+
+
 def test_tokenizer_failure_is_loud(tmp_path, monkeypatch):
     """A model name without tokenizer files must raise (as AutoTokenizer does in the reference), not fall
     back to byte-level tokens; the byte tokenizer is for the tiny presets or an explicit opt-in."""
