@@ -4,7 +4,6 @@ Reference: HF ``LlamaMLP.forward`` ``down(act_fn(gate(x)) * up(x))`` and GPT-2 `
 """
 from __future__ import annotations
 
-import math
 
 import torch
 

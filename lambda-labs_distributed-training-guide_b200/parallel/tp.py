@@ -24,7 +24,7 @@ from ..models.llama_tp import TPLlamaForCausalLM
 from ..utils.flat import FlatUnit
 from ..utils.schedule import make_lr_scheduler
 from .base import Strategy
-from .comm import Comm, TorchComm
+from .comm import Comm
 from .fsdp import FSDP
 from .hooks import run_unit
 from .optimizer import FlatAdamW

@@ -165,6 +165,56 @@ def w_dcp(rank, world, tmp):
         return nxt, got, files
 
 
+def w_dcp_stock(rank, world, tmp):
+    """A checkpoint directory written by STOCK torch.distributed.checkpoint code -- DTensors sharded on dim 0
+    under the reference's keys (``model.<hf name>``, ``optimizer.state.<hf name>.exp_avg`` ...), which is
+    what ``04-fully-sharded-data-parallel/train_llm.py:252-258`` produces -- must load into this framework's
+    flat-shard FSDP, and a directory written here must load back into plain DTensor containers."""
+    from pathlib import Path
+
+    import torch.distributed.checkpoint as DCP
+    from torch.distributed.device_mesh import init_device_mesh
+    from torch.distributed.tensor import Shard, distribute_tensor
+
+    from b200train.ckpt.dcp import load_sharded, save_sharded
+    from b200train.models import build_model, load_config
+    from b200train.parallel import make_strategy
+
+    cfg = load_config("llama-tiny")
+    mesh = init_device_mesh("cpu", (world,), mesh_dim_names=("dp",))
+    src = build_model(cfg, device="cpu", dtype=torch.float32, seed=123)       # the "other framework's" weights
+    sd = {k: v.detach().clone() for k, v in src.hf_state_dict().items()}
+    state = {"model": {}, "optimizer": {"state": {}, "param_groups": [
+        {"lr": 5e-4, "betas": [0.9, 0.999], "eps": 1e-8, "weight_decay": 0.01, "initial_lr": 1e-3}]}}
+    for k, v in sd.items():
+        v2 = v.reshape(1) if v.dim() == 0 else v
+        state["model"][k] = distribute_tensor(v2, mesh, [Shard(0)])
+        state["optimizer"]["state"][k] = {"step": torch.tensor(7.0),
+                                          "exp_avg": distribute_tensor(v2 * 0.5, mesh, [Shard(0)]),
+                                          "exp_avg_sq": distribute_tensor(v2 * v2, mesh, [Shard(0)])}
+    DCP.save(state, checkpoint_id=Path(tmp) / "stock" / "checkpoint")
+    eng = make_strategy("fsdp", cfg, "cpu", lr=1e-3, dtype=torch.float32, seed=5)
+    load_sharded(Path(tmp) / "stock", eng)
+    got = eng.model_state_dict()
+    worst = max((got[k].float() - sd[k].float()).abs().max().item() for k in sd)
+    lr, step = eng.optimizer.param_groups[0]["lr"], eng.optimizer._step
+    # the other direction: our directory into plain DTensor containers
+    save_sharded(Path(tmp) / "ours", eng, state={"epoch": 0, "global_step": 7, "epoch_step": 7, "running_loss": 0.0},
+                 lr_scheduler=eng.lr_scheduler)
+    back = {"model": {k: distribute_tensor(torch.zeros_like(v.reshape(1) if v.dim() == 0 else v), mesh, [Shard(0)])
+                      for k, v in sd.items()}}
+    DCP.load(back, checkpoint_id=Path(tmp) / "ours" / "checkpoint")
+    worst_back = max((back["model"][k].full_tensor().reshape(sd[k].shape) - sd[k]).abs().max().item() for k in sd)
+    return worst, lr, step, worst_back
+
+
+def test_dcp_interoperates_with_stock_dtensor_checkpoints():
+    tmp = tempfile.mkdtemp()
+    worst, lr, step, worst_back = run_dist("w_dcp_stock", tmp)[0]
+    assert worst == 0.0 and worst_back == 0.0, (worst, worst_back)
+    assert abs(lr - 5e-4) < 1e-12 and step == 7, (lr, step)
+
+
 def test_dcp_sharded_roundtrip():
     tmp = tempfile.mkdtemp()
     nxt, got, files = run_dist("w_dcp", tmp)[0]
