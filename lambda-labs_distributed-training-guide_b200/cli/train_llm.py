@@ -89,6 +89,9 @@ def get_parser(chapter: str = "generic") -> argparse.ArgumentParser:
                         "AdamW launch behind the reduce-scatter; 'off' updates after backward like the reference; 'auto' picks "
                         "'kernel' up to 4 ranks and 'stream' from 8")
     p.add_argument("--deterministic", action="store_true")
+    p.add_argument("--progress-bar", choices=["on", "off"],
+                   default="off" if chapter in ("05-405b", "06-tensor-parallel", "07-2d-parallel") else "on",
+                   help="tqdm bar over the batches of an epoch on rank 0")
     p.add_argument("--packed", action="store_true", help="packed rows: derive position ids per document")
     p.add_argument("--max-steps", default=None, type=int, help="stop after this many optimizer steps")
     p.add_argument("--pretrained", default=None,
@@ -264,7 +267,19 @@ def main(chapter: str = "generic", argv=None):
         batches = iter(dataloader)
         n_batches = len(dataloader)
         micro = 0
+        # progress bar on rank 0 (01-single-gpu/train_llm.py:120, 02-.../train_llm.py:138); the large-scale chapters
+        # switch it off, as the reference does (05-training-llama-405b/train_llm.py:217)
+        bar = None
+        if rank == 0 and args.progress_bar == "on":
+            try:
+                import tqdm
+
+                bar = tqdm.tqdm(total=n_batches, initial=0, desc=f"epoch {state['epoch']}")
+            except ImportError:
+                bar = None
         for i_step in range(n_batches):
+            if bar is not None:
+                bar.update(1)
             with timers["data"], torch.no_grad():
                 batch = next(batches)
                 batch = engine.to_device(batch)
@@ -309,6 +324,8 @@ def main(chapter: str = "generic", argv=None):
             if args.max_steps is not None and steps_done >= args.max_steps:
                 stop = True
                 break
+        if bar is not None:
+            bar.close()
         if stop:
             break
         state["epoch_step"] = 0
