@@ -292,6 +292,10 @@ static int launch_rs(int W, int blocks, cudaStream_t stream, V4* out, PeerPtrs f
 
 // In-place all-reduce of a symmetric buffer: phase 1 reduces slice `rank` from all peers into the
 // local copy, phase 2 (after a barrier) pulls the other reduced slices.
+// Contract: the kernel itself has no exit handshake. A rank may return while peers are still pulling
+// its reduced slice, so `buf` must not be overwritten before a cross-rank ordering point on the same
+// stream. PeerComm._all_reduce therefore launches b2_peer_barrier on a channel of its own right behind
+// this kernel; a caller of the C entry point has to do the same.
 __global__ void __launch_bounds__(256)
 peer_all_reduce_kernel(PeerPtrs buf, size_t n16_slice, int rank, int W, float scale, PeerPtrs pads,
                        int chan_base, uint32_t epoch, unsigned int* counter) {

@@ -92,6 +92,10 @@ def get_parser(chapter: str = "generic") -> argparse.ArgumentParser:
     p.add_argument("--progress-bar", choices=["on", "off"],
                    default="off" if chapter in ("05-405b", "06-tensor-parallel", "07-2d-parallel") else "on",
                    help="tqdm bar over the batches of an epoch on rank 0")
+    p.add_argument("--ce-chunk-rows", type=int, default=2048 if chapter == "00-rime" else 0,
+                   help="LM head + cross entropy in chunks of this many token rows: the logits of one chunk at a time, "
+                        "recomputed in backward (0: all rows at once, fastest; the fork's chapter 00 uses Liger's "
+                        "fused linear cross entropy for the same purpose)")
     p.add_argument("--packed", action="store_true", help="packed rows: derive position ids per document")
     p.add_argument("--max-steps", default=None, type=int, help="stop after this many optimizer steps")
     p.add_argument("--pretrained", default=None,
@@ -156,6 +160,8 @@ def main(chapter: str = "generic", argv=None):
     if args.deterministic:
         ckpt.set_determinism(args.seed)
     torch.manual_seed(args.seed)
+    if args.ce_chunk_rows:
+        os.environ["B200TRAIN_CE_CHUNK_ROWS"] = str(args.ce_chunk_rows)
 
     # node-local vs shared HF cache decides who goes first (02-.../README.md:377-408)
     first = (local_rank == 0) if os.environ.get("B200TRAIN_NODE_LOCAL_CACHE") else (rank == 0)

@@ -33,7 +33,8 @@ from .comm import TorchComm
 
 _ARENA_MIN_BYTES = 256 << 20
 _ALIGN = 256
-CHAN_RS, CHAN_AR, CHAN_BARRIER, CHAN_CE_IN, CHAN_CE_OUT = 0, 2, 4, 8, 9   # 6, 7: tp_fused barriers
+CHAN_RS, CHAN_AR, CHAN_BARRIER, CHAN_CE_IN, CHAN_CE_OUT = 0, 2, 4, 8, 9   # 6, 7, 10: tp_fused barriers
+CHAN_AR_EXIT = 11
 
 
 class _Arena:
@@ -308,6 +309,10 @@ class PeerComm(TorchComm):
         _C.call("b2_peer_all_reduce", bufs, t.numel(), self.rank, self.world,
                 (1.0 / self.world) if average else 1.0, self._pad_ptrs, CHAN_AR, self._epoch(CHAN_AR),
                 self._counter().data_ptr(), max_blocks, self._stream())
+        # the two-phase kernel returns while peers may still be pulling this rank's reduced slice: hold the
+        # stream until every rank is out, so the caller may rewrite ``t`` as soon as the stream gets there
+        _C.call("b2_peer_barrier", self._pad_ptrs, self.rank, self.world, CHAN_AR_EXIT,
+                self._epoch(CHAN_AR_EXIT), self._stream())
         return t
 
     # ---- public surface: NVTX range + optional cross-check against NCCL --------------------------------

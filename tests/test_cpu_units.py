@@ -308,3 +308,24 @@ def test_pretrained_roundtrip_and_vocab_growth(tmp_path):
     emb = c.model.model.embed_tokens.weight
     assert torch.allclose(emb[-1], a.model.model.embed_tokens.weight.mean(0), atol=1e-6)
     assert torch.equal(emb[:cfg.vocab_size], a.model.model.embed_tokens.weight)
+
+
+def test_chunked_linear_cross_entropy_matches_full():
+    """LM head + CE over row chunks (``--ce-chunk-rows``): loss and both gradients equal the all-rows reference
+    for chunk sizes that divide the rows, do not divide them, and exceed them; ignored rows contribute nothing."""
+    from b200train.ops.cross_entropy import IGNORE, linear_cross_entropy, linear_cross_entropy_ref
+
+    torch.manual_seed(0)
+    T, H, V = 37, 16, 101
+    x = torch.randn(T, H, requires_grad=True)
+    w = (torch.randn(V, H) * 0.3).requires_grad_()
+    labels = torch.randint(0, V, (T,))
+    labels[::5] = IGNORE
+    ref = linear_cross_entropy_ref(x, w, labels)
+    gx, gw = torch.autograd.grad(ref * 1.7, (x, w))
+    for chunk in (1, 8, 10, 36, 37, 64):
+        loss = linear_cross_entropy(x, w, labels, chunk_rows=chunk)
+        cx, cw = torch.autograd.grad(loss * 1.7, (x, w))
+        assert abs(loss.item() - ref.item()) < 1e-6
+        assert (cx - gx).abs().max().item() < 1e-6 and (cw - gw).abs().max().item() < 1e-6
+        assert cx[::5].abs().max().item() == 0.0
