@@ -140,7 +140,9 @@ def main(chapter: str = "generic", argv=None):
         args.batch_size = ds_cfg.get("train_micro_batch_size_per_gpu", 1)
         args.lr = ds_cfg.get("optimizer", {}).get("params", {}).get("lr", 3e-5)
         zero = ds_cfg.get("zero_optimization", {})
-        args.cpu_offload = "on" if zero.get("offload_param", {}).get("device", "none") == "cpu" else "off"
+        off = zero.get("offload_param") or {}   # a dict with a "device", or the reference's plain `false`
+        args.cpu_offload = "on" if (off is True or (isinstance(off, dict) and off.get("device", "none") == "cpu")) \
+            else "off"
         # ZeRO stage -> sharding: 3 = parameters + gradients + optimizer state (full shard), 2 = gradients +
         # optimizer state (parameters stay gathered), 1 = optimizer state only (DDP + ZeRO-1), 0 = plain DDP
         stage = int(zero.get("stage", 3))
@@ -200,6 +202,11 @@ def main(chapter: str = "generic", argv=None):
             tp = min(world_size, max(per_node, 1))
         kw.update(tp=tp, activation_checkpointing=act == "on")
     engine = make_strategy(strategy_name, config, device, **kw)
+    if chapter == "deepspeed" and ds_cfg.get("scheduler", {}).get("type") == "WarmupCosineLR":
+        # the engine builds the schedule named in the json (DS/train_llm.py:68-73, ds_config.json:9-16)
+        from ..utils.schedule import make_warmup_cosine
+
+        engine.lr_scheduler = make_warmup_cosine(engine.optimizer, **ds_cfg["scheduler"].get("params", {}))
     if args.pretrained and not ckpt.has_checkpoint(Path(args.save_dir) / args.experiment_name):
         from ..models.pretrained import load_pretrained
 

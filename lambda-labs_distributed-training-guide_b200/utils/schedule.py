@@ -15,6 +15,25 @@ def make_lr_scheduler(optimizer: torch.optim.Optimizer, lr: float):
     return torch.optim.lr_scheduler.CosineAnnealingLR(optimizer, T_max=T_MAX, eta_min=lr * ETA_MIN_FACTOR)
 
 
+def warmup_cosine_ratio(step: int, total_num_steps: int, warmup_num_steps: int = 1000, cos_min_ratio: float = 1e-4,
+                        warmup_min_ratio: float = 0.0) -> float:
+    """Multiplier of DeepSpeed's ``WarmupCosineLR`` (the schedule of the reference's ``ds_config.json:9-16``):
+    linear from ``warmup_min_ratio`` to 1 over the warm-up steps, then half a cosine down to ``cos_min_ratio`` at
+    ``total_num_steps``, constant afterwards (unlike ``CosineAnnealingLR`` it is not periodic)."""
+    if step < warmup_num_steps:
+        return warmup_min_ratio + (1.0 - warmup_min_ratio) * step / max(warmup_num_steps, 1)
+    span = max(total_num_steps - warmup_num_steps, 1)
+    t = min(step - warmup_num_steps, span) / span
+    return cos_min_ratio + (1.0 - cos_min_ratio) * (1 + math.cos(math.pi * t)) / 2
+
+
+def make_warmup_cosine(optimizer: torch.optim.Optimizer, **params):
+    """``LambdaLR`` over :func:`warmup_cosine_ratio`; ``params`` are the json's ``scheduler.params``."""
+    keys = ("total_num_steps", "warmup_num_steps", "cos_min_ratio", "warmup_min_ratio")
+    kw = {k: params[k] for k in keys if k in params}
+    return torch.optim.lr_scheduler.LambdaLR(optimizer, lambda step: warmup_cosine_ratio(step, **kw))
+
+
 def cosine_lr(step: int, lr: float, t_max: int = T_MAX, eta_min_factor: float = ETA_MIN_FACTOR) -> float:
     """Closed form of the schedule above (what the chained torch implementation converges to)."""
     eta_min = lr * eta_min_factor

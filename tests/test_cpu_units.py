@@ -329,3 +329,25 @@ def test_chunked_linear_cross_entropy_matches_full():
         assert abs(loss.item() - ref.item()) < 1e-6
         assert (cx - gx).abs().max().item() < 1e-6 and (cw - gw).abs().max().item() < 1e-6
         assert cx[::5].abs().max().item() == 0.0
+
+
+def test_warmup_cosine_schedule_of_the_deepspeed_variant():
+    """``WarmupCosineLR`` as configured by the reference's ``ds_config.json``: linear warm-up, half a cosine down
+    to ``cos_min_ratio`` at ``total_num_steps``, flat afterwards; as a torch scheduler it drives ``param_groups``."""
+    from b200train.utils.schedule import make_warmup_cosine, warmup_cosine_ratio
+
+    kw = dict(total_num_steps=100, warmup_num_steps=10, cos_min_ratio=1e-2)
+    assert warmup_cosine_ratio(0, **kw) == 0.0
+    assert math.isclose(warmup_cosine_ratio(5, **kw), 0.5)
+    assert math.isclose(warmup_cosine_ratio(10, **kw), 1.0)
+    assert math.isclose(warmup_cosine_ratio(55, **kw), 1e-2 + 0.99 * 0.5)
+    assert math.isclose(warmup_cosine_ratio(100, **kw), 1e-2)
+    assert math.isclose(warmup_cosine_ratio(500, **kw), 1e-2)
+    p = torch.nn.Parameter(torch.zeros(1))
+    opt = torch.optim.AdamW([p], lr=3e-5)
+    sched = make_warmup_cosine(opt, total_num_steps=1000, warmup_num_steps=0, cos_min_ratio=1e-2, extra="ignored")
+    assert math.isclose(opt.param_groups[0]["lr"], 3e-5)
+    for _ in range(1000):
+        opt.step()
+        sched.step()
+    assert math.isclose(opt.param_groups[0]["lr"], 3e-7, rel_tol=1e-6)
