@@ -35,6 +35,15 @@ def _as_dtensor(full: torch.Tensor, mesh, rank: int, world: int):
                               stride=full.contiguous().stride())
 
 
+def _wrap_chunk(local: torch.Tensor, gshape, mesh):
+    """A dim-0 chunk that already is this rank's share of a tensor of shape ``gshape``."""
+    from torch.distributed.tensor import DTensor, Shard
+
+    stride = torch.empty(gshape, device="meta").stride()
+    return DTensor.from_local(local.contiguous(), mesh, [Shard(0)], run_check=False, shape=torch.Size(gshape),
+                              stride=stride)
+
+
 def _chunk(full: torch.Tensor, mesh, rank: int, world: int):
     if world == 1:
         return full.detach().clone()
@@ -96,10 +105,18 @@ def build_sharded_state(strategy, mesh):
     rank, world = strategy.rank, strategy.world_size
     two_d = hasattr(strategy, "mesh") and world > 1
     state = {"model": {}, "optimizer": {"state": {}, "param_groups": strategy.optimizer_param_groups()}}
+    exchange = getattr(strategy, "unit_named_chunks", None) if not two_d else None
     for i in range(strategy.num_units()):
         for kind in ("param", "exp_avg", "exp_avg_sq"):
-            for name, full in strategy.unit_named_full(i, kind).items():
-                piece = _chunk_2d(full, strategy, name) if two_d else _chunk(full, mesh, rank, world)
+            # flat-sharded strategies hand over their dim-0 chunks after one all-to-all (every element moves at
+            # most once); the others expose the whole unit and the chunk is cut out of it
+            chunks = exchange(i, kind) if exchange is not None else None
+            if chunks is not None:
+                pieces = {name: _wrap_chunk(local, gshape, mesh) for name, (local, gshape) in chunks.items()}
+            else:
+                pieces = {name: _chunk_2d(full, strategy, name) if two_d else _chunk(full, mesh, rank, world)
+                          for name, full in strategy.unit_named_full(i, kind).items()}
+            for name, piece in pieces.items():
                 if kind == "param":
                     state["model"][name] = piece
                 else:
@@ -138,9 +155,15 @@ def load_sharded(exp_dir: Path, strategy):
     sharded = build_sharded_state(strategy, None if hasattr(strategy, "mesh") else _mesh(strategy))
     load(sharded, checkpoint_id=exp_dir / "checkpoint", no_dist=not dist.is_initialized())
     opt_state = sharded["optimizer"]["state"]
+    store = getattr(strategy, "unit_store_chunks", None) if not two_d else None
     for i in range(strategy.num_units()):
         for kind in ("param", "exp_avg", "exp_avg_sq"):
             names = list(strategy.unit_named_full(i, kind, names_only=True))
+            if store is not None:
+                src = sharded["model"] if kind == "param" else None
+                local = {n: _to_local(src[n] if src is not None else opt_state[n][kind]) for n in names}
+                if store(i, kind, local):
+                    continue
             unpack = (lambda t, n: _local_from_2d(t, strategy, n)) if two_d else (lambda t, n: _to_full(t))
             if kind == "param":
                 tensors = {n: unpack(sharded["model"][n], n) for n in names}
@@ -153,6 +176,10 @@ def load_sharded(exp_dir: Path, strategy):
     # optimizer state: 04-fully-sharded-data-parallel/train_llm.py:132-154)
     strategy.set_optimizer_param_groups(sharded["optimizer"]["param_groups"])
     strategy.barrier()
+
+
+def _to_local(t):
+    return t.to_local() if hasattr(t, "to_local") else t
 
 
 def _to_full(t):

@@ -567,6 +567,117 @@ class FSDP(Strategy):
         shard.copy_(full[self.R * n:(self.R + 1) * n])
 
 
+    # ---- checkpoint surface without full-size gathers ---------------------------------------------------
+    # torch.distributed.checkpoint wants, from rank r, the r-th dim-0 chunk of every named tensor; the strategy
+    # owns the r-th slice of every flat unit. The two partitions cover the same bytes, so re-chunking is an
+    # exchange in which every element moves at most once: rank k sends to rank r the overlap of flat slice k with
+    # the chunks of rank r (one all-to-all per unit and kind, numel/W elements per rank), instead of gathering the
+    # whole unit on every rank and discarding (W-1)/W of it.
+    def _chunk_plan(self, i):
+        """``[(name, shape, flat offset)]`` of unit ``i``'s named tensors in flat order, or None when a named tensor
+        is not one contiguous range of the flat unit (then the gather path is used)."""
+        plans = self.__dict__.setdefault("_chunk_plans", {})
+        if i not in plans:
+            probe = self._names_probe(i)
+            base, es = probe.data_ptr(), probe.element_size()
+            plan = []
+            for name, v in self._named_views(i, probe).items():
+                if not v.is_contiguous():
+                    plan = None
+                    break
+                plan.append((name, tuple(v.shape) if v.dim() else (1,), (v.data_ptr() - base) // es))
+            plans[i] = sorted(plan, key=lambda t: t[2]) if plan is not None else None
+        return plans[i]
+
+    def _chunk_range(self, shape, off, r):
+        """Flat range of the dim-0 chunk that rank ``r`` of ``W`` holds (torch's ``Shard(0)`` split: ceil)."""
+        rows = shape[0]
+        rowsz = 1
+        for d in shape[1:]:
+            rowsz *= d
+        per = (rows + self.W - 1) // self.W
+        lo = min(r * per, rows)
+        hi = min(lo + per, rows)
+        return off + lo * rowsz, off + hi * rowsz, (hi - lo,) + tuple(shape[1:])
+
+    def _overlaps(self, i, chunk_rank, slice_rank):
+        """``[(j, lo, hi)]``: flat ranges that are both in flat slice ``slice_rank`` and in a chunk of ``chunk_rank``."""
+        n = self.units[i].numel // self.W
+        s_lo, s_hi = slice_rank * n, (slice_rank + 1) * n
+        out = []
+        for j, (_, shape, off) in enumerate(self._chunk_plan(i)):
+            a, b, _ = self._chunk_range(shape, off, chunk_rank)
+            lo, hi = max(a, s_lo), min(b, s_hi)
+            if lo < hi:
+                out.append((j, lo, hi))
+        return out
+
+    def _supports_chunk_exchange(self, i):
+        return (not self.resident and self.W > 1 and self.W == self.world_size and self._chunk_plan(i) is not None)
+
+    @torch.no_grad()
+    def unit_named_chunks(self, i: int, kind: str):
+        """``{name: (local dim-0 chunk, global shape)}`` of unit ``i`` (``kind``: param / exp_avg / exp_avg_sq) for this
+        rank, or None when the exchange does not apply (single rank, hybrid shard, non-contiguous named tensors)."""
+        if not self._supports_chunk_exchange(i):
+            return None
+        if self.is_cuda:
+            torch.cuda.synchronize(self.device)
+        plan = self._chunk_plan(i)
+        n = self.units[i].numel // self.W
+        mine = self._shard_of(i, kind).to(self.device)
+        send, ins = [], []
+        for r in range(self.W):
+            parts = [mine[lo - self.R * n:hi - self.R * n] for _, lo, hi in self._overlaps(i, r, self.R)]
+            ins.append(sum(p.numel() for p in parts))
+            send += parts
+        recv_plan = [self._overlaps(i, self.R, k) for k in range(self.W)]
+        outs = [sum(hi - lo for _, lo, hi in ov) for ov in recv_plan]
+        got = torch.empty(sum(outs), dtype=mine.dtype, device=self.device)
+        src = torch.cat(send) if send else mine[:0]
+        self.comm.all_to_all(got, src, outs, ins)
+        chunks, flat_lo = {}, {}
+        for j, (name, shape, off) in enumerate(plan):
+            a, _, cshape = self._chunk_range(shape, off, self.R)
+            chunks[name] = (torch.empty(cshape, dtype=mine.dtype, device=self.device), torch.Size(shape))
+            flat_lo[j] = a
+        pos = 0
+        for ov in recv_plan:
+            for j, lo, hi in ov:
+                chunks[plan[j][0]][0].view(-1)[lo - flat_lo[j]:hi - flat_lo[j]].copy_(got[pos:pos + hi - lo])
+                pos += hi - lo
+        return chunks
+
+    @torch.no_grad()
+    def unit_store_chunks(self, i: int, kind: str, chunks) -> bool:
+        """Inverse of :meth:`unit_named_chunks`: ``chunks[name]`` is this rank's dim-0 chunk of every named tensor
+        of unit ``i``; every element travels to the rank whose flat slice holds it."""
+        if not self._supports_chunk_exchange(i):
+            return False
+        plan = self._chunk_plan(i)
+        n = self.units[i].numel // self.W
+        flat_lo = {j: self._chunk_range(shape, off, self.R)[0] for j, (_, shape, off) in enumerate(plan)}
+        local = {j: chunks[name].to(device=self.device, dtype=self.dtype).reshape(-1) for j, (name, _, _) in enumerate(plan)}
+        send, ins = [], []
+        for k in range(self.W):
+            parts = [local[j][lo - flat_lo[j]:hi - flat_lo[j]] for j, lo, hi in self._overlaps(i, self.R, k)]
+            ins.append(sum(p.numel() for p in parts))
+            send += parts
+        recv_plan = [self._overlaps(i, r, self.R) for r in range(self.W)]
+        outs = [sum(hi - lo for _, lo, hi in ov) for ov in recv_plan]
+        got = torch.empty(sum(outs), dtype=self.dtype, device=self.device)
+        src = torch.cat(send) if send else got[:0]
+        self.comm.all_to_all(got, src, outs, ins)
+        new = torch.zeros(n, dtype=self.dtype, device=self.device)   # gaps between tensors (alignment) stay zero
+        pos = 0
+        for ov in recv_plan:
+            for _, lo, hi in ov:
+                new[lo - self.R * n:hi - self.R * n].copy_(got[pos:pos + hi - lo])
+                pos += hi - lo
+        self._shard_of(i, kind).copy_(new)
+        return True
+
+
 def _C_call_wait(flags, first, count, epoch, device):
     from .. import _C
 

@@ -223,6 +223,49 @@ def test_dcp_sharded_roundtrip():
     assert os.path.exists(os.path.join(tmp, "state.json"))
 
 
+def w_chunk_exchange(rank, world):
+    from b200train.models import load_config
+    from b200train.parallel import make_strategy
+
+    cfg = load_config("llama-tiny")
+    eng = make_strategy("fsdp", cfg, "cpu", lr=1e-3, dtype=torch.float32, seed=3)
+    ids = _batches(cfg, 1, 2, 32, seed=rank)[0]
+    eng.train_step({"input_ids": ids, "labels": ids})       # non-trivial moments
+    worst, n_tensors, moved = 0.0, 0, 0
+    for i in range(eng.num_units()):
+        for kind in ("param", "exp_avg", "exp_avg_sq"):
+            chunks = eng.unit_named_chunks(i, kind)
+            assert chunks is not None
+            full = {k: v.clone() for k, v in eng.unit_named_full(i, kind).items()}
+            assert set(chunks) == set(full)
+            for name, (local, gshape) in chunks.items():
+                want = full[name].reshape(gshape)
+                per = (gshape[0] + world - 1) // world
+                lo = min(rank * per, gshape[0])
+                want = want[lo:min(lo + per, gshape[0])]
+                assert local.shape == want.shape, (name, local.shape, want.shape)
+                worst = max(worst, (local - want).abs().max().item() if want.numel() else 0.0)
+                n_tensors += 1
+                moved += local.numel()
+            # the inverse exchange: store 2 x the chunks, the gathered unit must come back doubled
+            assert eng.unit_store_chunks(i, kind, {k: v[0] * 2 for k, v in chunks.items()})
+            back = eng.unit_named_full(i, kind)
+            worst = max(worst, max((back[k] - 2 * full[k]).abs().max().item() for k in full))
+    return worst, n_tensors, moved
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_fsdp_checkpoint_chunks_come_from_one_exchange(world):
+    """DCP's dim-0 chunks are produced from the flat shards by an all-to-all (no full-size gather): they equal the
+    chunks cut from the gathered unit for every tensor and moment, also when the rows do not divide by the world
+    size, and the inverse exchange puts every element back into the right flat slice."""
+    res = run_dist("w_chunk_exchange", world=world)
+    total = sum(r[2] for r in res)
+    for worst, n_tensors, _ in res:
+        assert worst == 0.0 and n_tensors > 10, (worst, n_tensors)
+    assert total > 0
+
+
 def w_order(rank, world, tmp):
     if True:
         import time
