@@ -64,6 +64,9 @@ def get_parser(chapter: str = "generic") -> argparse.ArgumentParser:
                        choices=["full_shard", "shard_grad_op", "no_shard", "hybrid_shard"])
         p.add_argument("--replicas", default=None, type=int,
                        help="hybrid_shard: number of replica groups (default: one per node)")
+        p.add_argument("--sync-module-states", default="off", choices=["on", "off"],
+                       help="broadcast every freshly initialised unit from rank 0 (the reference's "
+                            "sync_module_states=True); off: every rank initialises from the same seed, no traffic")
     if chapter in ("07-2d-parallel", "generic"):
         p.add_argument("--tp", default=8 if chapter == "07-2d-parallel" else 1, type=int)
     if chapter == "deepspeed":
@@ -184,7 +187,8 @@ def main(chapter: str = "generic", argv=None):
         args.zero1 = "off"
     if strategy_name == "fsdp":
         kw.update(cpu_offload=getattr(args, "cpu_offload", "off") == "on", activation_checkpointing=act == "on",
-                  numel_to_wrap=getattr(args, "numel_to_wrap", 0))
+                  numel_to_wrap=getattr(args, "numel_to_wrap", 0),
+                  sync_module_states=getattr(args, "sync_module_states", "off") == "on")
         if device.type == "cuda" and args.grad_accum_steps <= 1:
             kw.update(fuse_optimizer=False if args.fuse_optimizer == "off" else args.fuse_optimizer)
         if sharding == "shard_grad_op":  # parameters stay gathered between forward and backward (ZeRO-2)

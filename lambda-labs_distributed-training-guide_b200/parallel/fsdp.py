@@ -87,8 +87,13 @@ class FSDP(Strategy):
     def __init__(self, cfg, device, lr=3e-5, seed=0, dtype=torch.bfloat16, group=None,
                  comm: Optional[Comm] = None, cpu_offload: bool = False, activation_checkpointing: bool = False,
                  reshard_after_forward: bool = True, fuse_optimizer: bool = False, numel_to_wrap: int = 0,
-                 prefer_peer: bool = True):
+                 prefer_peer: bool = True, sync_module_states: bool = False):
         super().__init__(cfg, device, lr, seed, dtype)
+        # N1 (``sync_module_states=True`` of the reference, 04-.../train_llm.py:87-95): every unit is broadcast
+        # from the first rank of the group while it is being materialised. Off by default: all ranks initialise
+        # from the same seed, which gives the same parameters without the traffic; switch it on when the ranks
+        # were (or may have been) seeded differently.
+        self.sync_module_states = sync_module_states
         self.comm = comm if comm is not None else make_comm(group, prefer_peer, self.device)
         self.W, self.R = self.comm.world, self.comm.rank
         self.cpu_offload = cpu_offload
@@ -141,6 +146,8 @@ class FSDP(Strategy):
             full = (torch.empty(u.numel, dtype=dtype, device=self.device) if self.resident
                     else self.param_pool.bufs[0][:u.numel])
             swap.update(u.materialize(self.model, full, self._init_seed(seed), ui, cfg))
+            if self.sync_module_states:
+                self._sync_unit(full)
             if self.resident:
                 self.shard_param.append(full)
                 self.shard_grad.append(torch.zeros(u.numel, dtype=dtype, device=self.device))
@@ -217,6 +224,10 @@ class FSDP(Strategy):
 
     def _init_seed(self, seed):
         return seed
+
+    def _sync_unit(self, full):
+        """Make every rank of the sharding group hold rank 0's freshly initialised unit."""
+        self.comm.broadcast(full, 0)
 
     def pre_reduce(self, i):
         """Called when unit ``i``'s gradients are complete, before they are reduced over this group."""
@@ -824,6 +835,11 @@ class HSDP(FSDP):
         self.rep_group = rep_groups[rank % S] if replicas > 1 else None
         kw.pop("comm", None)
         super().__init__(cfg, device, lr=lr, seed=seed, dtype=dtype, group=shard_groups[rank // S], **kw)
+
+    def _sync_unit(self, full):
+        import torch.distributed as dist
+
+        dist.broadcast(full, src=0)   # all replicas, not only this one's sharding group
 
     def post_reduce(self, i, shard):
         if self.rep_group is None:

@@ -266,6 +266,31 @@ def test_fsdp_checkpoint_chunks_come_from_one_exchange(world):
     assert total > 0
 
 
+def w_sync_states(rank, world, sync):
+    from b200train.models import load_config
+    from b200train.parallel import make_strategy
+
+    cfg = load_config("llama-tiny")
+    eng = make_strategy("fsdp", cfg, "cpu", lr=1e-3, dtype=torch.float32, seed=100 + rank, sync_module_states=sync)
+    sd = eng.gather_full_state_dict()
+    return {k: v.clone() for k, v in sd.items()}
+
+
+def test_fsdp_sync_module_states_broadcasts_rank0_init():
+    """Ranks seeded differently: with ``sync_module_states`` the sharded model is rank 0's initialisation (N1,
+    rank-0 init + broadcast); without it the shards are cut from different initialisations."""
+    from b200train.models import load_config
+    from b200train.parallel import make_strategy
+
+    synced = run_dist("w_sync_states", True)
+    ref = make_strategy("fsdp", load_config("llama-tiny"), "cpu", lr=1e-3, dtype=torch.float32,
+                        seed=100).gather_full_state_dict()
+    for k, v in ref.items():
+        assert torch.equal(synced[0][k], v) and torch.equal(synced[1][k], v), k
+    loose = run_dist("w_sync_states", False)
+    assert any(not torch.equal(loose[0][k], v) for k, v in ref.items())
+
+
 def w_order(rank, world, tmp):
     if True:
         import time
