@@ -53,6 +53,8 @@ struct AttnBwdParams {
   float scale, scale_log2;
   int causal;
   AttnDropout drop;   // attention-probability dropout of the forward (thr == 0: none)
+  int n_items = 0;      // attn_bwd2_kernel<2>: work items (kv blocks x kv heads x documents) ...
+  int split_items = 0;  // ... of which the first (heaviest) split_items are shared by a CTA pair
 };
 
 __global__ void attn_dropout_mask_kernel(unsigned char* keep, int S, int doc, AttnDropout d) {
@@ -520,6 +522,17 @@ struct AttnBwd2Smem {
   static constexpr int kTotal = kK + kV + 2 * (kQ + kDO + kDS) + 4 * 2 * kDQBox + kStats + 256 + 1024;
 };
 
+// kSplit == 2: the grid is made of CTA pairs (clusters of 2). The first p.split_items work items are SHARED by
+// a pair, each CTA taking half of the query heads of the kv head's group; any remaining items go one per CTA
+// as in the plain kernel (the launcher shares all items or none; the mixed form exists for experiments and
+// measured slower than both). Sharing pays when whole items cannot fill or balance 148 SMs: few kv heads per
+// rank under tensor parallelism (Llama-70B with tp=4 at S=4096 has 64 items), short sequences, or large
+// groups whose heaviest item (causal: kv block 0) is longer than the per-SM average. dK / dV are sums over
+// all query heads of the group: in a shared item CTA 1 hands its partial sums to CTA 0 through distributed
+// shared memory at the end (128 KB, once per item), and CTA 0 adds them to its own while draining to global
+// memory. Every additional CTA costs about 16 steps of turnover (launch, TMEM allocation, pipeline fill,
+// drain), which the launcher's cost model weighs against the better balance.
+template <int kSplit>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                  const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
@@ -551,19 +564,30 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
 
   const int warp = threadIdx.x >> 5;
   const int per_kb = p.Hkv * p.ndocs;
-  const int jb = (int)blockIdx.x / per_kb;
-  const int kvh = ((int)blockIdx.x % per_kb) % p.Hkv;
-  const int doc = ((int)blockIdx.x % per_kb) / p.Hkv;
+  const int crank = kSplit == 2 ? (int)cluster_ctarank() : 0;
+  int item = (int)blockIdx.x;
+  bool shared_item = false;
+  if constexpr (kSplit == 2) {
+    const int cl = (int)blockIdx.x >> 1;
+    shared_item = cl < p.split_items;
+    item = shared_item ? cl : p.split_items + 2 * (cl - p.split_items) + crank;
+    if (item >= p.n_items) return;   // odd number of whole items: the last pair has one idle CTA
+  }
+  const int jb = item / per_kb;
+  const int kvh = (item % per_kb) % p.Hkv;
+  const int doc = (item % per_kb) / p.Hkv;
   const int doc_start = p.cu_seqlens[doc];
   const int doc_len = p.cu_seqlens[doc + 1] - doc_start;
   const int num_kb = (doc_len + KB2 - 1) / KB2;
-  if (jb >= num_kb) return;
+  if (jb >= num_kb) return;   // the CTAs of a shared item leave together; the others never meet
   const int kv0 = jb * KB2;
   const int num_qb = (doc_len + QB2 - 1) / QB2;
   const int i0 = p.causal ? kv0 / QB2 : 0;  // first query block with a row >= kv0
   const int nqi = num_qb - i0;
   const int group = p.Hq / p.Hkv;
-  const int n_iter = group * nqi;
+  const int my_heads = shared_item ? group / 2 : group;   // query heads this CTA walks
+  const int head0 = kvh * group + (shared_item ? crank * my_heads : 0);
+  const int n_iter = my_heads * nqi;
 
   if (warp == 0 && elect_one()) {
     tma_prefetch_desc(&tmQ);
@@ -608,7 +632,7 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       }
       for (int it = 0; it < n_iter; ++it) {
         const int s = it & 1;
-        const int head = kvh * group + it / nqi;
+        const int head = head0 + it / nqi;
         const int row = doc_start + (i0 + it % nqi) * QB2;
         mbar_wait(&qdo_empty[s], ((it >> 1) & 1) ^ 1);
         mbar_expect_tx(&qdo_full[s], SM::kQ + SM::kDO);
@@ -711,7 +735,7 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     for (int it = 0; it < n_iter; ++it) {
       const int s = it & 1;
       const uint32_t par = (it >> 1) & 1;
-      const int head = kvh * group + it / nqi;
+      const int head = head0 + it / nqi;
       const int q0 = (i0 + it % nqi) * QB2 + 32 * h;   // first query row of this warpgroup's columns
       // lane j fetches the row statistics of query q0 + j; after the wait below they go to a small
       // shared table (one per warpgroup and stage; the four warps store identical values, and a warp
@@ -792,31 +816,6 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       __syncwarp();
       if (lane_id() == 0) mbar_arrive(&ds_full[s]);
     }
-    // ---- drain dV: lane = kv row, this warpgroup takes head-dim columns [64h, 64h + 64) ----
-    if (n_iter > 0) {
-      mbar_wait(done_bar, 0);
-      tc_fence_after();
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(tm_dV + lane_off + h * 64 + c * 32, r);
-        tmem_ld_wait();
-        if (kv_ok) {
-          uint4* dst = reinterpret_cast<uint4*>(p.dv + (size_t)(doc_start + kv_idx) * p.dv_stride +
-                                                (size_t)kvh * D + h * 64 + c * 32);
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            uint4 o;
-            o.x = pack_bf16(__uint_as_float(r[8 * j]), __uint_as_float(r[8 * j + 1]));
-            o.y = pack_bf16(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
-            o.z = pack_bf16(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
-            o.w = pack_bf16(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
-            dst[j] = o;
-          }
-        }
-      }
-      tc_fence_before();
-    }
   } else {
     // ================= dQ^T drain: warp w owns head-dim lanes 32w .. 32w+31 =================
     const int w = warp & 3;   // warps 6..9 -> TMEM lane quarters 2,3,0,1
@@ -825,7 +824,7 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     const uint32_t chunk = lane_id() >> 2, sub = (lane_id() & 3) * 4;
     for (int it = 0; it < n_iter; ++it) {
       const int s = it & 1;
-      const int head = kvh * group + it / nqi;
+      const int head = head0 + it / nqi;
       const int q_row0 = doc_start + (i0 + it % nqi) * QB2;
       mbar_wait(&dq_full[s], (it >> 1) & 1);
       tc_fence_after();
@@ -855,33 +854,84 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       }
     }
     if (lane_id() == 0) tma_store_wait<0>();
-    // ---- drain dK: lane = kv row ----
-    if (n_iter > 0) {
-      const int kv_idx = kv0 + w * 32 + (int)lane_id();
-      mbar_wait(done_bar, 0);
-      tc_fence_after();
+  }
+  __syncwarp();
+
+  // ================= drain dV (softmax warps) and dK (dQ warps): lane = kv row =================
+  // The accumulators cover 32-column chunks `ch` of the two [128 kv x 128 d] tiles (dV: ch 0..3, dK: ch
+  // 4..7). Split items: CTA 1 writes its chunks as fp32 into CTA 0's shared memory (the K / V / Q / dO
+  // buffers, free once every MMA has completed), laid out [16-byte column group][kv row] so that the 32
+  // lanes of a warp touch consecutive 16-byte words on both sides; CTA 0 adds them while it drains.
+  const bool is_sm = (warp >= 2 && warp < 6) || warp >= 10;
+  const bool is_dq = warp >= 6 && warp < 10;
+  if (n_iter > 0 && (is_sm || is_dq)) {
+    mbar_wait(done_bar, 0);
+    tc_fence_after();
+  }
+  auto drain = [&](int mode) {   // 0: to global, 1: to CTA 0's shared memory, 2: add CTA 1's sums, to global
+    if (n_iter == 0 || !(is_sm || is_dq)) return;
+    const int quarter = warp & 3;   // TMEM lane quarter of this warp
+    const int row = quarter * 32 + (int)lane_id();
+    const int kv_idx = kv0 + row;
+    const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
+    const int c_lo = is_sm ? (warp >= 10 ? 2 : 0) : 0, c_n = is_sm ? 2 : 4;
+    const uint32_t tm = is_sm ? tm_dV : tm_dK;
+    const float sc = is_sm ? 1.f : p.scale;
+    __nv_bfloat16* out = is_sm ? p.dv : p.dk;
+    const int ostride = is_sm ? p.dv_stride : p.dk_stride;
+    uint32_t xbase = smem_u32(sK);
+    if (mode == 1) asm volatile("mapa.shared::cluster.u32 %0, %1, 0;" : "=r"(xbase) : "r"(xbase));
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(tm_dK + lane_off + c * 32, r);
-        tmem_ld_wait();
-        if (kv_idx < doc_len) {
-          uint4* dst = reinterpret_cast<uint4*>(p.dk + (size_t)(doc_start + kv_idx) * p.dk_stride +
-                                                (size_t)kvh * D + c * 32);
-          const float sc = p.scale;
+    for (int c = c_lo; c < c_lo + c_n; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32b_x32(tm + lane_off + c * 32, r);
+      tmem_ld_wait();
+      const uint32_t xoff = xbase + (uint32_t)((((is_sm ? 0 : 32) + c * 8) * KB2 + row) * 16);
+      if (mode == 1) {
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            uint4 o;
-            o.x = pack_bf16(__uint_as_float(r[8 * j]) * sc, __uint_as_float(r[8 * j + 1]) * sc);
-            o.y = pack_bf16(__uint_as_float(r[8 * j + 2]) * sc, __uint_as_float(r[8 * j + 3]) * sc);
-            o.z = pack_bf16(__uint_as_float(r[8 * j + 4]) * sc, __uint_as_float(r[8 * j + 5]) * sc);
-            o.w = pack_bf16(__uint_as_float(r[8 * j + 6]) * sc, __uint_as_float(r[8 * j + 7]) * sc);
-            dst[j] = o;
-          }
+        for (int j = 0; j < 8; ++j)
+          asm volatile("st.shared::cluster.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(xoff + j * (KB2 * 16)),
+                       "r"(r[4 * j]), "r"(r[4 * j + 1]), "r"(r[4 * j + 2]), "r"(r[4 * j + 3])
+                       : "memory");
+        continue;
+      }
+      if (mode == 2) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          uint32_t a0, a1, a2, a3;
+          asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                       : "=r"(a0), "=r"(a1), "=r"(a2), "=r"(a3)
+                       : "r"(xoff + j * (KB2 * 16))
+                       : "memory");
+          r[4 * j] = __float_as_uint(__uint_as_float(r[4 * j]) + __uint_as_float(a0));
+          r[4 * j + 1] = __float_as_uint(__uint_as_float(r[4 * j + 1]) + __uint_as_float(a1));
+          r[4 * j + 2] = __float_as_uint(__uint_as_float(r[4 * j + 2]) + __uint_as_float(a2));
+          r[4 * j + 3] = __float_as_uint(__uint_as_float(r[4 * j + 3]) + __uint_as_float(a3));
         }
       }
-      tc_fence_before();
+      if (kv_idx < doc_len) {
+        uint4* dst = reinterpret_cast<uint4*>(out + (size_t)(doc_start + kv_idx) * ostride + (size_t)kvh * D +
+                                              c * 32);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint4 o;
+          o.x = pack_bf16(__uint_as_float(r[8 * j]) * sc, __uint_as_float(r[8 * j + 1]) * sc);
+          o.y = pack_bf16(__uint_as_float(r[8 * j + 2]) * sc, __uint_as_float(r[8 * j + 3]) * sc);
+          o.z = pack_bf16(__uint_as_float(r[8 * j + 4]) * sc, __uint_as_float(r[8 * j + 5]) * sc);
+          o.w = pack_bf16(__uint_as_float(r[8 * j + 6]) * sc, __uint_as_float(r[8 * j + 7]) * sc);
+          dst[j] = o;
+        }
+      }
     }
+    tc_fence_before();
+  };
+  if (kSplit == 2 && shared_item) {
+    cluster_sync_all();   // every MMA of both CTAs has completed: CTA 0's operand buffers are free
+    if (crank == 1) drain(1);
+    cluster_sync_all();   // CTA 1's sums are in CTA 0's shared memory
+    if (crank == 0) drain(2);
+  } else {
+    drain(0);
   }
 
   __syncwarp();
@@ -898,13 +948,68 @@ static int launch_attn_bwd2(const CUtensorMap& tmQ, const CUtensorMap& tmK, cons
   using SM = AttnBwd2Smem;
   static bool attr_set = false;
   if (!attr_set) {
-    B2_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    B2_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd2_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       SM::kTotal));
+    B2_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd2_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        SM::kTotal));
     attr_set = true;
   }
-  dim3 grid(max_kblocks * prm.Hkv * ndocs);
-  attn_bwd2_kernel<<<grid, kBwdThreads, SM::kTotal, stream>>>(tmQ, tmK, tmV, tmDO, tmDQ, prm);
-  B2_CUDA_CHECK(cudaGetLastError());
+  const int per_kb = prm.Hkv * ndocs;
+  const int items = max_kblocks * per_kb;
+  // Share every item between two CTAs, or none: the choice minimises the estimated makespan in steps,
+  // max(average per SM, longest piece) + CTAs per SM x 16 (a CTA's turnover: launch, TMEM allocation, pipeline
+  // fill, drain). Measured whole / shared, ms (profiles/attn_bwd_split_ab.jsonl): 8B S=4096 0.534 / 0.538,
+  // S=2048 0.273 / 0.177, B=2 1.017 / 1.101; 70B S=4096 1.098 / 1.030, with tp=4 (64 items) 0.925 / 0.493; 8B
+  // tp=8 B=16 S=1024 0.161 / 0.124 -- the model picks the faster one in each case. Sharing only the heaviest
+  // kv blocks (B200TRAIN_ATTN_BWD_SPLIT_KB=n) measured slower than either: pairs of independent whole items
+  // wait for each other's SM. B200TRAIN_ATTN_BWD_SPLIT=0 never shares, =1 always does.
+  static const int force = [] {
+    const char* e = getenv("B200TRAIN_ATTN_BWD_SPLIT");
+    return e ? (e[0] == '1' ? 1 : 0) : -1;
+  }();
+  const int group = prm.Hq / prm.Hkv;
+  int split_kb = 0;
+  if (group % 2 == 0 && force != 0) {
+    if (force == 1) {
+      split_kb = max_kblocks;
+    } else {
+      const int J = max_kblocks, sms = sm_count();
+      const int nq = J * (KB2 / QB2);                                  // query blocks of the longest document
+      double total = 0;
+      for (int j = 0; j < J; ++j) total += (double)group * (prm.causal ? nq - j * (KB2 / QB2) : nq) * per_kb;
+      const double avg = total / sms, longest = (double)group * nq;
+      const double whole = (avg > longest ? avg : longest) + 16.0 * items / sms;
+      const double shared = (avg > longest / 2 ? avg : longest / 2) + 32.0 * items / sms;
+      if (shared < 0.98 * whole) split_kb = J;
+    }
+    static const int fixed_kb = [] {   // B200TRAIN_ATTN_BWD_SPLIT_KB=n: share exactly the first n kv blocks
+      const char* e = getenv("B200TRAIN_ATTN_BWD_SPLIT_KB");
+      return e ? atoi(e) : -1;
+    }();
+    if (fixed_kb >= 0) split_kb = fixed_kb < max_kblocks ? fixed_kb : max_kblocks;
+  }
+  if (split_kb == 0) {
+    attn_bwd2_kernel<1><<<dim3(items), kBwdThreads, SM::kTotal, stream>>>(tmQ, tmK, tmV, tmDO, tmDQ, prm);
+    B2_CUDA_CHECK(cudaGetLastError());
+    return 0;
+  }
+  AttnBwdParams prm2 = prm;
+  prm2.n_items = items;
+  prm2.split_items = split_kb * per_kb;
+  const int clusters = prm2.split_items + (items - prm2.split_items + 1) / 2;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * clusters);
+  cfg.blockDim = dim3(kBwdThreads);
+  cfg.dynamicSmemBytes = SM::kTotal;
+  cfg.stream = stream;
+  cudaLaunchAttribute attrs[1];
+  attrs[0].id = cudaLaunchAttributeClusterDimension;
+  attrs[0].val.clusterDim.x = 2;
+  attrs[0].val.clusterDim.y = 1;
+  attrs[0].val.clusterDim.z = 1;
+  cfg.attrs = attrs;
+  cfg.numAttrs = 1;
+  B2_CUDA_CHECK(cudaLaunchKernelEx(&cfg, attn_bwd2_kernel<2>, tmQ, tmK, tmV, tmDO, tmDQ, prm2));
   return 0;
 }
 

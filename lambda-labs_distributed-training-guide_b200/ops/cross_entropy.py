@@ -101,8 +101,9 @@ class _ChunkedLinearCrossEntropy(torch.autograd.Function):
     same chunks: the logits of a chunk are recomputed into the same buffer, turned into dlogits in place, and
     consumed at once by the two gradient GEMMs (``dx`` rows of the chunk; ``dW`` accumulated in place through
     the GEMM's accumulate epilogue, straight into the flat gradient buffer when the strategy owns one). Cost:
-    one extra head GEMM (2 T V H FLOP, about 1.5 % of a Llama-8B step); saved: ``(T - chunk) * V * 2`` bytes of
-    activations (0.8 GB at T=4096, 3.9 GB at T=16384 with V=128256, chunk 1024), which is what the reference's
+    one extra head GEMM (2 T V H FLOP) and one read + write of dW per chunk -- measured 9.0 -> 15.0 ms at T=4096,
+    52.1 -> 65.3 ms at T=16384 (V=128256, chunk 2048; ``profiles/ce_chunk_bench_r2.jsonl``); saved:
+    ``(T - chunk) * V * 2`` bytes of activations (0.98 -> 0.49 GB and 3.91 -> 0.49 GB), which is what the reference's
     fork buys with Liger's fused linear cross entropy (``00-rime/train_llm_01-single-gpu.py:51-54``). The same
     code runs on CPU tensors with ATen pieces, which is how the chunk bookkeeping is unit-tested.
     """
