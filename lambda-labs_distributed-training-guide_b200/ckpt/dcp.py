@@ -10,8 +10,9 @@ rows, so saving / loading re-chunks one unit at a time through the strategy's co
 """
 from __future__ import annotations
 
+import os
+import shutil
 from pathlib import Path
-
 
 import torch
 import torch.distributed as dist
@@ -133,16 +134,57 @@ def save_sharded(exp_dir: Path, strategy, state: dict = None, lr_scheduler=None)
     from .state import save_state
 
     exp_dir = Path(exp_dir)
-    rank, world = strategy.rank, strategy.world_size
+    rank = strategy.rank
     strategy.barrier()
     sharded = build_sharded_state(strategy, None if hasattr(strategy, "mesh") else _mesh(strategy))
-    save(sharded, checkpoint_id=exp_dir / "checkpoint", no_dist=not dist.is_initialized())
+    # The reference saves into ``checkpoint/`` in place (04-.../train_llm.py:249-263): a crash in the middle
+    # leaves a torn directory under an older ``state.json``. Here the new checkpoint is written next to the old
+    # one and swapped in by one leader per file system once every rank has finished writing.
+    leader = _dir_leader(exp_dir, strategy)
+    tmp, final = exp_dir / "checkpoint.tmp", exp_dir / "checkpoint"
+    if leader:
+        shutil.rmtree(tmp, ignore_errors=True)
+    strategy.barrier()
+    save(sharded, checkpoint_id=tmp, no_dist=not dist.is_initialized())
+    strategy.barrier()
+    if leader:
+        old = exp_dir / "checkpoint.old"
+        shutil.rmtree(old, ignore_errors=True)
+        if final.exists():
+            os.replace(final, old)
+        os.replace(tmp, final)
+        shutil.rmtree(old, ignore_errors=True)
+    strategy.barrier()
     if rank == 0:
         if lr_scheduler is not None:
-            torch.save(lr_scheduler.state_dict(), exp_dir / "lr_scheduler.pt")
+            tmp_lr = exp_dir / "lr_scheduler.pt.tmp"
+            torch.save(lr_scheduler.state_dict(), tmp_lr)
+            os.replace(tmp_lr, exp_dir / "lr_scheduler.pt")
         if state is not None:
             save_state(exp_dir, state)
     strategy.barrier()
+
+
+def _dir_leader(exp_dir: Path, strategy) -> bool:
+    """One rank per distinct file system holding ``exp_dir``: rank 0, plus local rank 0 of every node that
+    cannot see a probe file rank 0 has just written (node-local output directories). ``exp_dir.is_mount()``, the
+    reference's test (04-.../train_llm.py:158-163), misses shared directories that are not mount points."""
+    rank = strategy.rank
+    if strategy.world_size == 1:
+        exp_dir.mkdir(parents=True, exist_ok=True)
+        return True
+    probe = exp_dir / ".shared-probe"
+    local0 = int(os.environ.get("LOCAL_RANK", "0")) == 0
+    if rank == 0 or local0:
+        exp_dir.mkdir(parents=True, exist_ok=True)
+    if rank == 0:
+        probe.write_text("x")
+    strategy.barrier()
+    leader = rank == 0 or (local0 and not probe.exists())
+    strategy.barrier()
+    if rank == 0:
+        probe.unlink(missing_ok=True)
+    return leader
 
 
 def load_sharded(exp_dir: Path, strategy):

@@ -46,13 +46,21 @@ def save_full(exp_dir: Path, model_sd=None, optimizer_sd=None, lr_scheduler=None
     exp_dir = Path(exp_dir)
     exp_dir.mkdir(parents=True, exist_ok=True)
     if optimizer_sd is not None:
-        torch.save(optimizer_sd, exp_dir / "optimizer.pt")
+        _save_atomic(optimizer_sd, exp_dir / "optimizer.pt")
     if model_sd is not None:
-        torch.save(model_sd, exp_dir / "model.pt")
+        _save_atomic(model_sd, exp_dir / "model.pt")
     if lr_scheduler is not None:
-        torch.save(lr_scheduler.state_dict(), exp_dir / "lr_scheduler.pt")
+        _save_atomic(lr_scheduler.state_dict(), exp_dir / "lr_scheduler.pt")
     if state is not None:
         save_state(exp_dir, state)
+
+
+def _save_atomic(obj, path: Path):
+    """``torch.save`` to a temporary name, then rename: a crash in the middle of a checkpoint leaves the previous
+    file whole (``state.json`` still describes it) instead of a torn one."""
+    tmp = path.with_name(path.name + ".tmp")
+    torch.save(obj, tmp)
+    os.replace(tmp, path)
 
 
 def load_full(exp_dir: Path, device, want_optimizer: bool = True):

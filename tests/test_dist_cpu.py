@@ -165,6 +165,47 @@ def w_dcp(rank, world, tmp):
         return nxt, got, files
 
 
+def w_dcp_swap(rank, world, tmp):
+    from pathlib import Path
+
+    from b200train.ckpt.dcp import load_sharded, save_sharded
+    from b200train.models import load_config
+    from b200train.parallel import make_strategy
+
+    cfg = load_config("llama-tiny")
+    eng = make_strategy("fsdp", cfg, "cpu", lr=1e-3, dtype=torch.float32)
+    ids = _batches(cfg, 1, 4, 32)[0][rank * 2:(rank + 1) * 2]
+    eng.train_step({"input_ids": ids, "labels": ids})
+    save_sharded(Path(tmp), eng, state={"epoch": 0, "global_step": 1, "epoch_step": 1, "running_loss": 0.0})
+    eng.train_step({"input_ids": ids, "labels": ids})
+    if rank == 0:   # what a crash in the middle of the next save leaves behind
+        (Path(tmp) / "checkpoint.tmp").mkdir()
+        (Path(tmp) / "checkpoint.tmp" / "__0_0.distcp").write_bytes(b"torn")
+    dist.barrier()
+    # the first checkpoint is still whole under the old state.json: a resume at this point works
+    probe = make_strategy("fsdp", cfg, "cpu", lr=1e-3, dtype=torch.float32, seed=5)
+    load_sharded(Path(tmp), probe)
+    first_step = probe.optimizer_step_count()
+    save_sharded(Path(tmp), eng, state={"epoch": 0, "global_step": 2, "epoch_step": 2, "running_loss": 0.0})
+    nxt = eng.train_step({"input_ids": ids, "labels": ids}).item()
+    eng2 = make_strategy("fsdp", cfg, "cpu", lr=1e-3, dtype=torch.float32, seed=7)
+    load_sharded(Path(tmp), eng2)
+    got = eng2.train_step({"input_ids": ids, "labels": ids}).item()
+    return first_step, eng2.optimizer_step_count(), nxt, got, sorted(p.name for p in Path(tmp).iterdir())
+
+
+def test_dcp_save_swaps_directories_and_survives_a_torn_attempt():
+    """A sharded save goes to ``checkpoint.tmp`` and replaces ``checkpoint`` only when every rank has written: the
+    previous checkpoint stays loadable until then, leftovers of a crashed attempt are discarded, and no temporary
+    directory remains afterwards."""
+    tmp = tempfile.mkdtemp()
+    first_step, last_step, nxt, got, names = run_dist("w_dcp_swap", tmp)[0]
+    assert first_step == 1 and last_step == 3, (first_step, last_step)   # 2 saved + the step taken after loading
+    assert abs(nxt - got) < 1e-5, (nxt, got)
+    assert "checkpoint" in names and "state.json" in names, names
+    assert not any(n.startswith("checkpoint.") or n.startswith(".shared") for n in names), names
+
+
 def w_dcp_stock(rank, world, tmp):
     """A checkpoint directory written by STOCK torch.distributed.checkpoint code -- DTensors sharded on dim 0
     under the reference's keys (``model.<hf name>``, ``optimizer.state.<hf name>.exp_avg`` ...), which is
