@@ -1,6 +1,6 @@
 """Attention backward, head_dim 128: whole work items against the heaviest items shared by a CTA pair
-(``B200TRAIN_ATTN_BWD_SPLIT`` / ``_SPLIT_KB``; read once per process, so every arm is a subprocess). Prints one JSON record per
-(shape, arm): median milliseconds of ``--iters`` runs timed with CUDA events, each preceded by an L2 flush,
+(``B200TRAIN_ATTN_BWD_SPLIT`` / ``_SPLIT_KB``; read once per process, so every arm is a subprocess). Prints one
+JSON record per (shape, arm): median milliseconds of ``--iters`` runs timed with CUDA events, each preceded by an L2 flush,
 and the largest difference of dq / dk / dv between the arms.
 
     python bench/attn_bwd_ab.py > profiles/attn_bwd_split_ab.jsonl

@@ -612,7 +612,7 @@ class FSDP(Strategy):
         return off + lo * rowsz, off + hi * rowsz, (hi - lo,) + tuple(shape[1:])
 
     def _overlaps(self, i, chunk_rank, slice_rank):
-        """``[(j, lo, hi)]``: flat ranges that are both in flat slice ``slice_rank`` and in a chunk of ``chunk_rank``."""
+        """``[(j, lo, hi)]``: flat ranges lying both in flat slice ``slice_rank`` and in a chunk of ``chunk_rank``."""
         n = self.units[i].numel // self.W
         s_lo, s_hi = slice_rank * n, (slice_rank + 1) * n
         out = []
@@ -668,7 +668,8 @@ class FSDP(Strategy):
         plan = self._chunk_plan(i)
         n = self.units[i].numel // self.W
         flat_lo = {j: self._chunk_range(shape, off, self.R)[0] for j, (_, shape, off) in enumerate(plan)}
-        local = {j: chunks[name].to(device=self.device, dtype=self.dtype).reshape(-1) for j, (name, _, _) in enumerate(plan)}
+        local = {j: chunks[name].to(device=self.device, dtype=self.dtype).reshape(-1)
+                 for j, (name, _, _) in enumerate(plan)}
         send, ins = [], []
         for k in range(self.W):
             parts = [local[j][lo - flat_lo[j]:hi - flat_lo[j]] for j, lo, hi in self._overlaps(i, self.R, k)]

@@ -1,6 +1,4 @@
 """Memory-bound kernels vs fp32 PyTorch references (forward and backward)."""
-import math
-
 import pytest
 import torch
 
@@ -22,7 +20,7 @@ def _close(a, b, atol, rtol=2e-2):
 @pytest.mark.parametrize("H", [768, 4096, 8192, 16384])
 @pytest.mark.parametrize("with_res", [False, True])
 def test_rmsnorm(H, with_res):
-    from b200train.ops.norm import rmsnorm, rmsnorm_ref
+    from b200train.ops.norm import rmsnorm
 
     T = 300
     x = _r(T, H, seed=1).requires_grad_()
