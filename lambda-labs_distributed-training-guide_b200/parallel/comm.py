@@ -77,11 +77,6 @@ class Comm:
     def broadcast(self, t: torch.Tensor, src: int = 0):
         return t
 
-    def all_to_all(self, out: torch.Tensor, src: torch.Tensor, out_splits, in_splits):
-        """``src`` is cut into ``in_splits`` (one piece per destination rank), ``out`` receives ``out_splits`` (one
-        piece per source rank). Checkpoint re-chunking only: not on the training path."""
-        out.copy_(src)
-
     def barrier(self):
         """Host-blocking barrier (filesystem coordination, start-up)."""
 
@@ -146,12 +141,6 @@ class TorchComm(Comm):
             dist.broadcast(t, src=dist.get_global_rank(self.group, src) if self.group is not None else src,
                            group=self.group)
         return t
-
-    def all_to_all(self, out, src, out_splits, in_splits):
-        if self.world == 1:
-            out.copy_(src)
-            return
-        dist.all_to_all_single(out, src, list(out_splits), list(in_splits), group=self.group)
 
     def barrier(self):
         if self.world > 1:

@@ -600,56 +600,70 @@ class FSDP(Strategy):
             plans[i] = sorted(plan, key=lambda t: t[2]) if plan is not None else None
         return plans[i]
 
-    def _chunk_range(self, shape, off, r):
-        """Flat range of the dim-0 chunk that rank ``r`` of ``W`` holds (torch's ``Shard(0)`` split: ceil)."""
+    def _xchg(self):
+        """Ranks taking part in the re-chunking exchange: ``(group, n, me, slice_of, same_replica)``. Rank r of n
+        holds DCP chunk r of every tensor and flat slice ``slice_of(r)``; ``same_replica(a, b)`` says whether a's
+        slice may serve b's chunk (hybrid shard: every replica holds every slice, only b's own replica sends)."""
+        return getattr(self.comm, "group", None), self.W, self.R, (lambda r: r), (lambda a, b: True)
+
+    def _chunk_range(self, shape, off, r, n):
+        """Flat range of the dim-0 chunk that rank ``r`` of ``n`` holds (torch's ``Shard(0)`` split: ceil)."""
         rows = shape[0]
         rowsz = 1
         for d in shape[1:]:
             rowsz *= d
-        per = (rows + self.W - 1) // self.W
+        per = (rows + n - 1) // n
         lo = min(r * per, rows)
         hi = min(lo + per, rows)
         return off + lo * rowsz, off + hi * rowsz, (hi - lo,) + tuple(shape[1:])
 
-    def _overlaps(self, i, chunk_rank, slice_rank):
-        """``[(j, lo, hi)]``: flat ranges lying both in flat slice ``slice_rank`` and in a chunk of ``chunk_rank``."""
-        n = self.units[i].numel // self.W
-        s_lo, s_hi = slice_rank * n, (slice_rank + 1) * n
+    def _overlaps(self, i, chunk_rank, n, slice_index):
+        """``[(j, lo, hi)]``: flat ranges lying both in flat slice ``slice_index`` and in a chunk of ``chunk_rank``."""
+        per = self.units[i].numel // self.W
+        s_lo, s_hi = slice_index * per, (slice_index + 1) * per
         out = []
         for j, (_, shape, off) in enumerate(self._chunk_plan(i)):
-            a, b, _ = self._chunk_range(shape, off, chunk_rank)
+            a, b, _ = self._chunk_range(shape, off, chunk_rank, n)
             lo, hi = max(a, s_lo), min(b, s_hi)
             if lo < hi:
                 out.append((j, lo, hi))
         return out
 
     def _supports_chunk_exchange(self, i):
-        return (not self.resident and self.W > 1 and self.W == self.world_size and self._chunk_plan(i) is not None)
+        return not self.resident and self._xchg()[1] > 1 and self._chunk_plan(i) is not None
+
+    def _all_to_all(self, group, out, src, outs, ins):
+        import torch.distributed as dist
+
+        dist.all_to_all_single(out, src, list(outs), list(ins), group=group)
 
     @torch.no_grad()
     def unit_named_chunks(self, i: int, kind: str):
         """``{name: (local dim-0 chunk, global shape)}`` of unit ``i`` (``kind``: param / exp_avg / exp_avg_sq) for this
-        rank, or None when the exchange does not apply (single rank, hybrid shard, non-contiguous named tensors)."""
+        rank, or None when the exchange does not apply (single rank, non-contiguous named tensors)."""
         if not self._supports_chunk_exchange(i):
             return None
         if self.is_cuda:
             torch.cuda.synchronize(self.device)
+        group, n, me, slice_of, same_replica = self._xchg()
         plan = self._chunk_plan(i)
-        n = self.units[i].numel // self.W
+        per = self.units[i].numel // self.W
+        my_lo = slice_of(me) * per
         mine = self._shard_of(i, kind).to(self.device)
         send, ins = [], []
-        for r in range(self.W):
-            parts = [mine[lo - self.R * n:hi - self.R * n] for _, lo, hi in self._overlaps(i, r, self.R)]
+        for r in range(n):
+            ov = self._overlaps(i, r, n, slice_of(me)) if same_replica(me, r) else []
+            parts = [mine[lo - my_lo:hi - my_lo] for _, lo, hi in ov]
             ins.append(sum(p.numel() for p in parts))
             send += parts
-        recv_plan = [self._overlaps(i, self.R, k) for k in range(self.W)]
+        recv_plan = [self._overlaps(i, me, n, slice_of(k)) if same_replica(k, me) else [] for k in range(n)]
         outs = [sum(hi - lo for _, lo, hi in ov) for ov in recv_plan]
         got = torch.empty(sum(outs), dtype=mine.dtype, device=self.device)
         src = torch.cat(send) if send else mine[:0]
-        self.comm.all_to_all(got, src, outs, ins)
+        self._all_to_all(group, got, src, outs, ins)
         chunks, flat_lo = {}, {}
         for j, (name, shape, off) in enumerate(plan):
-            a, _, cshape = self._chunk_range(shape, off, self.R)
+            a, _, cshape = self._chunk_range(shape, off, me, n)
             chunks[name] = (torch.empty(cshape, dtype=mine.dtype, device=self.device), torch.Size(shape))
             flat_lo[j] = a
         pos = 0
@@ -662,29 +676,31 @@ class FSDP(Strategy):
     @torch.no_grad()
     def unit_store_chunks(self, i: int, kind: str, chunks) -> bool:
         """Inverse of :meth:`unit_named_chunks`: ``chunks[name]`` is this rank's dim-0 chunk of every named tensor
-        of unit ``i``; every element travels to the rank whose flat slice holds it."""
+        of unit ``i``; every element travels to the rank (under hybrid shard: the ranks) whose flat slice holds it."""
         if not self._supports_chunk_exchange(i):
             return False
+        group, n, me, slice_of, _ = self._xchg()
         plan = self._chunk_plan(i)
-        n = self.units[i].numel // self.W
-        flat_lo = {j: self._chunk_range(shape, off, self.R)[0] for j, (_, shape, off) in enumerate(plan)}
+        per = self.units[i].numel // self.W
+        my_lo = slice_of(me) * per
+        flat_lo = {j: self._chunk_range(shape, off, me, n)[0] for j, (_, shape, off) in enumerate(plan)}
         local = {j: chunks[name].to(device=self.device, dtype=self.dtype).reshape(-1)
                  for j, (name, _, _) in enumerate(plan)}
         send, ins = [], []
-        for k in range(self.W):
-            parts = [local[j][lo - flat_lo[j]:hi - flat_lo[j]] for j, lo, hi in self._overlaps(i, self.R, k)]
+        for k in range(n):
+            parts = [local[j][lo - flat_lo[j]:hi - flat_lo[j]] for j, lo, hi in self._overlaps(i, me, n, slice_of(k))]
             ins.append(sum(p.numel() for p in parts))
             send += parts
-        recv_plan = [self._overlaps(i, r, self.R) for r in range(self.W)]
+        recv_plan = [self._overlaps(i, r, n, slice_of(me)) for r in range(n)]
         outs = [sum(hi - lo for _, lo, hi in ov) for ov in recv_plan]
         got = torch.empty(sum(outs), dtype=self.dtype, device=self.device)
         src = torch.cat(send) if send else got[:0]
-        self.comm.all_to_all(got, src, outs, ins)
-        new = torch.zeros(n, dtype=self.dtype, device=self.device)   # gaps between tensors (alignment) stay zero
+        self._all_to_all(group, got, src, outs, ins)
+        new = torch.zeros(per, dtype=self.dtype, device=self.device)   # gaps between tensors (alignment) stay zero
         pos = 0
         for ov in recv_plan:
             for _, lo, hi in ov:
-                new[lo - self.R * n:hi - self.R * n].copy_(got[pos:pos + hi - lo])
+                new[lo - my_lo:hi - my_lo].copy_(got[pos:pos + hi - lo])
                 pos += hi - lo
         self._shard_of(i, kind).copy_(new)
         return True
@@ -841,6 +857,11 @@ class HSDP(FSDP):
         import torch.distributed as dist
 
         dist.broadcast(full, src=0)   # all replicas, not only this one's sharding group
+
+    def _xchg(self):
+        # chunks are cut over the whole world, slices repeat in every replica: the exchange spans all ranks
+        S = self.W
+        return None, self.global_world, self.global_rank, (lambda r: r % S), (lambda a, b: a // S == b // S)
 
     def post_reduce(self, i, shard):
         if self.rep_group is None:

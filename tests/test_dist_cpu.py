@@ -264,12 +264,13 @@ def test_dcp_sharded_roundtrip():
     assert os.path.exists(os.path.join(tmp, "state.json"))
 
 
-def w_chunk_exchange(rank, world):
+def w_chunk_exchange(rank, world, strategy="fsdp"):
     from b200train.models import load_config
     from b200train.parallel import make_strategy
 
     cfg = load_config("llama-tiny")
-    eng = make_strategy("fsdp", cfg, "cpu", lr=1e-3, dtype=torch.float32, seed=3)
+    kw = dict(replicas=2) if strategy == "hsdp" else {}
+    eng = make_strategy(strategy, cfg, "cpu", lr=1e-3, dtype=torch.float32, seed=3, **kw)
     ids = _batches(cfg, 1, 2, 32, seed=rank)[0]
     eng.train_step({"input_ids": ids, "labels": ids})       # non-trivial moments
     worst, n_tensors, moved = 0.0, 0, 0
@@ -293,6 +294,13 @@ def w_chunk_exchange(rank, world):
             back = eng.unit_named_full(i, kind)
             worst = max(worst, max((back[k] - 2 * full[k]).abs().max().item() for k in full))
     return worst, n_tensors, moved
+
+
+def test_hybrid_shard_checkpoint_chunks_come_from_one_exchange():
+    """2 replicas x 2 shards: chunks are cut over all 4 ranks, each rank is served by its own replica; on load every
+    replica receives every chunk."""
+    for worst, n_tensors, _ in run_dist("w_chunk_exchange", "hsdp", world=4):
+        assert worst == 0.0 and n_tensors > 10, (worst, n_tensors)
 
 
 @pytest.mark.parametrize("world", [2, 3])
