@@ -206,6 +206,66 @@ def test_dcp_save_swaps_directories_and_survives_a_torn_attempt():
     assert not any(n.startswith("checkpoint.") or n.startswith(".shared") for n in names), names
 
 
+def _moment_energy(eng):
+    """Sum of squares of all first moments over all ranks (a fingerprint of the optimizer state)."""
+    t = torch.zeros(1, dtype=torch.float64)
+    for m in eng.optimizer.exp_avg:
+        t += m.double().pow(2).sum()
+    if dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(t)
+    return t.item()
+
+
+def w_ws_save(rank, world, tmp):
+    from pathlib import Path
+
+    from b200train.ckpt.dcp import save_sharded
+    from b200train.models import load_config
+    from b200train.parallel import make_strategy
+
+    cfg = load_config("llama-tiny")
+    eng = make_strategy("fsdp", cfg, "cpu", lr=1e-3, dtype=torch.float32)
+    ids = _batches(cfg, 1, 4, 32)[0]
+    for _ in range(2):
+        eng.train_step({"input_ids": ids[rank::world], "labels": ids[rank::world]})
+    save_sharded(Path(tmp), eng, state={"epoch": 0, "global_step": 2, "epoch_step": 2, "running_loss": 0.0})
+    with torch.no_grad():
+        probe = eng.forward(eng.to_device({"input_ids": ids, "labels": ids})).loss.item()
+    return probe, _moment_energy(eng)
+
+
+def w_ws_load(rank, world, tmp):
+    from pathlib import Path
+
+    from b200train.ckpt.dcp import load_sharded
+    from b200train.models import load_config
+    from b200train.parallel import make_strategy
+
+    cfg = load_config("llama-tiny")
+    eng = make_strategy("fsdp", cfg, "cpu", lr=1e-3, dtype=torch.float32, seed=99)
+    load_sharded(Path(tmp), eng)
+    ids = _batches(cfg, 1, 4, 32)[0]
+    with torch.no_grad():
+        probe = eng.forward(eng.to_device({"input_ids": ids, "labels": ids})).loss.item()
+    return probe, _moment_energy(eng), eng.optimizer_step_count()
+
+
+@pytest.mark.parametrize("new_world", [3, 1])
+def test_sharded_checkpoint_loads_into_a_different_world_size(new_world):
+    """Elastic restarts change the number of ranks: a checkpoint written by 2 ranks must load into 3 (chunks that
+    do not divide evenly) and into 1 (nothing sharded), with the same weights, moments and step count."""
+    tmp = tempfile.mkdtemp()
+    probe, energy = run_dist("w_ws_save", tmp, world=2)[0]
+    if new_world == 1:
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(_free_port()))
+        got = run_dist("w_ws_load", tmp, world=1)[0]
+    else:
+        got = run_dist("w_ws_load", tmp, world=new_world)[0]
+    assert abs(got[0] - probe) < 1e-5, (got, probe)
+    assert abs(got[1] - energy) <= 1e-6 * max(energy, 1e-12), (got, energy)
+    assert got[2] == 2
+
+
 def w_dcp_stock(rank, world, tmp):
     """A checkpoint directory written by STOCK torch.distributed.checkpoint code -- DTensors sharded on dim 0
     under the reference's keys (``model.<hf name>``, ``optimizer.state.<hf name>.exp_avg`` ...), which is
