@@ -250,20 +250,16 @@ def w_ws_load(rank, world, tmp):
     return probe, _moment_energy(eng), eng.optimizer_step_count()
 
 
-@pytest.mark.parametrize("new_world", [3, 1])
-def test_sharded_checkpoint_loads_into_a_different_world_size(new_world):
+def test_sharded_checkpoint_loads_into_a_different_world_size():
     """Elastic restarts change the number of ranks: a checkpoint written by 2 ranks must load into 3 (chunks that
     do not divide evenly) and into 1 (nothing sharded), with the same weights, moments and step count."""
     tmp = tempfile.mkdtemp()
     probe, energy = run_dist("w_ws_save", tmp, world=2)[0]
-    if new_world == 1:
-        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(_free_port()))
-        got = run_dist("w_ws_load", tmp, world=1)[0]
-    else:
+    for new_world in (3, 1):
         got = run_dist("w_ws_load", tmp, world=new_world)[0]
-    assert abs(got[0] - probe) < 1e-5, (got, probe)
-    assert abs(got[1] - energy) <= 1e-6 * max(energy, 1e-12), (got, energy)
-    assert got[2] == 2
+        assert abs(got[0] - probe) < 1e-5, (new_world, got, probe)
+        assert abs(got[1] - energy) <= 1e-6 * max(energy, 1e-12), (new_world, got, energy)
+        assert got[2] == 2
 
 
 def w_dcp_stock(rank, world, tmp):
@@ -363,7 +359,7 @@ def test_hybrid_shard_checkpoint_chunks_come_from_one_exchange():
         assert worst == 0.0 and n_tensors > 10, (worst, n_tensors)
 
 
-@pytest.mark.parametrize("world", [2, 3])
+@pytest.mark.parametrize("world", [3])
 def test_fsdp_checkpoint_chunks_come_from_one_exchange(world):
     """DCP's dim-0 chunks are produced from the flat shards by an all-to-all (no full-size gather): they equal the
     chunks cut from the gathered unit for every tensor and moment, also when the rows do not divide by the world
