@@ -248,6 +248,8 @@ if __name__ == "__main__":
         fns = fns[1:]
     if "--only-gemm" in sys.argv:
         fns = fns[:1]
+    if "--only-elementwise" in sys.argv:
+        fns = (bench_elementwise,)
     for fn in fns:
         try:
             fn(results, quick) if fn is bench_gemm else fn(results)
@@ -255,5 +257,6 @@ if __name__ == "__main__":
             print(f"{fn.__name__} failed: {type(e).__name__}: {e}", flush=True)
             results[fn.__name__ + "_error"] = str(e)
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
-    out = "kernel_bench_gemm.json" if "--only-gemm" in sys.argv else "kernel_bench.json"
+    out = ("kernel_bench_gemm.json" if "--only-gemm" in sys.argv else
+           "kernel_bench_elementwise.json" if "--only-elementwise" in sys.argv else "kernel_bench.json")
     json.dump(results, open(os.path.join(ROOT, "gpurun_out", out), "w"), indent=1)
