@@ -123,6 +123,14 @@ int b2_colsum(void* out, float* partial, const void* x, int T, int N, int ld, in
  * Reference: AdamW(fused=True) running on CPU under CPUOffload, 05-training-llama-405b/README.md:147-153. */
 int b2_cpu_adamw_bf16(void* p, void* m, void* v, const void* g, size_t n, float lr, float beta1,
                       float beta2, float eps, float wd, int step, float grad_scale);
+int b2_cpu_set_threads(int n);   /* OpenMP threads of the host kernels (n <= 0: query); returns the count */
+
+/* ---- host dropout (OpenMP + AVX-512), same Philox mask as b2_dropout ---------------------------------
+ * out = dropout(x) over n HOST elements of elem_size 2 (bf16) or 4 (fp32); out may alias x. Element e is kept
+ * iff the device kernel keeps it for the same (p, seed, offset): backward calls this on the gradient.
+ * Reference: GPT-2's three dropout sites on the CPU path of 01-single-gpu/train_llm.py (ATen bernoulli_). */
+int b2_cpu_dropout(void* out, const void* x, size_t n, int elem_size, float p, unsigned long long seed,
+                   unsigned long long offset);
 
 /* ---- GEMMs with fused elementwise neighbours ----------------------------------------------------------
  * b2_gemm_swiglu : GU[M, 2I] = x W^T (gate | up, kept for backward) and H[M, I] = silu(gate) * up in one GEMM

@@ -78,6 +78,7 @@ def _declare(lib):
         "b2_peer_all_gather_chunks": [P, P, Z, I, I, P, ctypes.c_uint, P],
         "b2_cpu_adamw_bf16": [P, P, P, P, Z, F, F, F, F, F, I, F],
         "b2_cpu_set_threads": [I],
+        "b2_cpu_dropout": [P, P, Z, I, F, ctypes.c_ulonglong, ctypes.c_ulonglong],
         "b2_peer_barrier": [P, I, I, I, ctypes.c_uint, P],
         "b2_peer_all_gather": [P, P, Z, I, I, I, I, P],
         "b2_peer_all_gather_ce": [P, P, Z, I, I, I, I, P],

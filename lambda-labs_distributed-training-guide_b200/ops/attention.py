@@ -99,6 +99,19 @@ class _Attention(torch.autograd.Function):
         return dqkv, None, None, None, None, None, None, None, None
 
 
+_MASKS = {}
+
+
+def _causal_mask(L: int) -> torch.Tensor:
+    """[L, L] bool, True above the diagonal (cached per length: the CPU path builds it once, not per layer)."""
+    m = _MASKS.get(L)
+    if m is None:
+        if len(_MASKS) > 8:
+            _MASKS.clear()
+        m = _MASKS[L] = torch.ones(L, L, dtype=torch.bool).triu_(1)
+    return m
+
+
 def attention_ref(qkv, cu_seqlens, max_seqlen, n_q, n_kv, D, scale=None, causal=True, dropout_p=0.0):
     """fp32 PyTorch reference over each document separately (``dropout_p``: torch's own mask)."""
     scale = scale if scale is not None else 1.0 / math.sqrt(D)
@@ -118,8 +131,18 @@ def attention_ref(qkv, cu_seqlens, max_seqlen, n_q, n_kv, D, scale=None, causal=
             vi = v[s:e].transpose(0, 1).unsqueeze(0)
             if g > 1:
                 ki, vi = ki.repeat_interleave(g, dim=1), vi.repeat_interleave(g, dim=1)
-            oi = torch.nn.functional.scaled_dot_product_attention(qi, ki, vi, is_causal=causal, scale=scale,
-                                                                  dropout_p=dropout_p)
+            if dropout_p > 0.0:
+                # ATen's fused CPU attention has no dropout and its math fallback draws the mask from one
+                # sequential stream (half of a GPT-2 CPU step): explicit products + the Philox dropout of ops.dropout
+                from .dropout import dropout as _dropout
+
+                att = torch.matmul(qi * scale, ki.transpose(-1, -2))   # scale on [L, D], not on [L, L]
+                if causal:
+                    att.masked_fill_(_causal_mask(e - s), float("-inf"))
+                pi = _dropout(torch.softmax(att, dim=-1), dropout_p)
+                oi = torch.matmul(pi, vi)
+            else:
+                oi = torch.nn.functional.scaled_dot_product_attention(qi, ki, vi, is_causal=causal, scale=scale)
             outs.append(oi[0].transpose(0, 1).reshape(e - s, n_q * D))
             continue
         qi = q[s:e].transpose(0, 1).float()

@@ -351,3 +351,53 @@ def test_warmup_cosine_schedule_of_the_deepspeed_variant():
         opt.step()
         sched.step()
     assert math.isclose(opt.param_groups[0]["lr"], 3e-7, rel_tol=1e-6)
+
+
+def _philox_np(ctr, k0, k1):
+    import numpy as np
+
+    c = [np.uint32(v) for v in ctr]
+    for _ in range(10):
+        p0 = np.uint64(0xD2511F53) * np.uint64(c[0])
+        p1 = np.uint64(0xCD9E8D57) * np.uint64(c[2])
+        hi0, lo0 = np.uint32(p0 >> np.uint64(32)), np.uint32(p0 & np.uint64(0xFFFFFFFF))
+        hi1, lo1 = np.uint32(p1 >> np.uint64(32)), np.uint32(p1 & np.uint64(0xFFFFFFFF))
+        c = [hi1 ^ c[1] ^ np.uint32(k0), lo1, hi0 ^ c[3] ^ np.uint32(k1), lo0]
+        k0, k1 = (k0 + 0x9E3779B9) & 0xFFFFFFFF, (k1 + 0xBB67AE85) & 0xFFFFFFFF
+    return [int(v) for v in c]
+
+
+def test_host_dropout_is_philox_and_regenerates_its_mask_in_backward():
+    """``csrc/cpu_dropout.cpp`` against an independent Philox4x32-10 in numpy with the device kernel's counter
+    layout (vector of 8 elements -> two blocks, keep iff draw >= p * 2^32): the AVX-512 groups and the scalar
+    tail give the same mask; backward applies the same mask to the gradient without having stored it."""
+    from b200train.ops.dropout import _cpu_kernel_ok, dropout
+
+    if not _cpu_kernel_ok():
+        pytest.skip("native library not built")
+    n, p = 128 * 3 + 29, 0.25
+    seed, offset = 0x0123456789ABCDEF, 0x0FEDCBA987654321
+    k0 = (seed ^ offset) & 0xFFFFFFFF
+    k1 = ((seed >> 32) ^ (offset >> 32) ^ 0x27D4EB2F) & 0xFFFFFFFF
+    keep = torch.zeros(n, dtype=torch.bool)
+    for i in range((n + 7) // 8):
+        r = _philox_np([i, 0, 0, 0], k0, k1) + _philox_np([i, 0, 1, 0], k0, k1)
+        for j in range(8):
+            if i * 8 + j < n:
+                keep[i * 8 + j] = r[j] >= int(p * 2 ** 32)
+    assert 0.6 < keep.float().mean().item() < 0.9
+    sc = torch.tensor(1.0 / (1.0 - p), dtype=torch.float32)   # the kernel multiplies by the fp32 reciprocal
+    for dt in (torch.float32, torch.bfloat16):
+        x = (torch.arange(1, n + 1, dtype=torch.float32) / 64).to(dt).requires_grad_()
+        y = dropout(x, p, philox=(seed, offset))
+        want = torch.where(keep, (x.detach().float() * sc).to(dt), torch.zeros(n, dtype=dt))
+        assert torch.equal(y.detach(), want), dt
+        g = torch.ones(n, dtype=dt)
+        y.backward(g)
+        assert torch.equal(x.grad, torch.where(keep, (g.float() * sc).to(dt), torch.zeros(n, dtype=dt))), dt
+    # draws from the default generator: repeatable under manual_seed, different between calls
+    torch.manual_seed(5)
+    a, b = dropout(torch.ones(4096), 0.5), dropout(torch.ones(4096), 0.5)
+    torch.manual_seed(5)
+    a2 = dropout(torch.ones(4096), 0.5)
+    assert torch.equal(a, a2) and not torch.equal(a, b) and abs(a.mean().item() - 1.0) < 0.1

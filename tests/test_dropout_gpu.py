@@ -40,6 +40,19 @@ def test_elementwise_dropout_statistics_and_backward():
     assert ops.dropout(x, p, training=False) is x and ops.dropout(x, 0.0) is x
 
 
+def test_host_and_device_dropout_drop_the_same_elements():
+    """``csrc/cpu_dropout.cpp`` mirrors the device kernel's Philox layout: the same (seed, offset) gives the same
+    output bit for bit on a CPU tensor and on a CUDA tensor (also across the AVX-512 / scalar-tail boundary)."""
+    from b200train.ops.dropout import dropout
+
+    for n in (8 * 1000, 128 * 77 + 8 * 5):
+        x = torch.randn(n).to(torch.bfloat16)
+        for p, philox in ((0.1, (1234, 99)), (0.5, (2 ** 62 + 12345, 2 ** 40 + 7))):
+            host = dropout(x, p, philox=philox)
+            dev = dropout(x.cuda(), p, philox=philox)
+            assert torch.equal(host, dev.cpu()), (n, p)
+
+
 def _keep_mask(nq, S, p, seed, offset):
     from b200train import _C
     from b200train.ops.dispatch import stream
