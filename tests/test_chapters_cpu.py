@@ -27,9 +27,18 @@ def _run(script, nproc, args, timeout=420):
     else:
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
                "--master-addr", "127.0.0.1", "--master-port", str(_port()), str(ROOT / script)] + args
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=env, cwd=str(ROOT))
-    assert r.returncode == 0, (r.stdout + r.stderr)[-3000:]
-    return r.stdout + r.stderr
+    for attempt in range(3):
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=env, cwd=str(ROOT))
+        out = r.stdout + r.stderr
+        # gloo's TCP mesh set-up occasionally fails on a loaded box before the script has done anything: retry
+        # that (on a fresh port), and only that
+        if r.returncode != 0 and attempt < 2 and nproc > 1 and "global_step" not in out and any(
+                t in out for t in ("connectFullMesh", "Connection refused", "Connection reset by peer")):
+            cmd = [c if not c.isdigit() or cmd[i - 1] != "--master-port" else str(_port()) for i, c in enumerate(cmd)]
+            continue
+        break
+    assert r.returncode == 0, out[-3000:]
+    return out
 
 
 COMMON = ["-d", "synthetic:64", "-m", "llama-tiny", "--device", "cpu", "-b", "2", "-s", "32", "--log-freq", "2",

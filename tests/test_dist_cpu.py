@@ -34,10 +34,22 @@ def _worker_impl(rank, world, port, fn, ret):
         dist.destroy_process_group()
 
 
+_TRANSPORT_ERRORS = ("connectFullMesh", "Connection refused", "Connection reset by peer", "Address already in use")
+
+
 def run_dist(fn_name, *args, world=2):
-    ret = mp.Manager().dict()
-    mp.spawn(_worker, args=(world, _free_port(), fn_name, args, ret), nprocs=world, join=True)
-    return [ret[r] for r in range(world)]
+    """Spawn ``world`` gloo ranks. gloo's TCP mesh set-up occasionally fails on a loaded box before any test code
+    has run (``connectFullMesh ... Connection refused``): that alone is retried on a fresh port, nothing else is."""
+    os.environ.setdefault("GLOO_SOCKET_IFNAME", "lo")
+    for attempt in range(3):
+        ret = mp.Manager().dict()
+        try:
+            mp.spawn(_worker, args=(world, _free_port(), fn_name, args, ret), nprocs=world, join=True)
+        except Exception as e:
+            if attempt < 2 and any(t in str(e) for t in _TRANSPORT_ERRORS):
+                continue
+            raise
+        return [ret[r] for r in range(world)]
 
 
 def _batches(cfg, n, B, S, seed=0):
