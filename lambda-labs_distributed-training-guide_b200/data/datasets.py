@@ -112,6 +112,52 @@ def _read_local_texts(path: Path):
                     yield row["text"] if "text" in row else next(iter(row.values()))
 
 
+def _cache_dir() -> Path:
+    root = os.environ.get("B200TRAIN_CACHE") or os.environ.get("HF_HOME") or os.path.join(os.getcwd(), "tmp")
+    d = Path(root) / "b200train-tokenized"
+    d.mkdir(parents=True, exist_ok=True)
+    return d
+
+
+def _tokenize_local(path: Path, tokenizer, model_name: str, batch: int = 512) -> torch.Tensor:
+    """One long token stream from local ``.txt`` / ``.jsonl`` files: texts go to the tokenizer in batches (the fast
+    tokenizers parallelise over a batch) and the stream is cached on disk keyed by the files' names, sizes and
+    modification times and the tokenizer, as ``datasets.map(load_from_cache_file=True)`` does for hub datasets
+    (``01-single-gpu/train_llm.py:204-247``). The callers run this under ``rank0_first``: one rank fills the cache,
+    the others read it."""
+    import hashlib
+
+    files = sorted(f for f in (path.rglob("*") if path.is_dir() else [path]) if f.is_file())
+    h = hashlib.sha256(f"{model_name}|{type(tokenizer).__name__}|{getattr(tokenizer, 'vocab_size', 0)}".encode())
+    for f in files:
+        st = f.stat()
+        h.update(f"{f.resolve()}|{st.st_size}|{st.st_mtime_ns}".encode())
+    cache = _cache_dir() / f"{h.hexdigest()[:32]}.pt"
+    if cache.exists():
+        try:
+            return torch.load(cache, weights_only=True)
+        except Exception:   # a torn or foreign file: rebuild it
+            pass
+    chunks, pending = [], []
+
+    def flush():
+        if pending:
+            for row in tokenizer(pending)["input_ids"]:
+                chunks.append(torch.as_tensor(row, dtype=torch.long))
+            pending.clear()
+
+    for text in _read_local_texts(path):
+        pending.append(text)
+        if len(pending) >= batch:
+            flush()
+    flush()
+    ids = torch.cat(chunks) if chunks else torch.zeros(0, dtype=torch.long)
+    tmp = cache.with_name(cache.name + f".tmp{os.getpid()}")
+    torch.save(ids, tmp)
+    os.replace(tmp, cache)
+    return ids
+
+
 def group_texts(examples: dict, seq_length: int) -> dict:
     """Concatenate then chunk (the reference's inner ``group_texts``, ``01-.../train_llm.py:223-236``)."""
     concatenated = {k: list(chain(*examples[k])) for k in examples.keys()}
@@ -134,10 +180,7 @@ def load_and_preprocess_data(dataset_name: str, model_name: str, config, seq_len
                             config.max_position_embeddings)
     p = Path(dataset_name)
     if p.exists():
-        ids = []
-        for text in _read_local_texts(p):
-            ids.extend(tokenizer([text])["input_ids"][0])
-        return TokenBlocks(torch.tensor(ids, dtype=torch.long), sl)
+        return TokenBlocks(_tokenize_local(p, tokenizer, model_name), sl)
     import datasets  # hub / cache datasets, exactly the reference flow
 
     data = datasets.load_dataset(dataset_name, trust_remote_code=True)

@@ -401,3 +401,32 @@ def test_host_dropout_is_philox_and_regenerates_its_mask_in_backward():
     torch.manual_seed(5)
     a2 = dropout(torch.ones(4096), 0.5)
     assert torch.equal(a, a2) and not torch.equal(a, b) and abs(a.mean().item() - 1.0) < 0.1
+
+
+def test_local_corpus_is_tokenized_in_batches_and_cached(tmp_path, monkeypatch):
+    """A local .txt / .jsonl corpus: concatenated token stream cut into blocks, cached on disk (second call does
+    not tokenize), cache invalidated when a file changes."""
+    from b200train.data import datasets as D
+    from b200train.models import load_config
+
+    monkeypatch.setenv("B200TRAIN_CACHE", str(tmp_path / "cache"))
+    corpus = tmp_path / "corpus"
+    corpus.mkdir()
+    (corpus / "a.txt").write_text("hello world " * 40)
+    (corpus / "b.jsonl").write_text("\n".join(json.dumps({"text": f"row {i} " * 10}) for i in range(30)))
+    cfg = load_config("llama-tiny")
+    calls = []
+    real = D.ByteTokenizer.__call__
+    monkeypatch.setattr(D.ByteTokenizer, "__call__", lambda self, texts: (calls.append(len(texts)), real(self, texts))[1])
+    ds = D.load_and_preprocess_data(str(corpus), "llama-tiny", cfg, 32)
+    assert sum(calls) == 31 and len(calls) == 1                      # one batch for all 31 texts
+    want = ("hello world " * 40).encode() + b""
+    assert bytes(ds[0]["input_ids"].tolist()) == want[:32] and torch.equal(ds[0]["labels"], ds[0]["input_ids"])
+    n_blocks = len(ds)
+    assert n_blocks == (len(want) + 1 + sum(len((f"row {i} " * 10).encode()) + 1 for i in range(30))) // 32
+    calls.clear()
+    ds2 = D.load_and_preprocess_data(str(corpus), "llama-tiny", cfg, 32)
+    assert calls == [] and len(ds2) == n_blocks and torch.equal(ds2[3]["input_ids"], ds[3]["input_ids"])
+    (corpus / "a.txt").write_text("changed " * 50)
+    D.load_and_preprocess_data(str(corpus), "llama-tiny", cfg, 32)
+    assert calls == [31]                                              # the cache key covers size and mtime
