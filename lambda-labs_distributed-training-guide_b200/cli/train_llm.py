@@ -17,6 +17,7 @@ import argparse
 import json
 import os
 from contextlib import contextmanager, nullcontext
+from functools import partial
 from pathlib import Path
 
 import torch
@@ -100,6 +101,9 @@ def get_parser(chapter: str = "generic") -> argparse.ArgumentParser:
                         "recomputed in backward (0: all rows at once, fastest; the fork's chapter 00 uses Liger's "
                         "fused linear cross entropy for the same purpose)")
     p.add_argument("--packed", action="store_true", help="packed rows: derive position ids per document")
+    p.add_argument("--eos-id", type=int, default=None,
+                   help="document separator of packed rows (default: 128262, the fork's extended-vocabulary EOS, "
+                        "when the vocabulary has it, else the last id of the vocabulary)")
     p.add_argument("--max-steps", default=None, type=int, help="stop after this many optimizer steps")
     p.add_argument("--pretrained", default=None,
                    help="local directory with *.safetensors to start from (reference: from_pretrained, ch05 / ch00)")
@@ -218,9 +222,17 @@ def main(chapter: str = "generic", argv=None):
         LOGGER.info(f"loaded {n_loaded} pretrained tensors from {args.pretrained}")
     LOGGER.info(f"After sharding: {get_mem_stats(device)}")
 
+    packed = args.packed or chapter == "00-rime"
+    eos_id = None
+    if packed:
+        from ..data.packed import EOS_ID_DEFAULT
+
+        eos_id = args.eos_id if args.eos_id is not None else (
+            EOS_ID_DEFAULT if config.vocab_size > EOS_ID_DEFAULT else config.vocab_size - 1)
+        LOGGER.info(f"packed rows: documents end at token id {eos_id}")
     with rank_ordered(first):
         train_data = load_and_preprocess_data(args.dataset_name, args.model_name, config, args.seq_length,
-                                              seed=args.seed)
+                                              seed=args.seed, packed_eos_id=eos_id)
     seq_length = len(train_data[0]["input_ids"])
     LOGGER.info(f"{len(train_data)} training samples")
     if hasattr(engine, "data_parallel_coords"):
@@ -229,7 +241,7 @@ def main(chapter: str = "generic", argv=None):
         dp_rank, dp_size = rank, world_size
     dataloader = make_dataloader(train_data, args.batch_size, dp_rank=dp_rank, dp_size=dp_size, seed=args.seed,
                                  num_workers=args.num_workers, prefetch_factor=args.prefetch_factor,
-                                 collate_fn=pad_and_collate if (args.packed or chapter == "00-rime") else None,
+                                 collate_fn=partial(pad_and_collate, eos_id=eos_id) if packed else None,
                                  pin_memory=device.type == "cuda", distributed=strategy_name != "single")
     LOGGER.info(f"{len(dataloader)} batches per epoch")
 

@@ -27,15 +27,25 @@ from torch.utils.data import Dataset
 class SyntheticTokens(Dataset):
     """Deterministic random token rows; sample ``i`` depends only on ``(seed, i)``."""
 
-    def __init__(self, vocab_size: int, seq_length: int, n_samples: int = 4096, seed: int = 0):
+    def __init__(self, vocab_size: int, seq_length: int, n_samples: int = 4096, seed: int = 0, eos_id=None,
+                 doc_length: int = 701):
+        """``eos_id``: make the rows PACKED -- every ``doc_length``-th token is ``eos_id`` (and no other token is),
+        so a row holds ``seq_length / doc_length`` documents the way the fork's pre-packed dataset does
+        (``00-rime/packed_dataset.py``: EOS-separated documents in 8192-token rows)."""
         self.vocab_size, self.seq_length, self.n, self.seed = vocab_size, seq_length, n_samples, seed
+        self.eos_id, self.doc_length = eos_id, doc_length
 
     def __len__(self):
         return self.n
 
     def __getitem__(self, i):
         g = torch.Generator().manual_seed(self.seed * 1_000_003 + int(i))
-        ids = torch.randint(0, self.vocab_size, (self.seq_length,), generator=g)
+        if self.eos_id is None:
+            ids = torch.randint(0, self.vocab_size, (self.seq_length,), generator=g)
+        else:
+            ids = torch.randint(0, self.vocab_size - 1, (self.seq_length,), generator=g)
+            ids += (ids >= self.eos_id).long()          # skip the EOS id: it only appears as a separator
+            ids[self.doc_length - 1::self.doc_length] = self.eos_id
         return {"input_ids": ids, "attention_mask": torch.ones_like(ids), "labels": ids.clone()}
 
 
@@ -169,12 +179,14 @@ def group_texts(examples: dict, seq_length: int) -> dict:
     return result
 
 
-def load_and_preprocess_data(dataset_name: str, model_name: str, config, seq_length=None, seed: int = 0):
-    """Returns a map-style dataset of ``{"input_ids", "attention_mask", "labels"}`` rows."""
+def load_and_preprocess_data(dataset_name: str, model_name: str, config, seq_length=None, seed: int = 0,
+                             packed_eos_id=None):
+    """Returns a map-style dataset of ``{"input_ids", "attention_mask", "labels"}`` rows. ``packed_eos_id``: the
+    synthetic rows are packed documents separated by that token (chapter 00 / ``--packed``)."""
     if dataset_name.startswith("synthetic"):
         n = int(dataset_name.split(":")[1]) if ":" in dataset_name else 4096
         sl = resolve_seq_length(seq_length, 1024, config.max_position_embeddings)
-        return SyntheticTokens(config.vocab_size, sl, n, seed)
+        return SyntheticTokens(config.vocab_size, sl, n, seed, eos_id=packed_eos_id)
     tokenizer = _load_tokenizer(model_name)
     sl = resolve_seq_length(seq_length, min(getattr(tokenizer, "model_max_length", 1024), 1 << 20),
                             config.max_position_embeddings)

@@ -430,3 +430,26 @@ def test_local_corpus_is_tokenized_in_batches_and_cached(tmp_path, monkeypatch):
     (corpus / "a.txt").write_text("changed " * 50)
     D.load_and_preprocess_data(str(corpus), "llama-tiny", cfg, 32)
     assert calls == [31]                                              # the cache key covers size and mtime
+
+
+def test_synthetic_packed_rows_hold_several_documents():
+    """Chapter 00 / ``--packed`` with synthetic data: rows are documents of 701 tokens separated by the EOS id (which
+    appears nowhere else), and the collator restarts the position ids at every document."""
+    from functools import partial
+
+    from b200train.data.datasets import SyntheticTokens
+    from b200train.data.packed import cu_seqlens_from_positions, pad_and_collate
+
+    eos = 999
+    ds = SyntheticTokens(1000, 2048, n_samples=4, seed=1, eos_id=eos)
+    row = ds[2]["input_ids"]
+    ends = torch.nonzero(row == eos).flatten().tolist()
+    assert ends == [700, 1401] and int(row.max()) <= 999
+    batch = partial(pad_and_collate, eos_id=eos)([ds[0], ds[1]])
+    pos = batch["position_ids"]
+    assert pos.shape == (2, 2048) and pos[0, 700] == 700 and pos[0, 701] == 0 and pos[0, 1402] == 0
+    assert int(pos[0, -1]) == 2048 - 1402 - 1
+    cu = cu_seqlens_from_positions(pos)
+    assert cu.tolist() == [0, 701, 1402, 2048, 2749, 3450, 4096]
+    plain = SyntheticTokens(1000, 2048, n_samples=4, seed=1)
+    assert not torch.equal(plain[2]["input_ids"], row)
