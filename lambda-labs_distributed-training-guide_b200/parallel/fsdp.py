@@ -579,6 +579,9 @@ class FSDP(Strategy):
 
 
     # ---- checkpoint surface without full-size gathers ---------------------------------------------------
+    # Reference: get_state_dict(..., StateDictOptions(full_state_dict=False)) + DCP save / load of the sharded
+    # containers (04-fully-sharded-data-parallel/train_llm.py:122,132-154,249-263), where FSDP1's flat-parameter
+    # runtime re-chunks into ShardedTensors internally.
     # torch.distributed.checkpoint wants, from rank r, the r-th dim-0 chunk of every named tensor; the strategy
     # owns the r-th slice of every flat unit. The two partitions cover the same bytes, so re-chunking is an
     # exchange in which every element moves at most once: rank k sends to rank r the overlap of flat slice k with
