@@ -313,6 +313,17 @@ def run_reference(args):
 
 if __name__ == "__main__":
     a = parse()
+    try:
+        import torch
+
+        no_gpu = not torch.cuda.is_available()
+    except Exception:   # never let this courtesy check stand in the way of a run
+        no_gpu = False
+    if no_gpu:
+        # the headline configuration is a GPU one; say so instead of dying inside CUDA initialisation
+        print("bench.py needs a CUDA device (the CPU configuration of BASELINE.json is bench/config1_cpu.py)",
+              file=sys.stderr)
+        sys.exit(2)
     if a.impl == "reference":
         run_reference(a)
     else:
