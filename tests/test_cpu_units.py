@@ -453,3 +453,32 @@ def test_synthetic_packed_rows_hold_several_documents():
     assert cu.tolist() == [0, 701, 1402, 2048, 2749, 3450, 4096]
     plain = SyntheticTokens(1000, 2048, n_samples=4, seed=1)
     assert not torch.equal(plain[2]["input_ids"], row)
+
+
+def test_cpu_attention_with_dropout_uses_the_philox_mask():
+    """The CPU attention path with ``dropout_p`` > 0 (GPT-2 on CPU): explicit products with the host Philox dropout
+    on the probabilities. Same generator state -> same result as a hand-written softmax(QK^T)V with ``ops.dropout``
+    at the same site; without dropout it equals ATen's fused attention; gradients reach q, k and v."""
+    from b200train.ops.attention import attention_ref
+    from b200train.ops.dropout import dropout
+
+    torch.manual_seed(0)
+    L, H, D = 48, 3, 16
+    qkv = torch.randn(2 * L, 3 * H * D, requires_grad=True)
+    cu = torch.tensor([0, L, 2 * L], dtype=torch.int32)
+    torch.manual_seed(11)
+    out = attention_ref(qkv, cu, L, H, H, D, causal=True, dropout_p=0.25)
+    q, k, v = (t.reshape(2 * L, H, D) for t in qkv.detach().split(H * D, dim=1))
+    torch.manual_seed(11)
+    rows = []
+    for s in (0, L):
+        qi, ki, vi = (t[s:s + L].transpose(0, 1).unsqueeze(0) for t in (q, k, v))
+        att = torch.matmul(qi * D ** -0.5, ki.transpose(-1, -2))
+        att = att.masked_fill(torch.ones(L, L, dtype=torch.bool).triu_(1), float("-inf"))
+        pi = dropout(torch.softmax(att, dim=-1), 0.25)
+        rows.append(torch.matmul(pi, vi)[0].transpose(0, 1).reshape(L, H * D))
+    assert torch.allclose(out.detach(), torch.cat(rows), atol=1e-6)
+    assert not torch.allclose(out.detach(), attention_ref(qkv, cu, L, H, H, D, causal=True).detach(), atol=1e-3)
+    out.square().sum().backward()
+    g = qkv.grad.reshape(2 * L, 3, H * D)
+    assert all(g[:, j].abs().sum().item() > 0 for j in range(3))
