@@ -157,10 +157,9 @@ class Strategy:
         return self._named_views(i, self._unit_full_flat(i, kind))
 
     def _names_probe(self, i: int):
-        u = self.units[i]
-        if not hasattr(self, "_probe") or self._probe.numel() < u.numel:
-            self._probe = torch.empty(max(x.numel for x in self.units), dtype=self.dtype, device=self.device)
-        return self._probe[:u.numel]
+        """Scratch laid out like unit ``i`` (only its addresses are used: which named tensor sits where). Not kept:
+        a unit of Llama-405B is 6.4 GB, and checkpoints are rare."""
+        return torch.empty(self.units[i].numel, dtype=self.dtype, device=self.device)
 
     @torch.no_grad()
     def unit_store_named(self, i: int, kind: str, tensors):
