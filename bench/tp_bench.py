@@ -20,7 +20,16 @@ from b200train.ops.linear import gemm  # noqa: E402
 from b200train.parallel.comm import init_distributed  # noqa: E402
 from b200train.parallel.tp_fused import FusedTP  # noqa: E402
 
-PEAK = 1637.5e12
+def _peak_flops():
+    """Measured bf16 GEMM peak of this pool (MEASURED_PEAKS.json, written by the driver); the profiling recipe's
+    fallback when the file is absent."""
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops"]) * 1e12
+    except Exception:
+        return 1590.0e12
+
+
+PEAK = _peak_flops()
 LINK = 770e9
 
 
