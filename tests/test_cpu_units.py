@@ -482,3 +482,23 @@ def test_cpu_attention_with_dropout_uses_the_philox_mask():
     out.square().sum().backward()
     g = qkv.grad.reshape(2 * L, 3, H * D)
     assert all(g[:, j].abs().sum().item() > 0 for j in range(3))
+
+
+def test_reduce_scatter_transport_policy():
+    """``PeerComm._transport``: which path a reduce-scatter takes (copy engines + local reduce, in-switch
+    ``multimem.ld_reduce``, SM loads from the peers) as a function of world size, fusion with AdamW, the
+    availability of a multicast mapping and the ``B200TRAIN_RS_TRANSPORT`` override."""
+    from types import SimpleNamespace
+
+    from b200train.parallel.peer import PeerComm
+
+    def pick(world, fused=False, mc=True, override="auto", nvls_flag=True, forced=None):
+        stub = SimpleNamespace(rs_transport=override, world=world, nvls=nvls_flag)
+        return PeerComm._transport(stub, forced, mc, fused)
+
+    assert pick(2) == "ce" and pick(4) == "nvls" and pick(8) == "nvls"          # plain: in-switch from 4 ranks
+    assert pick(4, mc=False) == "ce" and pick(8, nvls_flag=False) == "ce"       # no multicast mapping: copy engines
+    assert all(pick(w, fused=True) == "ce" for w in (2, 4, 8))                  # fused with AdamW: always the CE pull
+    assert pick(8, override="peer") == "peer" and pick(2, override="nvls") == "nvls"
+    assert pick(2, override="nvls", mc=False) == "ce"                           # an override cannot invent a mapping
+    assert pick(8, forced=True) == "nvls" and pick(8, forced=True, mc=False) == "peer" and pick(8, forced=False) == "peer"
