@@ -228,15 +228,21 @@ def _moment_energy(eng):
     return t.item()
 
 
-def w_ws_save(rank, world, tmp):
-    from pathlib import Path
-
-    from b200train.ckpt.dcp import save_sharded
+def _ws_engine(strategy, seed=0):
     from b200train.models import load_config
     from b200train.parallel import make_strategy
 
     cfg = load_config("llama-tiny")
-    eng = make_strategy("fsdp", cfg, "cpu", lr=1e-3, dtype=torch.float32)
+    kw = dict(zero1=True) if strategy == "ddp" else {}
+    return cfg, make_strategy(strategy, cfg, "cpu", lr=1e-3, dtype=torch.float32, seed=seed, **kw)
+
+
+def w_ws_save(rank, world, tmp, strategy="fsdp"):
+    from pathlib import Path
+
+    from b200train.ckpt.dcp import save_sharded
+
+    cfg, eng = _ws_engine(strategy)
     ids = _batches(cfg, 1, 4, 32)[0]
     for _ in range(2):
         eng.train_step({"input_ids": ids[rank::world], "labels": ids[rank::world]})
@@ -246,15 +252,12 @@ def w_ws_save(rank, world, tmp):
     return probe, _moment_energy(eng)
 
 
-def w_ws_load(rank, world, tmp):
+def w_ws_load(rank, world, tmp, strategy="fsdp"):
     from pathlib import Path
 
     from b200train.ckpt.dcp import load_sharded
-    from b200train.models import load_config
-    from b200train.parallel import make_strategy
 
-    cfg = load_config("llama-tiny")
-    eng = make_strategy("fsdp", cfg, "cpu", lr=1e-3, dtype=torch.float32, seed=99)
+    cfg, eng = _ws_engine(strategy, seed=99)
     load_sharded(Path(tmp), eng)
     ids = _batches(cfg, 1, 4, 32)[0]
     with torch.no_grad():
@@ -262,13 +265,15 @@ def w_ws_load(rank, world, tmp):
     return probe, _moment_energy(eng), eng.optimizer_step_count()
 
 
-def test_sharded_checkpoint_loads_into_a_different_world_size():
+@pytest.mark.parametrize("strategy,new_worlds", [("fsdp", (3, 1)), ("ddp", (3,))])
+def test_sharded_checkpoint_loads_into_a_different_world_size(strategy, new_worlds):
     """Elastic restarts change the number of ranks: a checkpoint written by 2 ranks must load into 3 (chunks that
-    do not divide evenly) and into 1 (nothing sharded), with the same weights, moments and step count."""
+    do not divide evenly) and into 1 (nothing sharded), with the same weights, moments and step count -- for FSDP
+    and for DDP with a sharded (ZeRO-1) optimizer."""
     tmp = tempfile.mkdtemp()
-    probe, energy = run_dist("w_ws_save", tmp, world=2)[0]
-    for new_world in (3, 1):
-        got = run_dist("w_ws_load", tmp, world=new_world)[0]
+    probe, energy = run_dist("w_ws_save", tmp, strategy, world=2)[0]
+    for new_world in new_worlds:
+        got = run_dist("w_ws_load", tmp, strategy, world=new_world)[0]
         assert abs(got[0] - probe) < 1e-5, (new_world, got, probe)
         assert abs(got[1] - energy) <= 1e-6 * max(energy, 1e-12), (new_world, got, energy)
         assert got[2] == 2
